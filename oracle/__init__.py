@@ -1,0 +1,20 @@
+"""CPU oracle for the Pynama KLE hot path -- TEST INFRASTRUCTURE ONLY.
+
+This package is a numpy/scipy restatement of the reference's algorithm for the
+hot path named in BASELINE.json (spectral-element KLE matrices and operators,
+their scatter-add assembly, the KLE solve, the vorticity-transport RHS and the
+RK5(4)BS step).  Every function cites the reference file:line it follows.
+
+Only ``tests/``, ``__graft_entry__.smoke()`` and ``bench.py``'s CPU-baseline /
+``--impl reference`` legs may import it.  Nothing under ``pynama_b200/`` does:
+the product path is CUDA behind ``libpynama_b200.so`` and fails loudly without
+it.
+
+Pinning: the element tables and element matrices are pinned against golden
+vectors generated from the reference's own ``Spectral`` class
+(``tests/golden/make_golden.py`` -> ``tests/golden/*.npz``); the assembled
+solve is pinned through the reference's known-answer tests KAT-1/2/3
+(``src/tests/test_solver.py``).  Global node numbering of PETSc DMPlex for
+ngl >= 3, PETSc's TS adaptivity and KSP internals are NOT in the reference
+tree: for those parts parity is unpinned.
+"""
