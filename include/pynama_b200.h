@@ -1,0 +1,185 @@
+/* pynama_b200.h -- C ABI of libpynama_b200.so (B200 / sm_100a).
+ *
+ * The reference (maiterm/Pynama) has no FFI: its hot path calls petsc4py
+ * objects directly.  The entry points below are what a ctypes/cffi binding of
+ * that path binds instead; each one names the reference call site it replaces
+ * (paths relative to the reference root).  All functions return 0 on success
+ * and a negative PYN_E_* code on failure; pyn_last_error() gives the message.
+ * Handles are opaque and owned by the library; host pointers are borrowed for
+ * the duration of the call.  Reals are IEEE fp64, node/column ids int32, row
+ * pointers / nnz / contribution counts int64.  There is no CPU fallback: every
+ * compute entry point needs a context created on a CUDA device.
+ */
+#ifndef PYNAMA_B200_H
+#define PYNAMA_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PYN_OK 0
+#define PYN_E_INVALID (-1)   /* bad argument */
+#define PYN_E_CUDA (-2)      /* CUDA runtime error (message in pyn_last_error) */
+#define PYN_E_NOMEM (-3)
+#define PYN_E_UNSUPPORTED (-4)
+#define PYN_E_NCCL (-5)
+
+typedef struct pyn_ctx pyn_ctx;
+typedef struct pyn_mesh pyn_mesh;
+typedef struct pyn_mat pyn_mat;
+typedef struct pyn_vec pyn_vec;
+typedef struct pyn_ksp pyn_ksp;
+
+int pyn_version(void);
+const char* pyn_last_error(void);
+
+/* ---- host-only helpers (no GPU needed) -------------------------------------
+ * Reference-element tables, src/domain/elements/utilities.py:43-92 (1-D rules),
+ * element.py:13-44 (Lagrange basis), spectral.py:230-252,356-441 (local order). */
+/* kind: 0 = Gauss-Legendre, 1 = Gauss-Lobatto-Legendre; x,w: n doubles. */
+int pyn_rule_1d(int kind, int n, double* x, double* w);
+/* h, dh: npts*nnodes doubles, row-major [point][node]. */
+int pyn_lagrange_1d(int nnodes, const double* nodes, int npts, const double* pts,
+                    double* h, double* dh);
+/* Tensor index (a1,a2[,a3]) of every local position of an n^dim grid, in the
+ * reference's vertex/edge/face/body order: out is n^dim * dim int32. */
+int pyn_local_order(int dim, int n, int32_t* out);
+
+/* ---- context ---------------------------------------------------------------*/
+int pyn_init(int device, pyn_ctx** out);
+int pyn_finalize(pyn_ctx* ctx);
+int pyn_sync(pyn_ctx* ctx);
+/* CUDA-event stopwatch on the library's stream (bench.py's device timing). */
+int pyn_timer_start(pyn_ctx* ctx);
+int pyn_timer_stop(pyn_ctx* ctx, double* ms);
+/* number of kernels this library has launched on ctx so far */
+int pyn_launch_count(pyn_ctx* ctx, int64_t* count);
+/* write `bytes` of device scratch (> L2) to evict the cache between timed runs */
+int pyn_flush_l2(pyn_ctx* ctx);
+/* device memory in use by library objects of this context */
+int pyn_mem_used(pyn_ctx* ctx, int64_t* bytes);
+
+/* ---- mesh tables (inputs A0: dmplex.py:93-100,193-196; domain.py:233-250) ----
+ * corner_xyz: nel * 2^dim * dim, DMPlex closure-vertex order;
+ * elem_nodes: nel * ngl^dim global node ids in the reference's local order.
+ * The symbolic node graph (sort + unique of the COO keys) is built here;
+ * replaces DMPlexDom.getConnectivityNodes (dmplex.py:352-372) and the
+ * preallocation of mat_fs.py:21-113. */
+int pyn_mesh_create(pyn_ctx* ctx, int dim, int ngl, int64_t nel, int64_t nnodes,
+                    const double* corner_xyz, const int32_t* elem_nodes, pyn_mesh** out);
+int pyn_mesh_destroy(pyn_mesh* mesh);
+/* node-graph statistics: number of (row node, col node) pairs, COO length */
+int pyn_mesh_graph_info(pyn_mesh* mesh, int64_t* npairs, int64_t* ncontrib, int* max_row);
+/* dof classes of the velocity dofs (nnodes*dim bytes): 0 free, 1 Dirichlet
+ * (free-slip BC, mat_fs.py:158-172), 2 no-slip normal, 3 no-slip tangential
+ * (mat_ns.py:59-75). */
+int pyn_mesh_set_dof_class(pyn_mesh* mesh, const uint8_t* cls);
+
+/* ---- element kernels (debug / parity export of raw element blocks) ---------
+ * Spectral.getElemKLEMatrices (spectral.py:92-160): K_e [3nn x 3nn],
+ * Rw_e [dim*nn x dim_w*nn], Rd_e [dim*nn x nn] per element, row-major, dofs
+ * interleaved node*ncomp+comp.  Output pointers are HOST buffers (may be NULL). */
+int pyn_elem_kle(pyn_mesh* mesh, int64_t e0, int64_t ne, double* K_e, double* Rw_e, double* Rd_e);
+/* Spectral.getElemKLEOperators (spectral.py:162-228): SrT_e [dim_s*nn x dim*nn],
+ * DivSrT_e [dim*nn x dim_s*nn], Curl_e [dim_w*nn x dim*nn], W_e [nn]. */
+int pyn_elem_ops(pyn_mesh* mesh, int64_t e0, int64_t ne, double* SrT_e, double* Div_e,
+                 double* Curl_e, double* W_e);
+
+/* ---- assembly ----------------------------------------------------------------
+ * mode 0: MatFS.build/buildFS (mat_fs.py:131-192) -> out[0..3] = K, Krhs, Rw, Rd(NULL)
+ * mode 1: MatNS.build/buildNS (mat_ns.py:47-166)  -> out[0..7] = K, Krhs, Rw, Rd,
+ *         Kfs, Krhsfs, Rwfs, Rdfs.  Needs pyn_mesh_set_dof_class first. */
+#define PYN_MAT_K 0
+#define PYN_MAT_KRHS 1
+#define PYN_MAT_RW 2
+#define PYN_MAT_RD 3
+#define PYN_MAT_KFS 4
+#define PYN_MAT_KRHSFS 5
+#define PYN_MAT_RWFS 6
+#define PYN_MAT_RDFS 7
+int pyn_assemble_kle(pyn_mesh* mesh, int mode, pyn_mat** out8);
+/* MatFS.buildOperators + Operators.setValues/assembleAll (mat_fs.py:194-271):
+ * Curl, SrT, DivSrT already row-scaled by the reciprocal lumped mass; weights =
+ * per-node lumped mass before the reciprocal (the reference's weig* vectors
+ * repeat it per component).  compact != 0 stores only the structurally
+ * non-zero node blocks (the exported CSR still carries the reference's
+ * explicit zeros). */
+int pyn_assemble_ops(pyn_mesh* mesh, int compact, pyn_mat** curl, pyn_mat** srt,
+                     pyn_mat** divsrt, pyn_vec** weights);
+/* CUDA-event time of the last assembly phases on this mesh:
+ * 0 symbolic graph, 1 element KLE kernel, 2 KLE numeric, 3 element operator
+ * kernel, 4 operator numeric */
+int pyn_mesh_phase_ms(pyn_mesh* mesh, int phase, double* ms);
+
+/* ---- Mat (PETSc.Mat AIJ surface used by the hot path) --------------------------*/
+int pyn_mat_shape(pyn_mat* m, int64_t* nrows, int64_t* ncols, int* br, int* bc);
+/* nnz of the reference (scalar AIJ, explicit zeros kept) pattern and stored blocks */
+int pyn_mat_nnz(pyn_mat* m, int64_t* nnz_ref, int64_t* nblocks);
+/* scalar CSR in the reference pattern; rowptr nrows+1, col/val nnz_ref */
+int pyn_mat_export_csr(pyn_mat* m, int64_t* rowptr, int32_t* col, double* val);
+/* y = A x   (Mat.mult, base_problem.py:123-136; Mat.__mul__, kle_solver.py:35-41) */
+int pyn_mat_mult(pyn_mat* m, pyn_vec* x, pyn_vec* y);
+/* y = alpha*A x + beta*z  (z may alias y or be NULL when beta == 0) */
+int pyn_mat_mult_axpby(pyn_mat* m, double alpha, pyn_vec* x, double beta, pyn_vec* z, pyn_vec* y);
+/* C = A + B on the union pattern (K + Kfs, kle_solver.py:25) */
+int pyn_mat_add_new(pyn_mat* a, pyn_mat* b, pyn_mat** out);
+int pyn_mat_get_diagonal(pyn_mat* m, pyn_vec* d);
+/* A <- diag(l) A  (Mat.diagonalScale(L=), mat_fs.py:257-267) */
+int pyn_mat_scale_rows(pyn_mat* m, pyn_vec* l);
+int pyn_mat_bytes(pyn_mat* m, int64_t* stored_bytes, int64_t* spmv_bytes);
+int pyn_mat_destroy(pyn_mat* m);
+
+/* ---- Vec (PETSc.Vec surface used by the hot path) ---------------------------------*/
+int pyn_vec_create(pyn_ctx* ctx, int64_t n, pyn_vec** out);
+int pyn_vec_destroy(pyn_vec* v);
+int pyn_vec_size(pyn_vec* v, int64_t* n);
+int pyn_vec_set(pyn_vec* v, double a);
+int pyn_vec_copy(pyn_vec* src, pyn_vec* dst);
+int pyn_vec_scale(pyn_vec* v, double a);
+int pyn_vec_axpy(pyn_vec* y, double a, pyn_vec* x);              /* y += a x */
+int pyn_vec_aypx(pyn_vec* y, double a, pyn_vec* x);              /* y = a y + x */
+int pyn_vec_waxpy(pyn_vec* w, double a, pyn_vec* x, pyn_vec* y); /* w = a x + y */
+int pyn_vec_axpby(pyn_vec* y, double a, pyn_vec* x, double b);   /* y = a x + b y */
+int pyn_vec_pointwise_mult(pyn_vec* w, pyn_vec* x, pyn_vec* y);
+int pyn_vec_reciprocal(pyn_vec* v);
+int pyn_vec_dot(pyn_vec* x, pyn_vec* y, double* out);
+int pyn_vec_norm2(pyn_vec* x, double* out);
+int pyn_vec_sum(pyn_vec* x, double* out);
+/* y = y + sum_k a[k] x[k]   (VecMAXPY; RK stage combination) */
+int pyn_vec_maxpy(pyn_vec* y, int k, const double* a, pyn_vec* const* x);
+/* Vec.setValues(idx, vals, addv) (boundary_conditions.py:252-260) */
+int pyn_vec_set_values(pyn_vec* v, int64_t k, const int64_t* idx, const double* vals, int add);
+int pyn_vec_get_values(pyn_vec* v, int64_t k, const int64_t* idx, double* vals);
+/* persistent scatter plan: indices uploaded once, values per call (k10) */
+int pyn_vec_to_host(pyn_vec* v, double* out);
+int pyn_vec_from_host(pyn_vec* v, const double* in);
+/* raw device pointer (for torch.distributed plumbing) */
+int pyn_vec_device_ptr(pyn_vec* v, void** ptr);
+
+/* ---- KSP (solver/kle_solver.py:49-64 -> PETSc KSP/PC) -------------------------------*/
+#define PYN_KSP_CG 0
+#define PYN_KSP_GMRES 1
+#define PYN_KSP_BCGS 2
+#define PYN_KSP_PREONLY 3
+#define PYN_PC_NONE 0
+#define PYN_PC_JACOBI 1
+#define PYN_PC_BJACOBI 2 /* node-block (br x br) Jacobi */
+int pyn_ksp_create(pyn_ctx* ctx, pyn_mat* a, int type, int pc, pyn_ksp** out);
+int pyn_ksp_set_tolerances(pyn_ksp* k, double rtol, double atol, int maxit, int restart);
+/* x: initial guess in, solution out (KSP.__call__(b, x), kle_solver.py:35).
+ * reason > 0 converged (2 rtol, 3 atol), < 0 diverged (-3 max iterations). */
+int pyn_ksp_solve(pyn_ksp* k, pyn_vec* b, pyn_vec* x, int* its, int* reason, double* rnorm);
+int pyn_ksp_destroy(pyn_ksp* k);
+
+/* ---- vorticity-transport RHS pieces (cases/base_problem.py:111-154) --------------------*/
+/* computeVtensV (base_problem.py:139-154): out[node*dim_s + s] packed v (x) v */
+int pyn_vtensv(pyn_vec* vel, pyn_vec* out, int dim);
+/* aux = 2 mu * aux - rho * vtensv(vel)   (base_problem.py:127-130 fused) */
+int pyn_stress_combine(pyn_vec* aux, pyn_vec* vel, double mu, double rho, int dim);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PYNAMA_B200_H */

@@ -1,0 +1,158 @@
+// common.cuh -- context, error plumbing, device buffers shared by all kernels.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/pynama_b200.h"
+
+#ifndef PYN_HD
+#ifdef __CUDACC__
+#define PYN_HD __host__ __device__ __forceinline__
+#else
+#define PYN_HD inline
+#endif
+#endif
+
+namespace pyn {
+
+void set_error(const char* fmt, ...);
+
+#define PYN_CUDA(call)                                                                 \
+  do {                                                                                 \
+    cudaError_t _e = (call);                                                           \
+    if (_e != cudaSuccess) {                                                           \
+      pyn::set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(_e)); \
+      return PYN_E_CUDA;                                                               \
+    }                                                                                  \
+  } while (0)
+
+#define PYN_CHECK(call)         \
+  do {                          \
+    int _r = (call);            \
+    if (_r != PYN_OK) return _r; \
+  } while (0)
+
+#define PYN_REQUIRE(cond, ...)      \
+  do {                              \
+    if (!(cond)) {                  \
+      pyn::set_error(__VA_ARGS__);  \
+      return PYN_E_INVALID;         \
+    }                               \
+  } while (0)
+
+// after a kernel launch
+#define PYN_LAUNCHED(ctx)             \
+  do {                                \
+    (ctx)->launches++;                \
+    PYN_CUDA(cudaGetLastError());     \
+  } while (0)
+
+constexpr int kNumSMs = 148;  // B200: 2 dies x 74 SMs
+
+}  // namespace pyn
+
+struct pyn_ctx {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  int64_t launches = 0;
+  int64_t bytes_in_use = 0;
+  int num_sms = pyn::kNumSMs;
+  size_t smem_optin = 0;
+  // reduction scratch: per-CTA partials + ticket + pinned result
+  double* red_partials = nullptr;   // [kRedMaxBlocks * kRedMaxVals]
+  unsigned int* red_ticket = nullptr;
+  double* red_result_dev = nullptr; // [kRedMaxVals]
+  double* red_result_host = nullptr;  // pinned
+  void* flush_buf = nullptr;
+  size_t flush_bytes = 0;
+};
+
+namespace pyn {
+
+constexpr int kRedMaxBlocks = 1184;  // 8 CTAs per SM
+constexpr int kRedMaxVals = 8;
+
+// Device buffer with byte accounting on the owning context.
+template <typename T>
+struct DevBuf {
+  T* p = nullptr;
+  int64_t n = 0;
+  pyn_ctx* ctx = nullptr;
+  DevBuf() {}
+  DevBuf(const DevBuf&) = delete;
+  DevBuf& operator=(const DevBuf&) = delete;
+  ~DevBuf() { release(); }
+  int alloc(pyn_ctx* c, int64_t count) {
+    release();
+    ctx = c;
+    n = count;
+    if (count <= 0) return PYN_OK;
+    cudaError_t e = cudaMalloc((void**)&p, sizeof(T) * (size_t)count);
+    if (e != cudaSuccess) {
+      p = nullptr;
+      n = 0;
+      set_error("cudaMalloc(%lld bytes) failed: %s", (long long)(sizeof(T) * count),
+                cudaGetErrorString(e));
+      return PYN_E_NOMEM;
+    }
+    ctx->bytes_in_use += (int64_t)sizeof(T) * count;
+    return PYN_OK;
+  }
+  int zero() {
+    if (n > 0) PYN_CUDA(cudaMemsetAsync(p, 0, sizeof(T) * (size_t)n, ctx->stream));
+    return PYN_OK;
+  }
+  int upload(const T* host, int64_t count) {
+    if (count > 0)
+      PYN_CUDA(cudaMemcpyAsync(p, host, sizeof(T) * (size_t)count, cudaMemcpyHostToDevice, ctx->stream));
+    return PYN_OK;
+  }
+  int download(T* host, int64_t count) const {
+    if (count > 0) {
+      PYN_CUDA(cudaMemcpyAsync(host, p, sizeof(T) * (size_t)count, cudaMemcpyDeviceToHost, ctx->stream));
+      PYN_CUDA(cudaStreamSynchronize(ctx->stream));
+    }
+    return PYN_OK;
+  }
+  void release() {
+    if (p) {
+      cudaFree(p);
+      if (ctx) ctx->bytes_in_use -= (int64_t)sizeof(T) * n;
+    }
+    p = nullptr;
+    n = 0;
+  }
+  void swap(DevBuf& o) {
+    std::swap(p, o.p);
+    std::swap(n, o.n);
+    std::swap(ctx, o.ctx);
+  }
+};
+
+inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
+
+// grid size for a grid-stride kernel: a multiple of the SM count
+inline int grid_for(const pyn_ctx* ctx, int64_t work_items, int block, int ctas_per_sm = 8) {
+  int64_t need = ceil_div(work_items, block);
+  int64_t cap = (int64_t)ctx->num_sms * ctas_per_sm;
+  if (need < 1) need = 1;
+  return (int)(need < cap ? need : cap);
+}
+
+// exclusive scan of int64 counts on the device (single CTA chained; symbolic phase only)
+int exclusive_scan_i64(pyn_ctx* ctx, const int64_t* in, int64_t* out, int64_t n, int64_t* total_host);
+int exclusive_scan_i32_to_i64(pyn_ctx* ctx, const int32_t* in, int64_t* out, int64_t n, int64_t* total_host);
+
+}  // namespace pyn
+
+struct pyn_vec {
+  pyn_ctx* ctx = nullptr;
+  int64_t n = 0;
+  pyn::DevBuf<double> d;
+};

@@ -1,0 +1,407 @@
+// ksp.cu -- Krylov solve of the KLE system (k7): replaces the PETSc KSP/PC the
+// reference configures in KspSolver.createSolver (kle_solver.py:49-64) and calls
+// in KleSolver.solve (kle_solver.py:33-41).
+//
+// Preconditioned CG (K is SPD after Dirichlet elimination) with Jacobi or
+// node-block Jacobi.  All Krylov scalars live on the device; an iteration is
+//   (1) w = A p fused with p.w            (SpMV, one HBM pass over A)
+//   (2) x += a p; r -= a w; z = M^-1 r; r.z and z.z reduced in the same pass
+//   (3) p = z + b p
+// and the convergence test (PETSc's default: preconditioned residual norm
+// against max(rtol*||M^-1 b||, atol)) is evaluated on the device by the last
+// CTA of (2).  The host only polls a pinned status word every few iterations;
+// iterations launched after convergence return immediately.
+#include "ksp.cuh"
+#include "vec.cuh"
+
+namespace pyn {
+
+// device scalar block
+enum {
+  S_RZ0 = 0,   // r.z, ping
+  S_RZ1 = 1,   // r.z, pong
+  S_PW = 2,    // p.Ap
+  S_ZZ = 3,    // z.z (preconditioned residual norm^2)
+  S_DONE = 4,  // != 0 once converged / broken down
+  S_ITS = 5,   // iterations performed
+  S_TTOL = 6,  // absolute threshold on sqrt(S_ZZ)
+  S_REASON = 7,
+  S_RNORM = 8,
+  S_DTOL = 9,
+  S_COUNT = 16
+};
+
+template <int B>
+__device__ __forceinline__ void apply_pc_node(int pc, const double* __restrict__ pcd, int64_t node,
+                                              const double* r, double* z) {
+  if (pc == PYN_PC_NONE) {
+#pragma unroll
+    for (int i = 0; i < B; ++i) z[i] = r[i];
+  } else if (pc == PYN_PC_JACOBI) {
+#pragma unroll
+    for (int i = 0; i < B; ++i) z[i] = pcd[node * B + i] * r[i];
+  } else {
+#pragma unroll
+    for (int i = 0; i < B; ++i) {
+      double s = 0.0;
+#pragma unroll
+      for (int j = 0; j < B; ++j) s += pcd[(node * B + i) * B + j] * r[j];
+      z[i] = s;
+    }
+  }
+}
+
+// z = M^-1 r ; out[0] = r.z ; out[1] = z.z          (set-up and residual restarts)
+template <int B>
+__global__ void __launch_bounds__(256)
+pc_apply_dots_kernel(int pc, const double* __restrict__ pcd, const double* __restrict__ r,
+                     double* __restrict__ z, int64_t nnodes, double* partials, unsigned int* ticket,
+                     double* out) {
+  __shared__ double sm[64];
+  double v[2] = {0.0, 0.0};
+  for (int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; n < nnodes;
+       n += (int64_t)gridDim.x * blockDim.x) {
+    double rr[B], zz[B];
+#pragma unroll
+    for (int i = 0; i < B; ++i) rr[i] = r[n * B + i];
+    apply_pc_node<B>(pc, pcd, n, rr, zz);
+#pragma unroll
+    for (int i = 0; i < B; ++i) {
+      z[n * B + i] = zz[i];
+      v[0] += rr[i] * zz[i];
+      v[1] += zz[i] * zz[i];
+    }
+  }
+  block_reduce<2>(v, sm);
+  grid_reduce_finish<2>(v, partials, ticket, out);
+}
+
+// step (2) of the iteration + convergence test in the last CTA
+template <int B>
+__global__ void __launch_bounds__(256)
+cg_update_kernel(int pc, const double* __restrict__ pcd, const double* __restrict__ p,
+                 const double* __restrict__ w, double* __restrict__ x, double* __restrict__ r,
+                 double* __restrict__ z, int64_t nnodes, double* S, int parity, int maxit,
+                 double* partials, unsigned int* ticket) {
+  __shared__ double sm[64];
+  __shared__ bool is_last;
+  if (S[S_DONE] != 0.0) return;
+  const double rz = S[parity ? S_RZ1 : S_RZ0];
+  const double pw = S[S_PW];
+  const double alpha = rz / pw;
+  double v[2] = {0.0, 0.0};
+  for (int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; n < nnodes;
+       n += (int64_t)gridDim.x * blockDim.x) {
+    double rr[B], zz[B];
+#pragma unroll
+    for (int i = 0; i < B; ++i) {
+      x[n * B + i] += alpha * p[n * B + i];
+      rr[i] = r[n * B + i] - alpha * w[n * B + i];
+      r[n * B + i] = rr[i];
+    }
+    apply_pc_node<B>(pc, pcd, n, rr, zz);
+#pragma unroll
+    for (int i = 0; i < B; ++i) {
+      z[n * B + i] = zz[i];
+      v[0] += rr[i] * zz[i];
+      v[1] += zz[i] * zz[i];
+    }
+  }
+  block_reduce<2>(v, sm);
+  // grid reduction, then the scalar bookkeeping by the last CTA
+  if (threadIdx.x == 0) {
+    partials[(size_t)blockIdx.x * 2 + 0] = v[0];
+    partials[(size_t)blockIdx.x * 2 + 1] = v[1];
+    __threadfence();
+    is_last = (atomicAdd(ticket, 1u) == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  if (wid < 2) {
+    double t = 0.0;
+    for (unsigned int b = lane; b < gridDim.x; b += 32) t += partials[(size_t)b * 2 + wid];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+    if (lane == 0) sm[wid] = t;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    *ticket = 0u;
+    const double rz_new = sm[0], zz = sm[1];
+    S[parity ? S_RZ0 : S_RZ1] = rz_new;
+    S[S_ZZ] = zz;
+    const double its = S[S_ITS] + 1.0;
+    S[S_ITS] = its;
+    const double rn = sqrt(zz);
+    S[S_RNORM] = rn;
+    if (!(rn == rn) || !(pw == pw) || pw == 0.0) {       // NaN / breakdown
+      S[S_REASON] = -9.0;
+      S[S_DONE] = 1.0;
+    } else if (rn <= S[S_TTOL]) {
+      S[S_REASON] = S[S_REASON] == 0.0 ? 2.0 : S[S_REASON];
+      S[S_DONE] = 1.0;
+    } else if (rn >= S[S_DTOL]) {
+      S[S_REASON] = -4.0;                                  // DIVERGED_DTOL
+      S[S_DONE] = 1.0;
+    } else if (its >= (double)maxit) {
+      S[S_REASON] = -3.0;                                  // DIVERGED_ITS
+      S[S_DONE] = 1.0;
+    }
+  }
+}
+
+// step (3): p = z + (rz_new/rz_old) p
+__global__ void __launch_bounds__(256)
+cg_direction_kernel(const double* __restrict__ z, double* __restrict__ p, int64_t n, const double* S,
+                    int parity) {
+  if (S[S_DONE] != 0.0) return;
+  const double beta = S[parity ? S_RZ0 : S_RZ1] / S[parity ? S_RZ1 : S_RZ0];
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (int64_t)gridDim.x * blockDim.x)
+    p[i] = z[i] + beta * p[i];
+}
+
+// start-up scalars: out2 = {r.z, z.z} of the initial residual, bnorm2 = {.., ||M^-1 b||^2}
+__global__ void cg_init_scalars_kernel(double* S, const double* rz_zz, const double* b_zz, double rtol,
+                                       double atol, double dtol, int zero_guess) {
+  const double bn = sqrt(b_zz[1]);
+  const double rn = sqrt(rz_zz[1]);
+  double ttol = rtol * bn;
+  double reason_if = 2.0;
+  if (atol > ttol) {
+    ttol = atol;
+    reason_if = 3.0;
+  }
+  S[S_RZ0] = rz_zz[0];
+  S[S_RZ1] = 0.0;
+  S[S_PW] = 0.0;
+  S[S_ZZ] = rz_zz[1];
+  S[S_ITS] = 0.0;
+  S[S_TTOL] = ttol;
+  S[S_DTOL] = dtol * (bn > 0.0 ? bn : 1.0);
+  S[S_RNORM] = rn;
+  S[S_REASON] = reason_if == 3.0 ? 3.0 : 0.0;
+  S[S_DONE] = 0.0;
+  if (rn <= ttol) {            // converged before the first iteration (also b = 0)
+    S[S_REASON] = reason_if;
+    S[S_DONE] = 1.0;
+  }
+  (void)zero_guess;
+}
+
+// Jacobi / node-block Jacobi set-up from the diagonal blocks
+template <int B>
+__global__ void pc_setup_kernel(int pc, const double* __restrict__ dblk, double* __restrict__ pcd,
+                                int64_t nnodes) {
+  for (int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; n < nnodes;
+       n += (int64_t)gridDim.x * blockDim.x) {
+    const double* d = dblk + n * B * B;
+    if (pc == PYN_PC_JACOBI) {
+      for (int i = 0; i < B; ++i) {
+        const double v = d[i * B + i];
+        pcd[n * B + i] = v != 0.0 ? 1.0 / v : 1.0;   // PCJacobi replaces zero diagonals by 1
+      }
+    } else {
+      double inv[B * B];
+      bool ok = true;
+      if (B == 1) {
+        ok = d[0] != 0.0;
+        inv[0] = ok ? 1.0 / d[0] : 1.0;
+      } else if (B == 2) {
+        const double det = d[0] * d[3] - d[1] * d[2];
+        ok = det != 0.0;
+        if (ok) {
+          inv[0] = d[3] / det; inv[1] = -d[1] / det; inv[2] = -d[2] / det; inv[3] = d[0] / det;
+        }
+      } else {
+        const double c0 = d[4] * d[8] - d[5] * d[7], c1 = d[5] * d[6] - d[3] * d[8],
+                     c2 = d[3] * d[7] - d[4] * d[6];
+        const double det = d[0] * c0 + d[1] * c1 + d[2] * c2;
+        ok = det != 0.0;
+        if (ok) {
+          const double id = 1.0 / det;
+          inv[0] = c0 * id;
+          inv[1] = (d[2] * d[7] - d[1] * d[8]) * id;
+          inv[2] = (d[1] * d[5] - d[2] * d[4]) * id;
+          inv[3] = c1 * id;
+          inv[4] = (d[0] * d[8] - d[2] * d[6]) * id;
+          inv[5] = (d[2] * d[3] - d[0] * d[5]) * id;
+          inv[6] = c2 * id;
+          inv[7] = (d[1] * d[6] - d[0] * d[7]) * id;
+          inv[8] = (d[0] * d[4] - d[1] * d[3]) * id;
+        }
+      }
+      for (int q = 0; q < B * B; ++q)
+        pcd[n * B * B + q] = ok ? inv[q] : ((q / B == q % B) ? 1.0 : 0.0);
+    }
+  }
+}
+
+}  // namespace pyn
+
+using namespace pyn;
+
+struct pyn_ksp {
+  pyn_ctx* ctx = nullptr;
+  pyn_mat* A = nullptr;
+  int type = PYN_KSP_CG, pc = PYN_PC_BJACOBI;
+  double rtol = 1e-5, atol = 1e-50, dtol = 1e5;
+  int maxit = 10000, restart = 30;
+  int check_every = 8;
+  int B = 0;
+  int64_t n = 0, nnodes = 0;
+  DevBuf<double> pcd, r, z, p, w, S, tmp2;
+  double* status_host = nullptr;  // pinned [2][S_COUNT]
+  cudaEvent_t ev[2] = {nullptr, nullptr};
+  bool pc_ready = false;
+};
+
+template <int B>
+static int ksp_setup_pc(pyn_ksp* k) {
+  pyn_ctx* ctx = k->ctx;
+  if (k->pc == PYN_PC_NONE) {
+    k->pc_ready = true;
+    return PYN_OK;
+  }
+  DevBuf<double> dblk;
+  PYN_CHECK(dblk.alloc(ctx, k->nnodes * B * B));
+  PYN_CHECK(diag_blocks(k->A, dblk.p));
+  PYN_CHECK(k->pcd.alloc(ctx, k->pc == PYN_PC_JACOBI ? k->n : k->nnodes * B * B));
+  pc_setup_kernel<B><<<grid_for(ctx, k->nnodes, 128), 128, 0, ctx->stream>>>(k->pc, dblk.p, k->pcd.p, k->nnodes);
+  PYN_LAUNCHED(ctx);
+  PYN_CUDA(cudaStreamSynchronize(ctx->stream));
+  k->pc_ready = true;
+  return PYN_OK;
+}
+
+template <int B>
+static int ksp_solve_cg(pyn_ksp* k, const double* b, double* x, int* its, int* reason, double* rnorm) {
+  pyn_ctx* ctx = k->ctx;
+  const int64_t n = k->n, nn = k->nnodes;
+  double* S = k->S.p;
+  const int gridn = grid_for(ctx, nn, 256);
+  if (!k->pc_ready) PYN_CHECK(ksp_setup_pc<B>(k));
+  // ||M^-1 b|| for the threshold (KSPConvergedDefault with the preconditioned norm)
+  pc_apply_dots_kernel<B><<<gridn, 256, 0, ctx->stream>>>(k->pc, k->pcd.p, b, k->z.p, nn, ctx->red_partials,
+                                                          ctx->red_ticket, k->tmp2.p + 2);
+  PYN_LAUNCHED(ctx);
+  // r = b - A x ; z = M^-1 r ; p = z
+  PYN_CHECK(spmv(k->A, -1.0, x, 1.0, b, k->r.p));
+  pc_apply_dots_kernel<B><<<gridn, 256, 0, ctx->stream>>>(k->pc, k->pcd.p, k->r.p, k->z.p, nn,
+                                                          ctx->red_partials, ctx->red_ticket, k->tmp2.p);
+  PYN_LAUNCHED(ctx);
+  cg_init_scalars_kernel<<<1, 1, 0, ctx->stream>>>(S, k->tmp2.p, k->tmp2.p + 2, k->rtol, k->atol, k->dtol, 0);
+  PYN_LAUNCHED(ctx);
+  PYN_CUDA(cudaMemcpyAsync(k->p.p, k->z.p, sizeof(double) * n, cudaMemcpyDeviceToDevice, ctx->stream));
+
+  // Chunks of `check_every` iterations; the status of chunk c-1 is read while
+  // chunk c runs, so the GPU never idles on the host.
+  int it = 0;
+  for (int chunk = 0;; ++chunk) {
+    const int todo = (k->maxit - it) < k->check_every ? (k->maxit - it) : k->check_every;
+    for (int j = 0; j < todo; ++j, ++it) {
+      const int parity = it & 1;
+      PYN_CHECK(spmv_dot(k->A, k->p.p, k->w.p, S + S_PW, S + S_DONE));
+      cg_update_kernel<B><<<gridn, 256, 0, ctx->stream>>>(k->pc, k->pcd.p, k->p.p, k->w.p, x, k->r.p,
+                                                          k->z.p, nn, S, parity, k->maxit,
+                                                          ctx->red_partials, ctx->red_ticket);
+      PYN_LAUNCHED(ctx);
+      cg_direction_kernel<<<grid_for(ctx, n, 256), 256, 0, ctx->stream>>>(k->z.p, k->p.p, n, S, parity);
+      PYN_LAUNCHED(ctx);
+    }
+    const int slot = chunk & 1;
+    PYN_CUDA(cudaMemcpyAsync(k->status_host + slot * S_COUNT, S, sizeof(double) * S_COUNT,
+                             cudaMemcpyDeviceToHost, ctx->stream));
+    PYN_CUDA(cudaEventRecord(k->ev[slot], ctx->stream));
+    if (chunk >= 1) {
+      PYN_CUDA(cudaEventSynchronize(k->ev[slot ^ 1]));
+      if (k->status_host[(slot ^ 1) * S_COUNT + S_DONE] != 0.0) break;
+    }
+    if (it >= k->maxit) break;
+  }
+  PYN_CUDA(cudaStreamSynchronize(ctx->stream));
+  PYN_CUDA(cudaMemcpyAsync(k->status_host, S, sizeof(double) * S_COUNT, cudaMemcpyDeviceToHost, ctx->stream));
+  PYN_CUDA(cudaStreamSynchronize(ctx->stream));
+  const double* st = k->status_host;
+  if (its) *its = (int)st[S_ITS];
+  if (reason) *reason = st[S_DONE] != 0.0 ? (int)st[S_REASON] : -3;
+  if (rnorm) *rnorm = st[S_RNORM];
+  return PYN_OK;
+}
+
+extern "C" {
+
+int pyn_ksp_create(pyn_ctx* ctx, pyn_mat* a, int type, int pc, pyn_ksp** out) {
+  PYN_REQUIRE(ctx && a && out, "pyn_ksp_create: null argument");
+  PYN_REQUIRE(a->br == a->bc && a->nbrows == a->nbcols, "KSP operator must be square");
+  PYN_REQUIRE(pc >= PYN_PC_NONE && pc <= PYN_PC_BJACOBI, "unknown pc type %d", pc);
+  if (type != PYN_KSP_CG) {
+    set_error("KSP type %d is not implemented yet (available: cg)", type);
+    return PYN_E_UNSUPPORTED;
+  }
+  pyn_ksp* k = new pyn_ksp();
+  k->ctx = ctx;
+  k->A = a;
+  k->type = type;
+  k->pc = pc;
+  k->B = a->br;
+  k->nnodes = a->nbrows;
+  k->n = a->nbrows * a->br;
+  int rc = PYN_OK;
+  if (rc == PYN_OK) rc = k->r.alloc(ctx, k->n);
+  if (rc == PYN_OK) rc = k->z.alloc(ctx, k->n);
+  if (rc == PYN_OK) rc = k->p.alloc(ctx, k->n);
+  if (rc == PYN_OK) rc = k->w.alloc(ctx, k->n);
+  if (rc == PYN_OK) rc = k->S.alloc(ctx, S_COUNT);
+  if (rc == PYN_OK) rc = k->tmp2.alloc(ctx, 4);
+  if (rc == PYN_OK && cudaMallocHost((void**)&k->status_host, sizeof(double) * 2 * S_COUNT) != cudaSuccess) {
+    set_error("cudaMallocHost failed");
+    rc = PYN_E_NOMEM;
+  }
+  if (rc == PYN_OK) {
+    cudaEventCreateWithFlags(&k->ev[0], cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&k->ev[1], cudaEventDisableTiming);
+  }
+  if (rc != PYN_OK) {
+    pyn_ksp_destroy(k);
+    return rc;
+  }
+  *out = k;
+  return PYN_OK;
+}
+
+int pyn_ksp_set_tolerances(pyn_ksp* k, double rtol, double atol, int maxit, int restart) {
+  PYN_REQUIRE(k, "null ksp");
+  if (rtol >= 0) k->rtol = rtol;
+  if (atol >= 0) k->atol = atol;
+  if (maxit > 0) k->maxit = maxit;
+  if (restart > 0) k->restart = restart;
+  return PYN_OK;
+}
+
+int pyn_ksp_solve(pyn_ksp* k, pyn_vec* b, pyn_vec* x, int* its, int* reason, double* rnorm) {
+  PYN_REQUIRE(k && b && x, "pyn_ksp_solve: null argument");
+  PYN_REQUIRE(b->n == k->n && x->n == k->n, "pyn_ksp_solve: vector size %lld/%lld, operator %lld",
+              (long long)b->n, (long long)x->n, (long long)k->n);
+  PYN_REQUIRE(b != x, "pyn_ksp_solve: b and x must differ");
+  switch (k->B) {
+    case 1: return ksp_solve_cg<1>(k, b->d.p, x->d.p, its, reason, rnorm);
+    case 2: return ksp_solve_cg<2>(k, b->d.p, x->d.p, its, reason, rnorm);
+    case 3: return ksp_solve_cg<3>(k, b->d.p, x->d.p, its, reason, rnorm);
+  }
+  set_error("unsupported block size %d", k->B);
+  return PYN_E_UNSUPPORTED;
+}
+
+int pyn_ksp_destroy(pyn_ksp* k) {
+  if (!k) return PYN_OK;
+  if (k->status_host) cudaFreeHost(k->status_host);
+  if (k->ev[0]) cudaEventDestroy(k->ev[0]);
+  if (k->ev[1]) cudaEventDestroy(k->ev[1]);
+  delete k;
+  return PYN_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,278 @@
+// spmv.cu -- node-block SpMV (k6) and the small Mat operations around it.
+//
+// y = alpha*A*x + beta*z on the row-plane BSR layout: a warp (or a sub-warp
+// group of G lanes for short rows) owns one block row; lane l takes blocks
+// l, l+G, ... and reads the same position of each of the br*bc planes, so
+// every plane load of the group is one contiguous run of 8-byte words.
+// Replaces PETSc MatMult on AIJ (kle_solver.py:35-41, base_problem.py:123-136).
+// HBM-bound: per block 8*br*bc bytes of values + 4 bytes of column index; x
+// (a few MB) lives in L2.
+#include "elem.cuh"
+#include "spmv.cuh"
+#include "vec.cuh"
+
+namespace pyn {
+
+// Optional fusions for the Krylov loop: `skip` (device flag, non-zero = solver
+// already converged -> return at once) and DOT (also reduce sum_i y_i*x_i, the
+// p.Ap of CG, into dot_out with the deterministic grid reduction).
+struct SpmvFuse {
+  const double* skip;
+  double* partials;
+  unsigned int* ticket;
+  double* dot_out;
+};
+
+template <int BR, int BC, int G, bool DOT>
+__global__ void __launch_bounds__(256)
+spmv_kernel(int64_t nbrows, const int64_t* __restrict__ rowptr, const int32_t* __restrict__ colidx,
+            const double* __restrict__ val, const double* __restrict__ x, double alpha, double beta,
+            const double* __restrict__ z, double* __restrict__ y, SpmvFuse fuse) {
+  constexpr int BB = BR * BC;
+  __shared__ double red_sm[32];
+  if (fuse.skip && *fuse.skip != 0.0) return;
+  double dotacc[1] = {0.0};
+  const int lane = threadIdx.x & (G - 1);
+  const int64_t grp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / G;
+  const int64_t ngrp = ((int64_t)gridDim.x * blockDim.x) / G;
+  // uniform trip count per warp: sub-warp groups past the end run empty rows
+  const int64_t iters = (nbrows + ngrp - 1) / ngrp;
+  for (int64_t it = 0; it < iters; ++it) {
+    const int64_t r = grp + it * ngrp;
+    const bool live = r < nbrows;
+    const int64_t p0 = live ? rowptr[r] : 0;
+    const int nb = live ? (int)(rowptr[r + 1] - p0) : 0;
+    const double* __restrict__ v = val + p0 * BB;
+    double acc[BR];
+#pragma unroll
+    for (int i = 0; i < BR; ++i) acc[i] = 0.0;
+    for (int u = lane; u < nb; u += G) {
+      const int64_t c = colidx[p0 + u];
+      double xv[BC];
+#pragma unroll
+      for (int j = 0; j < BC; ++j) xv[j] = x[c * BC + j];
+#pragma unroll
+      for (int i = 0; i < BR; ++i)
+#pragma unroll
+        for (int j = 0; j < BC; ++j) acc[i] += v[(int64_t)(i * BC + j) * nb + u] * xv[j];
+    }
+#pragma unroll
+    for (int i = 0; i < BR; ++i)
+#pragma unroll
+      for (int o = G / 2; o > 0; o >>= 1) acc[i] += __shfl_xor_sync(0xffffffffu, acc[i], o, G);
+#pragma unroll
+    for (int i = 0; i < BR; ++i) {
+      if (live && lane == i % G) {   // spread the br stores over the first lanes
+        double out = alpha * acc[i];
+        if (beta != 0.0) out += beta * z[r * BR + i];
+        y[r * BR + i] = out;
+        if (DOT) dotacc[0] += out * x[r * BC + i];
+      }
+    }
+  }
+  if (DOT) {
+    block_reduce<1>(dotacc, red_sm);
+    grid_reduce_finish<1>(dotacc, fuse.partials, fuse.ticket, fuse.dot_out);
+  }
+}
+
+static int spmv_launch(pyn_mat* m, double alpha, const double* x, double beta, const double* z,
+                       double* y, bool dot, SpmvFuse fuse) {
+  pyn_ctx* ctx = m->ctx;
+  if (m->nbrows == 0) return PYN_OK;
+  const double avg = m->nbrows ? (double)m->nblocks / (double)m->nbrows : 0.0;
+  const int G = avg > 24.0 ? 32 : (avg > 10.0 ? 16 : 8);
+  const int grid = grid_for(ctx, m->nbrows * G, 256, 8);
+#define LAUNCH(BR, BC, GG, DD)                                                                   \
+  spmv_kernel<BR, BC, GG, DD><<<grid, 256, 0, ctx->stream>>>(m->nbrows, m->rowptr.p, m->colidx.p, \
+                                                             m->val.p, x, alpha, beta, z, y, fuse)
+#define CALL(BR, BC)                                     \
+  do {                                                   \
+    if (dot) {                                           \
+      if (BR != BC) {                                    \
+        set_error("spmv+dot needs square blocks");       \
+        return PYN_E_INVALID;                            \
+      }                                                  \
+      if (G == 32) LAUNCH(BR, BC, 32, true);             \
+      else if (G == 16) LAUNCH(BR, BC, 16, true);        \
+      else LAUNCH(BR, BC, 8, true);                      \
+    } else {                                             \
+      if (G == 32) LAUNCH(BR, BC, 32, false);            \
+      else if (G == 16) LAUNCH(BR, BC, 16, false);       \
+      else LAUNCH(BR, BC, 8, false);                     \
+    }                                                    \
+  } while (0)
+  PYN_DISPATCH_BLOCK(m->br, m->bc, CALL);
+#undef CALL
+#undef LAUNCH
+  PYN_LAUNCHED(ctx);
+  return PYN_OK;
+}
+
+int spmv(pyn_mat* m, double alpha, const double* x, double beta, const double* z, double* y) {
+  SpmvFuse f = {nullptr, nullptr, nullptr, nullptr};
+  return spmv_launch(m, alpha, x, beta, z, y, false, f);
+}
+
+// y = A x and dot_out = x . y in one pass; no-op when *skip != 0
+int spmv_dot(pyn_mat* m, const double* x, double* y, double* dot_out, const double* skip) {
+  pyn_ctx* ctx = m->ctx;
+  SpmvFuse f = {skip, ctx->red_partials, ctx->red_ticket, dot_out};
+  return spmv_launch(m, 1.0, x, 0.0, nullptr, y, true, f);
+}
+
+// ---- diagonal blocks / row scaling ------------------------------------------------
+// dblk[r][i][j] = diagonal node block of a square-block matrix (zeros if absent)
+template <int B>
+__global__ void diag_blocks_kernel(int64_t nbrows, const int64_t* __restrict__ rowptr,
+                                   const int32_t* __restrict__ colidx, const double* __restrict__ val,
+                                   double* __restrict__ dblk) {
+  for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < nbrows;
+       r += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t p0 = rowptr[r];
+    const int nb = (int)(rowptr[r + 1] - p0);
+    int lo = 0, hi = nb - 1, pos = -1;
+    while (lo <= hi) {
+      const int mid = (lo + hi) >> 1;
+      const int32_t c = colidx[p0 + mid];
+      if (c == r) { pos = mid; break; }
+      if (c < r) lo = mid + 1; else hi = mid - 1;
+    }
+    for (int q = 0; q < B * B; ++q)
+      dblk[r * B * B + q] = pos >= 0 ? val[p0 * B * B + (int64_t)q * nb + pos] : 0.0;
+  }
+}
+
+int diag_blocks(pyn_mat* m, double* dblk) {
+  pyn_ctx* ctx = m->ctx;
+  PYN_REQUIRE(m->br == m->bc, "diagonal of a non-square-block matrix");
+  const int grid = grid_for(ctx, m->nbrows, 128);
+  if (m->br == 3)
+    diag_blocks_kernel<3><<<grid, 128, 0, ctx->stream>>>(m->nbrows, m->rowptr.p, m->colidx.p, m->val.p, dblk);
+  else if (m->br == 2)
+    diag_blocks_kernel<2><<<grid, 128, 0, ctx->stream>>>(m->nbrows, m->rowptr.p, m->colidx.p, m->val.p, dblk);
+  else if (m->br == 1)
+    diag_blocks_kernel<1><<<grid, 128, 0, ctx->stream>>>(m->nbrows, m->rowptr.p, m->colidx.p, m->val.p, dblk);
+  else {
+    set_error("diag_blocks: unsupported block size %d", m->br);
+    return PYN_E_UNSUPPORTED;
+  }
+  PYN_LAUNCHED(ctx);
+  return PYN_OK;
+}
+
+__global__ void scale_rows_kernel(int br, int bc, int64_t nbrows, const int64_t* __restrict__ rowptr,
+                                  const double* __restrict__ l, double* __restrict__ val) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  const int bb = br * bc;
+  for (int64_t r = warp; r < nbrows; r += nwarps) {
+    const int64_t p0 = rowptr[r];
+    const int64_t nb = rowptr[r + 1] - p0;
+    for (int64_t t = lane; t < nb * bb; t += 32) {
+      const int i = (int)(t / nb) / bc;
+      val[p0 * bb + t] *= l[r * br + i];
+    }
+  }
+}
+
+int scale_rows(pyn_mat* m, const double* l) {
+  pyn_ctx* ctx = m->ctx;
+  scale_rows_kernel<<<grid_for(ctx, m->nbrows * 32, 256), 256, 0, ctx->stream>>>(
+      m->br, m->bc, m->nbrows, m->rowptr.p, l, m->val.p);
+  PYN_LAUNCHED(ctx);
+  return PYN_OK;
+}
+
+// ---- C = A + B on the union pattern (both filtered from the same graph) -------------
+__global__ void mark_slots_kernel(const int64_t* __restrict__ base, int64_t n, int64_t* __restrict__ pos) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (int64_t)gridDim.x * blockDim.x)
+    pos[base[i]] = i;
+}
+
+// one warp per row of C: for every block find the source positions in A and B
+__global__ void add_values_kernel(int bb, int64_t nbrows, const int64_t* __restrict__ c_rowptr,
+                                  const int64_t* __restrict__ c_base,
+                                  const int64_t* __restrict__ a_rowptr, const int64_t* __restrict__ a_pos,
+                                  const double* __restrict__ a_val, const int64_t* __restrict__ b_rowptr,
+                                  const int64_t* __restrict__ b_pos, const double* __restrict__ b_val,
+                                  double* __restrict__ c_val) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  for (int64_t r = warp; r < nbrows; r += nwarps) {
+    const int64_t p0 = c_rowptr[r], nb = c_rowptr[r + 1] - p0;
+    const int64_t ap0 = a_rowptr[r], anb = a_rowptr[r + 1] - ap0;
+    const int64_t bp0 = b_rowptr[r], bnb = b_rowptr[r + 1] - bp0;
+    for (int64_t u = lane; u < nb; u += 32) {
+      const int64_t s = c_base[p0 + u];
+      const int64_t pa = a_pos[s], pb = b_pos[s];
+      for (int q = 0; q < bb; ++q) {
+        double v = 0.0;
+        if (pa >= 0) v += a_val[ap0 * bb + (int64_t)q * anb + (pa - ap0)];
+        if (pb >= 0) v += b_val[bp0 * bb + (int64_t)q * bnb + (pb - bp0)];
+        c_val[p0 * bb + (int64_t)q * nb + u] = v;
+      }
+    }
+  }
+}
+
+__global__ void fill_i64_kernel(int64_t* p, int64_t n, int64_t v) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (int64_t)gridDim.x * blockDim.x)
+    p[i] = v;
+}
+
+int mat_add_new(pyn_mat* a, pyn_mat* b, pyn_mat** out) {
+  PYN_REQUIRE(a->graph == b->graph && a->br == b->br && a->bc == b->bc,
+              "mat_add: operands must come from the same node graph with equal block shape");
+  PYN_REQUIRE(a->use_rowcls == b->use_rowcls && a->use_colcls == b->use_colcls,
+              "mat_add: operands use different dof-class masks");
+  pyn_ctx* ctx = a->ctx;
+  pyn_mat* c = new pyn_mat();
+  int rc = make_pattern(a->mesh, a->graph, a->br, a->bc, a->use_rowcls, a->use_colcls,
+                        a->pairmask | b->pairmask, a->diagmask | b->diagmask, c);
+  if (rc != PYN_OK) {
+    delete c;
+    return rc;
+  }
+  c->ref_dense = a->ref_dense;
+  DevBuf<int64_t> apos, bpos;
+  const int64_t ns = a->graph->nslots;
+  rc = apos.alloc(ctx, ns);
+  if (rc == PYN_OK) rc = bpos.alloc(ctx, ns);
+  if (rc != PYN_OK) {
+    delete c;
+    return rc;
+  }
+  const int g1 = grid_for(ctx, ns, 256);
+  fill_i64_kernel<<<g1, 256, 0, ctx->stream>>>(apos.p, ns, -1);
+  fill_i64_kernel<<<g1, 256, 0, ctx->stream>>>(bpos.p, ns, -1);
+  ctx->launches += 2;
+  if (a->nblocks) {
+    mark_slots_kernel<<<grid_for(ctx, a->nblocks, 256), 256, 0, ctx->stream>>>(a->base_slot.p, a->nblocks, apos.p);
+    ctx->launches++;
+  }
+  if (b->nblocks) {
+    mark_slots_kernel<<<grid_for(ctx, b->nblocks, 256), 256, 0, ctx->stream>>>(b->base_slot.p, b->nblocks, bpos.p);
+    ctx->launches++;
+  }
+  if (c->nblocks) {
+    add_values_kernel<<<grid_for(ctx, c->nbrows * 32, 256), 256, 0, ctx->stream>>>(
+        c->br * c->bc, c->nbrows, c->rowptr.p, c->base_slot.p, a->rowptr.p, apos.p, a->val.p,
+        b->rowptr.p, bpos.p, b->val.p, c->val.p);
+    ctx->launches++;
+  }
+  cudaError_t e = cudaStreamSynchronize(ctx->stream);
+  if (e != cudaSuccess) {
+    set_error("mat_add: %s", cudaGetErrorString(e));
+    delete c;
+    return PYN_E_CUDA;
+  }
+  *out = c;
+  return PYN_OK;
+}
+
+}  // namespace pyn

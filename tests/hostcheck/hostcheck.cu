@@ -1,0 +1,84 @@
+// hostcheck.cu -- TEST-ONLY host harness.  Runs the host+device inline element
+// arithmetic of pynama_b200/csrc/elem_math.cuh in plain CPU loops so that the
+// formulas and the C++ reference-element tables can be checked against the
+// golden vectors in the build container (no GPU there).  It is not part of
+// libpynama_b200.so and nothing in the product loads it.
+#include "../../pynama_b200/csrc/elem_math.cuh"
+
+using namespace pyn;
+
+template <int DIM>
+static void kle_host(const ElemTables& t, const double* X, double* K, double* Rw, double* Rd) {
+  constexpr int DW = DIM == 2 ? 1 : 3;
+  const int nn = t.nn;
+  std::vector<PairAcc<DIM>> acc((size_t)nn * nn);
+  for (auto& a : acc) a.clear();
+  for (int q = 0; q < 2; ++q) {
+    const Rule1D& r = t.rule[q == 0 ? RULE_FULL : RULE_RED];
+    std::vector<double> G((size_t)nn * DIM), H(nn);
+    for (int g = 0; g < r.npts; ++g) {
+      double jinv[9], det;
+      point_geometry<DIM>(r, t.corn_t, g, X, jinv, &det);
+      const double wd = point_weight<DIM>(r, g) * det;
+      for (int b = 0; b < nn; ++b) node_gradient<DIM>(r, t.node_t[b], g, jinv, &G[(size_t)b * DIM], &H[b]);
+      for (int a = 0; a < nn; ++a)
+        for (int b = 0; b < nn; ++b) {
+          if (q == 0) acc[(size_t)a * nn + b].add_full(wd, &G[(size_t)a * DIM], H[a], &G[(size_t)b * DIM]);
+          else acc[(size_t)a * nn + b].add_red(wd, &G[(size_t)a * DIM], &G[(size_t)b * DIM], H[b]);
+        }
+    }
+  }
+  for (int a = 0; a < nn; ++a)
+    for (int b = 0; b < nn; ++b) {
+      const PairAcc<DIM>& p = acc[(size_t)a * nn + b];
+      for (int c = 0; c < DIM; ++c) {
+        for (int e = 0; e < DIM; ++e) K[((size_t)a * DIM + c) * nn * DIM + b * DIM + e] = p.K[c][e];
+        for (int e = 0; e < DW; ++e) Rw[((size_t)a * DIM + c) * nn * DW + b * DW + e] = p.Rw[c][e];
+        Rd[((size_t)a * DIM + c) * nn + b] = p.Rd[c];
+      }
+    }
+}
+
+template <int DIM>
+static void ops_host(const ElemTables& t, const double* X, double* S, double* D, double* C, double* W) {
+  constexpr int DW = DIM == 2 ? 1 : 3;
+  constexpr int DS = DIM == 2 ? 3 : 6;
+  const int nn = t.nn;
+  const Rule1D& r = t.rule[RULE_NODAL];
+  for (int a = 0; a < nn; ++a) {
+    double jinv[9], det;
+    point_geometry<DIM>(r, t.corn_t, a, X, jinv, &det);
+    const double wd = point_weight<DIM>(r, a) * det;
+    W[a] = wd;
+    const double ha = tensor_val<DIM, kMaxNgl>(r.h, r.dh, r.gp_t[a], t.node_t[a], -1);
+    for (int b = 0; b < nn; ++b) {
+      double G[DIM], Hb;
+      node_gradient<DIM>(r, t.node_t[b], a, jinv, G, &Hb);
+      OpsAcc<DIM> acc;
+      acc.clear();
+      acc.add(wd, ha, G);
+      for (int s = 0; s < DS; ++s)
+        for (int c = 0; c < DIM; ++c) {
+          S[((size_t)a * DS + s) * nn * DIM + b * DIM + c] = acc.SrT[s][c];
+          D[((size_t)a * DIM + c) * nn * DS + b * DS + s] = acc.Div[c][s];
+        }
+      for (int rr = 0; rr < DW; ++rr)
+        for (int c = 0; c < DIM; ++c) C[((size_t)a * DW + rr) * nn * DIM + b * DIM + c] = acc.Curl[rr][c];
+    }
+  }
+}
+
+extern "C" {
+int hc_kle(int dim, int ngl, const double* X, double* K, double* Rw, double* Rd) {
+  ElemTables t;
+  if (build_elem_tables(dim, ngl, &t) != 0) return -1;
+  if (dim == 2) kle_host<2>(t, X, K, Rw, Rd); else kle_host<3>(t, X, K, Rw, Rd);
+  return 0;
+}
+int hc_ops(int dim, int ngl, const double* X, double* S, double* D, double* C, double* W) {
+  ElemTables t;
+  if (build_elem_tables(dim, ngl, &t) != 0) return -1;
+  if (dim == 2) ops_host<2>(t, X, S, D, C, W); else ops_host<3>(t, X, S, D, C, W);
+  return 0;
+}
+}
