@@ -1,0 +1,335 @@
+"""Boundary-condition bookkeeping of the hot path's callers.
+
+Mirrors the behaviour of the reference's ``boundaries.boundary`` and
+``boundaries.boundary_conditions`` modules (same class and method names,
+argument meaning and error behaviour) without PETSc index sets:
+
+* BC type detection            boundary_conditions.py:44-69
+* per-side values              boundary.py:27-36 (constants), :141-146 (functions)
+* Dirichlet / no-slip sets     boundary_conditions.py:191-243
+* scatter into a Vec           boundary_conditions.py:252-277
+
+Index sets are numpy arrays; the scatter goes to the device Vec through
+``Vec.setValues`` (kernel k10).  The values of all sides are merged into one
+scatter per call, keeping the reference's "later side overwrites earlier side"
+order at shared edges and corners.
+"""
+import importlib
+import logging
+from math import cos, radians, sin
+
+import numpy as np
+
+from ..petsc import COMM_WORLD
+
+# side name -> index of the normal direction (boundary.py:151-152)
+NORMAL_OF = {"left": 0, "right": 0, "up": 1, "down": 1, "front": 2, "back": 2}
+
+
+class Directions:
+    dirs = NORMAL_OF
+
+    def __init__(self, name, dim):
+        self._normal = self.dirs[name]
+        self._tangs = [d for d in range(dim) if d != self._normal]
+
+    def getNormal(self):
+        return self._normal
+
+    def getTangentials(self):
+        return self._tangs
+
+    def __repr__(self):
+        return f"Normals {self._normal} Tangs: {self._tangs}"
+
+
+class Boundary:
+    needsCoords = False
+
+    def __init__(self, name, typ, dim):
+        self._name, self._type, self._dim = name, typ, dim
+        self._dirs = Directions(name, dim)
+        self._nodes = np.zeros(0, dtype=np.int64)
+
+    def setType(self, t):
+        self._type = t
+
+    def getType(self):
+        return self._type
+
+    def getName(self):
+        return self._name
+
+    def setValues(self, attrName, vals):
+        try:
+            setattr(self, attrName, np.array(vals))
+        except Exception:
+            raise Exception(f"Error setting {attrName} with value; {vals} to {self._name} boundary")
+
+    def getValues(self, attrName, t=None, nu=None):
+        try:
+            val = getattr(self, attrName)
+        except AttributeError:
+            raise Exception(f"{attrName} Not defined")
+        return np.tile(val, len(self._nodes))
+
+    def getVelocitySetted(self):
+        return getattr(self, "velocity")
+
+    def getVelocitySettedTangential(self):
+        return getattr(self, "velocity")[self._dirs.getTangentials()]
+
+    def setNodes(self, nodes):
+        # PETSc.IS().createBlock keeps the nodes in the order given
+        self._nodes = np.asarray(list(nodes), dtype=np.int64)
+
+    def getNodes(self):
+        return self._nodes
+
+    def getNumOfNodes(self):
+        return len(self._nodes)
+
+    def getSize(self):
+        return len(self._nodes) * self._dim
+
+    def getDofsConstrained(self):
+        return (self._nodes[:, None] * self._dim + np.arange(self._dim)[None, :]).ravel()
+
+    def getNormalDofs(self):
+        return set((self._nodes * self._dim + self._dirs.getNormal()).tolist())
+
+    def getTangDofs(self, tangDir=None):
+        if tangDir is not None:
+            return set((self._nodes * self._dim + tangDir).tolist())
+        out = set()
+        for d in self._dirs.getTangentials():
+            out |= set((self._nodes * self._dim + d).tolist())
+        return out
+
+    def getTangDirections(self):
+        return self._dirs.getTangentials()
+
+    def __repr__(self):
+        return f"Boundary Name:{self._name}:: Type: {self._type}  :: DOFS Constrained {self._dim}\n"
+
+
+class FunctionBoundary(Boundary):
+    needsCoords = True
+
+    def __init__(self, name, func_name, attrs, dim):
+        super().__init__(name, "free-slip", dim)
+        self.funcName = func_name
+        lib = importlib.import_module(f".{func_name}", package="pynama_b200.functions")
+        for attr in attrs:
+            setattr(self, f"{attr}Func", getattr(lib, attr))
+        self._coords = None
+
+    def setNodesCoordinates(self, arr):
+        self._coords = np.asarray(arr, dtype=np.float64).reshape(len(self.getNodes()), self._dim)
+
+    def getNodesCoordinates(self):
+        return self._coords
+
+    def getValues(self, attrName, t, nu):
+        func = getattr(self, f"{attrName}Func")
+        # the reference calls alpha(t, nu) although it is declared alpha(nu, t)
+        # (boundary.py:144 vs functions/taylor_green.py:4); the product nu*t is symmetric
+        alpha = getattr(self, "alphaFunc")(t, nu)
+        return func(self._coords, alpha)
+
+
+class BoundaryConditions:
+    types = ["FS", "NS", "FS-NS"]
+    bcTypesAvailable = ("uniform", "custom-func", "free-slip", "no-slip")
+    comm = COMM_WORLD
+
+    def __init__(self, sides):
+        self._boundaries, self._ns, self._fs = [], [], []
+        self._type = None
+        self._byName = {}
+        self._byType = {"free-slip": [], "no-slip": []}
+        self._needsCoords = []
+        self._borderNames = list(sides)
+        self._dim = 2 if len(sides) == 4 else 3
+        self._plans = {}
+        self.logger = logging.getLogger(f"[{self.comm.rank}]Boundary Conditions:")
+
+    # ---- configuration (boundary_conditions.py:44-148) -------------------------------------
+    def setBoundaryConditions(self, data):
+        if "uniform" in data:
+            if "free-slip" in data or "no-slip" in data:
+                self.logger.warning("WARNING: Only constant bc its assumed")
+            self._type = "FS"
+            vals = self._handleUniform(data["uniform"])
+            for side in self._borderNames:
+                self._setBoundary(side, "free-slip", vals)
+        elif "custom-func" in data:
+            self._type = "FS"
+            for side in self._borderNames:
+                self._setFunctionBoundary(side, data["custom-func"]["name"], data["custom-func"]["attributes"])
+        elif "free-slip" in data and "no-slip" in data:
+            self._type = "FS-NS"
+            self._setPerBoundaries("free-slip", data["free-slip"])
+            self._setPerBoundaries("no-slip", data["no-slip"])
+        elif "free-slip" in data:
+            self._type = "FS"
+            self._setPerBoundaries("free-slip", data["free-slip"])
+        elif "no-slip" in data:
+            self._type = "NS"
+            self._setPerBoundaries("no-slip", data["no-slip"])
+        else:
+            raise Exception("Boundary Conditions not defined")
+
+    def getType(self):
+        return self._type
+
+    def _setPerBoundaries(self, t, sidesDict):
+        for name, vals in sidesDict.items():
+            if isinstance(vals, dict) and "custom-func" in vals:
+                self._setFunctionBoundary(name, vals["custom-func"]["name"], vals["custom-func"]["attributes"])
+            else:
+                self._setBoundary(name, t, vals)
+
+    @staticmethod
+    def _handleUniform(u):
+        if "velocity" in u and "vorticity" not in u:
+            return {"velocity": u["velocity"], "vorticity": [0]}
+        if "re" in u:
+            for key in ("mu", "rho", "Lref", "direction"):
+                if key not in u:
+                    raise Exception("mu, rho, Lref AND/OR direction not defined")
+            L = eval(u["Lref"]) if isinstance(u["Lref"], str) else u["Lref"]
+            velRef = u["re"] * (u["mu"] / u["rho"]) / L
+            ang = radians(u["direction"])
+            return {"velocity": [cos(ang) * velRef, sin(ang) * velRef], "vorticity": [0]}
+        return u
+
+    def _setBoundary(self, name, typ, vals):
+        b = Boundary(name, typ, self._dim)
+        if isinstance(vals, list):
+            b.setValues("velocity", vals)
+            b.setValues("vorticity", [0] if self._dim == 2 else [0] * 3)
+        else:
+            for attr, val in vals.items():
+                b.setValues(attr, val)
+        if typ not in self._byType:
+            raise Exception("Wrong boundary type")
+        self._register(b, typ)
+
+    def _setFunctionBoundary(self, name, funcName, attrs):
+        b = FunctionBoundary(name, funcName, attrs, self._dim)
+        self._register(b, "free-slip")
+        self._needsCoords.append(name)
+
+    def _register(self, b, typ):
+        self._boundaries.append(b)
+        (self._fs if typ == "free-slip" else self._ns).append(b)
+        self._byType[typ].append(b)
+        self._byName[b.getName()] = b
+        self._plans = {}
+
+    # ---- queries ---------------------------------------------------------------------------------
+    def getNames(self, bcs=None):
+        return [b.getName() for b in (self._boundaries if bcs is None else bcs)]
+
+    def getNamesByType(self, bcType):
+        return self.getNames(self._byType[bcType])
+
+    def getBordersNeedsCoords(self):
+        return self._needsCoords
+
+    def getIndicesByName(self, name):
+        return self._byName[name].getDofsConstrained()
+
+    def setBoundaryNodes(self, bName, nodes):
+        if bName not in self._byName:
+            raise Exception("Boundary Not found")
+        self._byName[bName].setNodes(nodes)
+        self._plans = {}
+
+    def setBoundaryCoords(self, bName, coords):
+        self._byName[bName].setNodesCoordinates(coords)
+
+    def getIndicesByType(self, bcType):
+        out = set()
+        for b in self._byType[bcType]:
+            out |= set(b.getDofsConstrained().tolist())
+        return out
+
+    def getNodesByType(self, bcType, allGather=False):
+        out = set()
+        for b in self._byType[bcType]:
+            out |= set(b.getNodes().tolist())
+        return out
+
+    def getNoSlipIndices(self, allGather=False):
+        return self.getIndicesByType("no-slip")
+
+    def getFreeSlipIndices(self):
+        return self.getIndicesByType("free-slip")
+
+    def getNoSlipTangDofs(self, allGather=False):
+        out = set()
+        for b in self._ns:
+            out |= b.getTangDofs()
+        return out
+
+    def getNoSlipNormalDofs(self, allGather=False):
+        """boundary_conditions.py:227-243, single-rank semantics: with allGather the
+        x-normal dof of a left/right node is dropped when the same node's next dof is
+        already a normal dof of a side processed earlier."""
+        dofs, remove = set(), set()
+        for b in self._ns:
+            loc = b.getNormalDofs()
+            if allGather and b.getName() in ("left", "right"):
+                for ind in loc:
+                    if (ind + 1) in dofs:
+                        remove.add(ind)
+            dofs |= loc
+        return dofs - remove
+
+    def getFreeStreamVelocity(self):
+        return self._boundaries[0].getVelocitySetted()
+
+    # ---- scatter into Vecs (boundary_conditions.py:252-277) ------------------------------------------
+    def _plan(self, name):
+        """merged index list of all sides for variable `name`; where sides overlap the
+        side listed last wins, as successive Vec.setValues(INSERT) calls do"""
+        if name not in self._plans:
+            idx = []
+            for b in self._boundaries:
+                idx.append(b.getNodes() if (self._dim == 2 and name == "vorticity") else b.getDofsConstrained())
+            allidx = np.concatenate(idx) if idx else np.zeros(0, dtype=np.int64)
+            # last occurrence of every index
+            _, first_rev = np.unique(allidx[::-1], return_index=True)
+            keep = np.sort(len(allidx) - 1 - first_rev)
+            self._plans[name] = (allidx[keep].astype(np.int64), keep)
+        return self._plans[name]
+
+    def getValuesMerged(self, name, t, nu):
+        idx, keep = self._plan(name)
+        vals = [np.asarray(b.getValues(name, t, nu), dtype=np.float64).ravel() for b in self._boundaries]
+        vals = np.concatenate(vals) if vals else np.zeros(0)
+        return idx, vals[keep]
+
+    def setValuesToVec(self, vec, name, t, nu):
+        idx, vals = self.getValuesMerged(name, t, nu)
+        vec.setValues(idx, vals, addv=False)
+        vec.assemble()
+
+    def setTangentialValuesToVec(self, vec, name, t, nu):
+        """impose the wall velocity on the tangential dofs of the no-slip sides"""
+        for bc in self._ns:
+            vel = bc.getVelocitySetted()
+            n = bc.getNumOfNodes()
+            for tang in bc.getTangDirections():
+                inds = bc.getNodes() * self._dim + tang
+                vec.setValues(inds, np.repeat(vel[tang], n), addv=False)
+        vec.assemble()
+
+    def __repr__(self):
+        txt = " --== Boundary Conditions ==--\n   Name   |   Type   |   Values   \n"
+        for b in self._boundaries:
+            val = getattr(b, "velocity", "Not defined")
+            txt += f"{b.getName():10}|{b.getType():10}|{str(val):12}\n"
+        return txt
