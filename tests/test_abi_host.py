@@ -1,0 +1,87 @@
+"""CPU: the C-ABI library loads and exports every symbol include/pynama_b200.h
+declares; host-only helpers (1-D rules, Lagrange tables, local order) and the
+host build of the element arithmetic (tests/hostcheck) agree with the golden
+vectors of the reference.  No compute entry point is called (no GPU here)."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+
+from pynama_b200 import _lib
+from tests.util import golden
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HEADER = os.path.join(ROOT, "include", "pynama_b200.h")
+HOSTCHECK = os.path.join(ROOT, "tests", "hostcheck", "libhostcheck.so")
+
+
+def _declared():
+    src = open(HEADER).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(pyn_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_library_exports_every_declared_symbol():
+    names = _declared()
+    assert len(names) >= 55
+    cdll = ctypes.CDLL(_lib.LIB_PATH)
+    missing = [n for n in names if not hasattr(cdll, n)]
+    assert not missing, f"declared in the header but not exported: {missing}"
+    # the ctypes prototypes cover the header and nothing else
+    assert sorted(_lib.EXPORTS) == names
+
+
+def test_version_and_error_plumbing():
+    l = _lib.lib()
+    assert l.pyn_version() >= 100
+    x = np.zeros(4)
+    with pytest.raises(_lib.PynamaError):
+        _lib.call("pyn_rule_1d", 7, 4, _lib.ptr(x), _lib.ptr(x))     # unknown rule kind
+    assert l.pyn_last_error()
+
+
+def test_host_rules_vs_reference():
+    g = golden("rules_1d.npz")
+    for n in range(2, 9):
+        x, w = _lib.rule_1d("gauss", n)
+        assert np.abs(x - g[f"gauss{n}_x"]).max() < 1e-14 and np.abs(w - g[f"gauss{n}_w"]).max() < 1e-14
+        x, w = _lib.rule_1d("lobatto", n)
+        assert np.abs(x - g[f"lobatto{n}_x"]).max() < 1e-14 and np.abs(w - g[f"lobatto{n}_w"]).max() < 1e-14
+
+
+@pytest.mark.parametrize("dim,ngl", [(2, 2), (2, 3), (2, 5), (2, 8), (3, 2), (3, 3), (3, 4), (3, 6)])
+def test_host_local_order_vs_reference(dim, ngl):
+    g = golden(f"elem_{dim}d_ngl{ngl}.npz")
+    nodes, _ = _lib.rule_1d("lobatto", ngl)
+    t = _lib.local_order(dim, ngl)
+    assert np.abs(nodes[t] - g["node_rst"]).max() < 1e-14
+
+
+def _hc():
+    if not os.path.exists(HOSTCHECK):
+        pytest.skip("tests/hostcheck/libhostcheck.so not built (run __graft_entry__.build())")
+    return ctypes.CDLL(HOSTCHECK)
+
+
+@pytest.mark.parametrize("dim,ngl", [(2, 2), (2, 3), (2, 4), (2, 5), (3, 2), (3, 3), (3, 4)])
+def test_element_arithmetic_host_build_vs_reference(dim, ngl):
+    """the same inline functions the CUDA kernels call, run in CPU loops"""
+    hc = _hc()
+    g = golden(f"elem_{dim}d_ngl{ngl}.npz")
+    nn, dw, ds = ngl ** dim, (1 if dim == 2 else 3), (3 if dim == 2 else 6)
+    vp = ctypes.c_void_p
+    for ci, X in enumerate(g["cells"]):
+        X = np.ascontiguousarray(X, dtype=np.float64)
+        K, Rw, Rd = np.zeros((nn * dim, nn * dim)), np.zeros((nn * dim, nn * dw)), np.zeros((nn * dim, nn))
+        S, D = np.zeros((nn * ds, nn * dim)), np.zeros((nn * dim, nn * ds))
+        C, W = np.zeros((nn * dw, nn * dim)), np.zeros(nn)
+        assert hc.hc_kle(dim, ngl, X.ctypes.data_as(vp), K.ctypes.data_as(vp), Rw.ctypes.data_as(vp),
+                         Rd.ctypes.data_as(vp)) == 0
+        assert hc.hc_ops(dim, ngl, X.ctypes.data_as(vp), S.ctypes.data_as(vp), D.ctypes.data_as(vp),
+                         C.ctypes.data_as(vp), W.ctypes.data_as(vp)) == 0
+        for name, arr in (("K", K), ("Rw", Rw), ("Rd", Rd), ("SrT", S), ("Div", D), ("Curl", C), ("W", W)):
+            ref = g[f"c{ci}_{name}"]
+            err = np.abs(arr - ref).max() / np.abs(ref).max()
+            assert err <= 1e-12, (name, ci, err)
