@@ -1,0 +1,404 @@
+#!/usr/bin/env python
+"""bench.py -- BASELINE.json's metric on BASELINE.json's config.
+
+Workload (N=1): configs[1], "3-D Taylor-Green vortex, 16^3 elements, ngl=4, one
+B200".  A *step* is one RK-5BS time step of the vorticity-transport equation
+through the reference's own time loop (run_case.py:152-162 -> TS -> evalRHS,
+base_problem.py:111-136): 7 right-hand-side evaluations (FSAL), each = BC scatter
++ KLE solve (CG + node-block Jacobi on K, to --rtol) + SpMV with Rw, Krhs, SrT,
+DivSrT, Curl + the pointwise stress kernel.  The operators are assembled once
+before the loop, as in the reference (setUpSolver, base_problem.py:156-179); the
+assembly is timed separately and reported under "assembly".
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+
+value  = velocity DOFs advanced one time step per second, fields resident in HBM;
+e2e    = the same through the public API with the fields living on the HOST:
+         every step uploads vorticity+velocity from pinned host memory and reads
+         them back (what the reference's post-step viewer does), BC values are
+         evaluated on the host and scattered every RHS evaluation.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "kle_timestep_throughput"
+UNIT = "DOF/s"          # velocity dofs advanced one RK5BS time step per second
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--nelem", type=int, default=16)
+    ap.add_argument("--ngl", type=int, default=4)
+    ap.add_argument("--rtol", type=float, default=1e-10, help="KSP relative tolerance")
+    ap.add_argument("--dt", type=float, default=1e-3, help="fixed time step (-ts_adapt_type none)")
+    ap.add_argument("--pc", default="bjacobi", choices=["jacobi", "bjacobi", "none"])
+    ap.add_argument("--cpu-nelem", type=int, default=8, help="mesh of the bounded CPU sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def load_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs, copy burst)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(index), f"--query-gpu={self.Q}",
+                                       "--format=csv,noheader,nounits", "-lms", "100"],
+                                      stdout=self.f, stderr=subprocess.DEVNULL)
+        except OSError:
+            self.p = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+        if self.p is None:
+            return out
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except Exception:
+            self.p.kill()
+        self.f.flush()
+        self.f.seek(0)
+        sm, smax, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in self.f.read().splitlines():
+            c = [x.strip() for x in line.split(",")]
+            if len(c) < 6:
+                continue
+            try:
+                sm.append(float(c[0]))
+                smax.append(float(c[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, c[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        self.f.close()
+        os.unlink(self.f.name)
+        if sm:
+            out = {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(smax)), "reasons": sorted(reasons),
+                   "samples": len(sm)}
+        return out
+
+
+def case_config(nelem, ngl):
+    """cases/taylor-green3d.yaml (the reference's src/cases/taylor-green3d.yaml) with the box set
+    to BASELINE.json configs[1]"""
+    from pynama_b200.run_case import loadCase
+    cfg = loadCase("taylor-green3d")
+    cfg["domain"]["ngl"] = ngl
+    cfg["domain"]["box-mesh"]["nelem"] = [nelem] * 3
+    cfg["time-solver"]["max-steps"] = 10 ** 9
+    cfg["time-solver"]["end-time"] = 1e9
+    return cfg
+
+
+# ---------------------------------------------------------------------------------------------
+# B200 arm
+# ---------------------------------------------------------------------------------------------
+def build_problem(args):
+    from pynama_b200.cases.base_problem import BaseProblem
+    from pynama_b200.petsc import Options
+    o = Options()
+    o.setValue("ksp_type", "cg")
+    o.setValue("pc_type", args.pc)
+    o.setValue("ksp_rtol", args.rtol)
+    o.setValue("ksp_max_it", 50000)
+    o.setValue("ts_adapt_type", "none")
+    o.setValue("ts_dt", args.dt)
+    fem = BaseProblem(case_config(args.nelem, args.ngl), case="taylor-green3d")
+    fem.setUp()
+    t0 = time.perf_counter()
+    fem.setUpSolver()
+    fem.setup_wall_s = time.perf_counter() - t0
+    fem.ts._post = None            # the post-step viewer is file output (out of scope); e2e reads back instead
+    fem.ts.setSolution(fem.vort)
+    return fem
+
+
+def bc_bytes_per_rhs(fem):
+    """host->device bytes of one evalRHS: merged BC index + value arrays of both fields"""
+    bc = fem.dom.getBoundaryConditions()
+    n = 0
+    for name in ("vorticity", "velocity"):
+        idx, vals = bc.getValuesMerged(name, 0.0, fem.nu)
+        n += np.asarray(idx).size * 8 + np.asarray(vals).size * 8
+    return n
+
+
+def run_b200(args, rank, world):
+    from pynama_b200.petsc import Context
+    ctx = Context.get()
+    fem = build_problem(args)
+    dm = fem.dom.getDeviceMesh()
+    K = fem.mat.K
+    ndof = K.getSize()[0]
+    nvort = fem.vort.getSize()
+    asm = {p: dm.phase_ms(p) for p in ("symbolic", "elem_kle", "kle_numeric", "elem_ops", "ops_numeric")}
+
+    def one_step():
+        fem.ts.step()
+
+    for _ in range(args.warmup):
+        one_step()
+    ctx.sync()
+    barrier(world)
+    sampler = ClockSampler(ctx.device)
+    its0, solves0, evals0 = fem.kspIterations, fem.kspSolves, fem.ts.rhs_evals
+    l0 = ctx.launch_count()
+    ctx.prof_enable(True)
+    ctx.sync()
+    ctx.timer_start()
+    for _ in range(args.steps):
+        one_step()
+    ms = ctx.timer_stop()
+    ctx.sync()
+    barrier(world)
+    clocks = sampler.stop()
+    launches = ctx.launch_count() - l0
+    n_spmv, ms_spmv = ctx.prof_get("spmv_ksp")
+    n_oth, ms_oth = ctx.prof_get("spmv")
+    n_upd, ms_upd = ctx.prof_get("cg_update")
+    n_dir, ms_dir = ctx.prof_get("cg_direction")
+    ctx.prof_enable(False)
+    its = fem.kspIterations - its0
+    solves = fem.kspSolves - solves0
+    evals = fem.ts.rhs_evals - evals0
+    ms = max_over_ranks(ms, world)
+    ms_per_step = ms / args.steps
+
+    # dominant kernel: SpMV(K) fused with p.Ap inside CG
+    stored, spmv_bytes = K.bytes()
+    nnz_ref, nblocks = K.nnz()
+    peak, peak_src = load_peaks()
+    # CG launches iterations in chunks of 8 and polls a pinned status word; launches issued after
+    # convergence return at once.  Only the `its` live iterations move bytes, so the average is
+    # taken over those (the few-us dead launches stay in the numerator: slightly pessimistic).
+    live = max(min(its, n_spmv), 1)
+    avg_ms = ms_spmv / live
+    achieved = spmv_bytes / (avg_ms * 1e-3) / 1e9 if n_spmv else 0.0
+    roofline = {"bound": "hbm", "kernel": "spmv_kernel<3,3,32,DOT> on K (row-plane BSR)",
+                "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4),
+                "peak_source": peak_src, "bytes_per_launch": int(spmv_bytes), "launches": int(live),
+                "dead_launches": int(n_spmv - live),
+                "avg_launch_us": round(avg_ms * 1e3, 2), "share_of_step": round(ms_spmv / ms, 4),
+                "frac_of_nominal_8TBs": round(achieved / 8000.0, 4),
+                "reference_equivalent_GBs": round((12 * nnz_ref + 16 * ndof + 8 * ndof) / (avg_ms * 1e-3) / 1e9, 1)
+                if n_spmv else 0.0,
+                "traffic": read_traffic()}
+
+    e2e = None
+    if not args.no_e2e:
+        e2e = run_e2e(args, fem, ctx, world, ndof, nvort)
+
+    out = {
+        "metric": METRIC, "value": ndof * world / (ms_per_step * 1e-3), "unit": UNIT, "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": f"3-D Taylor-Green vortex, {args.nelem}^3 elements, ngl={args.ngl}, unit box "
+                               "(BASELINE.json configs[1]); one RK5BS time step = 7 evalRHS",
+                   "dofs": int(ndof), "nodes": int(ndof // 3), "ksp": f"cg+{args.pc}", "ksp_rtol": args.rtol,
+                   "dt": args.dt, "rhs_evals_per_step": evals / args.steps,
+                   "ksp_iterations_per_step": its / args.steps, "ksp_solves_per_step": solves / args.steps,
+                   "parallelism": "1 GPU" if world == 1 else f"{world} independent replicas (one per GPU)",
+                   "l2": "inputs larger than L2 (K = %.2f GB per SpMV)" % (spmv_bytes / 1e9)},
+        "roofline": roofline,
+        "kernel_time_ms_per_step": {"spmv_K_dot": ms_spmv / args.steps, "cg_update": ms_upd / args.steps,
+                                    "cg_direction": ms_dir / args.steps, "spmv_other": ms_oth / args.steps},
+        "assembly": assembly_report(asm, fem, ndof, peak),
+        "gpu_launches": int(launches),
+        "clocks": clocks,
+    }
+    if e2e:
+        out["e2e"] = e2e
+    return out
+
+
+def assembly_report(asm, fem, ndof, peak):
+    mats = [fem.mat.K, fem.mat.Krhs, fem.mat.Rw, fem.operator.Curl, fem.operator.SrT, fem.operator.DivSrT]
+    stored = sum(m.bytes()[0] for m in mats)
+    ref_nnz = sum(m.nnz()[0] for m in mats)
+    numeric_ms = asm["kle_numeric"] + asm["ops_numeric"]
+    total_ms = sum(asm.values())
+    return {"phase_ms": {k: round(v, 3) for k, v in asm.items()}, "total_ms": round(total_ms, 3),
+            "dof_per_s": ndof / (total_ms * 1e-3) if total_ms else None,
+            "stored_bytes": int(stored), "reference_pattern_nnz": int(ref_nnz),
+            "numeric_GBs_stored": round(stored / (numeric_ms * 1e-3) / 1e9, 1) if numeric_ms else None,
+            "numeric_frac_of_peak": round(stored / (numeric_ms * 1e-3) / 1e9 / peak, 4) if numeric_ms else None,
+            "host_setup_wall_s": round(fem.setup_wall_s, 3)}
+
+
+def run_e2e(args, fem, ctx, world, ndof, nvort):
+    """public-API time step with HOST-resident fields: upload vorticity+velocity from pinned memory,
+    ts.step(), read both back."""
+    vel = fem.solverKLE.getSolution()
+    h_vort, h_vel = ctx.pinned_empty(nvort), ctx.pinned_empty(ndof)
+    fem.vort.getArray(out=h_vort)
+    vel.getArray(out=h_vel)
+    bcb = bc_bytes_per_rhs(fem)
+    evals0 = fem.ts.rhs_evals
+
+    def step():
+        fem.vort.setArray(h_vort)
+        vel.setArray(h_vel)
+        fem.ts.step()
+        fem.vort.getArray(out=h_vort)
+        vel.getArray(out=h_vel)
+
+    step()
+    ctx.sync()
+    barrier(world)
+    evals0 = fem.ts.rhs_evals
+    ctx.timer_start()
+    for _ in range(args.steps):
+        step()
+    ms = ctx.timer_stop()
+    ms = max_over_ranks(ms, world)
+    evals = (fem.ts.rhs_evals - evals0) / args.steps
+    return {"value": ndof * world / (ms / args.steps * 1e-3), "unit": UNIT, "ms_per_step": ms / args.steps,
+            "h2d_bytes_per_step": int((nvort + ndof) * 8 + evals * bcb),
+            "d2h_bytes_per_step": int((nvort + ndof) * 8)}
+
+
+def read_traffic():
+    """dram bytes per launch of the dominant kernel from the committed ncu capture, if any"""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    try:
+        with open(p) as f:
+            return json.load(f).get("spmv_K_dram_bytes_per_launch")
+    except Exception:
+        return None
+
+
+# ---------------------------------------------------------------------------------------------
+# CPU: the oracle (a port of the reference's algorithm; the reference itself needs petsc4py,
+# which is not installed) timed on the host cores.  Checker code, used here only as the
+# reported baseline / the --impl reference arm.
+# ---------------------------------------------------------------------------------------------
+def cpu_timestep(args, steps, warmup):
+    """one bounded sample: the same RK5BS time step on a (cpu_nelem)^3, ngl mesh with scipy CG +
+    the same preconditioner and tolerance; returns (DOF/s, ms_per_step, description)"""
+    from oracle import timestep
+    from pynama_b200.domain.box_mesh import BoxMesh
+    n = args.cpu_nelem
+    mesh = BoxMesh([n] * 3, [0, 0, 0], [1, 1, 1], args.ngl)
+    prob = timestep.OracleProblem(3, args.ngl, mesh.corner_xyz, mesh.elem_nodes, mesh.coords,
+                                  mesh.getBordersNodes(), rho=0.5, mu=0.01, solver="cg", rtol=args.rtol,
+                                  pc=args.pc if args.pc != "none" else "jacobi")
+    ndof = mesh.nnodes * 3
+    t, k0 = 0.0, None
+    for _ in range(max(warmup, 1)):
+        t, k0 = prob.step(t, args.dt, k0)
+    its0 = prob.iterations
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        t, k0 = prob.step(t, args.dt, k0)
+    wall = time.perf_counter() - t0
+    ms = wall / steps * 1e3
+    sample = (f"{steps} RK5BS step(s) of the same Taylor-Green problem on a {n}^3-element, ngl={args.ngl} box "
+              f"({ndof} dofs; the 16^3 mesh does not assemble in scipy within minutes), scipy CSR SpMV + "
+              f"scipy CG with {args.pc} to rtol {args.rtol:g}, {(prob.iterations - its0) / steps:.0f} CG its/step, "
+              f"{wall:.1f} s of CPU work")
+    return ndof / (ms * 1e-3), ms, sample
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return None
+    steps, warmup = min(args.steps, 3), min(args.warmup, 1)
+    v, ms, sample = cpu_timestep(args, steps, warmup)
+    return {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": f"3-D Taylor-Green vortex, {args.nelem}^3 elements, ngl={args.ngl}, unit box "
+                                   "(BASELINE.json configs[1]); one RK5BS time step = 7 evalRHS",
+                       "note": "petsc4py/PETSc/mpirun are not installed: the reference's own modules cannot be "
+                               "imported; this arm times the CPU restatement (oracle/) of the same path"},
+            "cpu_baseline": {"value": v, "unit": UNIT, "cores": 1, "kind": "port", "sample": sample},
+            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+
+
+# ---------------------------------------------------------------------------------------------
+_DIST = None
+
+
+def init_dist():
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    global _DIST
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        use_cuda = torch.cuda.is_available()
+        if use_cuda:
+            torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", "0")))
+        dist.init_process_group("nccl" if use_cuda else "gloo")
+        _DIST = (dist, torch, use_cuda)
+    return rank, world
+
+
+def barrier(world):
+    if world > 1 and _DIST:
+        dist, torch, use_cuda = _DIST
+        dist.barrier()
+        if use_cuda:
+            torch.cuda.synchronize()
+
+
+def max_over_ranks(x, world):
+    if world > 1 and _DIST:
+        dist, torch, use_cuda = _DIST
+        t = torch.tensor([x], dtype=torch.float64, device="cuda" if use_cuda else "cpu")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+    return x
+
+
+def main():
+    args = parse_args()
+    rank, world = init_dist()
+    if args.impl == "reference":
+        out = run_reference(args, rank, world)
+    else:
+        out = run_b200(args, rank, world)
+        if rank == 0 and world == 1 and not args.no_cpu_baseline:
+            v, ms, sample = cpu_timestep(args, 1, 1)
+            out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": 1, "kind": "port", "sample": sample}
+    if rank == 0 and out is not None:
+        print(json.dumps(out), flush=True)
+    if _DIST:
+        _DIST[0].barrier()
+        _DIST[0].destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

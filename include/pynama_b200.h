@@ -58,6 +58,16 @@ int pyn_timer_stop(pyn_ctx* ctx, double* ms);
 int pyn_launch_count(pyn_ctx* ctx, int64_t* count);
 /* write `bytes` of device scratch (> L2) to evict the cache between timed runs */
 int pyn_flush_l2(pyn_ctx* ctx);
+/* Per-kernel-class CUDA-event profiler on the library's stream: while enabled
+ * every launch of the class is bracketed by an event pair; pyn_prof_get returns
+ * the launches seen and their summed device time since pyn_prof_enable(ctx, 1).
+ * cls: 0 SpMV+dot of the Krylov loop, 1 other SpMV, 2 CG update, 3 CG direction,
+ * 4 element KLE kernel, 5 assembly numeric kernel. */
+int pyn_prof_enable(pyn_ctx* ctx, int on);
+int pyn_prof_get(pyn_ctx* ctx, int cls, int64_t* count, double* total_ms);
+/* page-locked host memory for the caller's staging buffers (cudaMallocHost) */
+int pyn_host_alloc(int64_t bytes, void** out);
+int pyn_host_free(void* p);
 /* device memory in use by library objects of this context */
 int pyn_mem_used(pyn_ctx* ctx, int64_t* bytes);
 

@@ -1,0 +1,174 @@
+"""Oracle: KLE solve, vorticity-transport RHS and the RK5BS step (numpy/scipy, fp64).
+
+TEST INFRASTRUCTURE -- see oracle/__init__.py.  Restates
+
+* KleSolver.solve           src/solver/kle_solver.py:33-37   (b = Rw*w + Krhs*v; KSP(b, v))
+* BaseProblem.evalRHS       src/cases/base_problem.py:111-136
+* BaseProblem.computeVtensV src/cases/base_problem.py:139-154
+* setValuesToVec            src/boundaries/boundary_conditions.py:252-260 (BC scatter)
+* Taylor-Green 3-D fields   src/functions/taylor_green3d.py:4-33
+* Taylor-Green 2-D fields   src/functions/taylor_green.py:4-36
+* TS rk/5bs                 src/solver/ts_solver.py:5-23 (tableau: SURVEY.md 8a-A13;
+                            PETSc's TS itself is not in the reference tree -> the
+                            fixed-step stage recurrence is restated, adaptivity UNPINNED)
+
+The free-slip (FS) path only: boundary nodes are Dirichlet with analytic values.
+``evalRHS`` keeps the reference's quirk of differentiating the step-start
+vorticity for every stage (base_problem.py:115,125 use self.vort, not the
+stage vector TS passes in).
+"""
+from math import exp, pi
+
+import numpy as np
+import scipy.sparse.linalg as spl
+
+from . import assembly, sem
+
+# Bogacki-Shampine 5(4): same numbers as SURVEY.md 8a-A13 (checked against the order conditions
+# in tests/test_oracle_kats.py through the product's table; restated here so the oracle is standalone)
+RK5BS_A = [
+    [],
+    [1 / 6],
+    [2 / 27, 4 / 27],
+    [183 / 1372, -162 / 343, 1053 / 1372],
+    [68 / 297, -4 / 11, 42 / 143, 1960 / 3861],
+    [597 / 22528, 81 / 352, 63099 / 585728, 58653 / 366080, 4617 / 20480],
+    [174197 / 959244, -30942 / 79937, 8152137 / 19744439, 666106 / 1039181, -29421 / 29068,
+     482048 / 414219],
+    [587 / 8064, 0, 4440339 / 15491840, 24353 / 124800, 387 / 44800, 2152 / 5985, 7267 / 94080],
+]
+RK5BS_B = [587 / 8064, 0, 4440339 / 15491840, 24353 / 124800, 387 / 44800, 2152 / 5985, 7267 / 94080, 0]
+RK5BS_C = [0, 1 / 6, 2 / 9, 3 / 7, 2 / 3, 3 / 4, 1, 1]
+
+
+# ---- analytic fields -------------------------------------------------------------------------
+def tg_alpha(nu, t, dim):
+    """taylor_green3d.py:4-9 / taylor_green.py:4-8 (unit box)"""
+    return exp(-4 * pi ** 2 * nu * t * (3.0 if dim == 3 else 2.0))
+
+
+def tg_velocity(X, a):
+    x = 2 * pi * X
+    if X.shape[1] == 2:                                     # taylor_green.py:10-19
+        return np.stack([np.cos(x[:, 0]) * np.sin(x[:, 1]) * a, -np.sin(x[:, 0]) * np.cos(x[:, 1]) * a], 1).ravel()
+    return np.stack([np.cos(x[:, 0]) * np.sin(x[:, 1]) * np.sin(x[:, 2]) * a,                # :11-21
+                     np.sin(x[:, 0]) * np.cos(x[:, 1]) * np.sin(x[:, 2]) * a,
+                     -2 * np.sin(x[:, 0]) * np.sin(x[:, 1]) * np.cos(x[:, 2]) * a], 1).ravel()
+
+
+def tg_vorticity(X, a):
+    x = 2 * pi * X
+    if X.shape[1] == 2:                                     # taylor_green.py:21-27
+        return -2 * pi * 2.0 * np.cos(x[:, 0]) * np.cos(x[:, 1]) * a
+    return np.stack([-2 * pi * 3.0 * np.sin(x[:, 0]) * np.cos(x[:, 1]) * np.cos(x[:, 2]) * a,  # :23-32
+                     2 * pi * 3.0 * np.cos(x[:, 0]) * np.sin(x[:, 1]) * np.cos(x[:, 2]) * a,
+                     0.0 * x[:, 0]], 1).ravel()
+
+
+def vtensv(v, dim):
+    """base_problem.py:139-154"""
+    v = v.reshape(-1, dim)
+    if dim == 2:
+        return np.stack([v[:, 0] ** 2, v[:, 0] * v[:, 1], v[:, 1] ** 2], 1).ravel()
+    return np.stack([v[:, 0] ** 2, v[:, 0] * v[:, 1], v[:, 1] ** 2, v[:, 1] * v[:, 2], v[:, 2] ** 2,
+                     v[:, 2] * v[:, 0]], 1).ravel()
+
+
+class OracleProblem:
+    """Free-slip Taylor-Green problem on given mesh tables, CPU only."""
+
+    def __init__(self, dim, ngl, corner_xyz, elem_nodes, coords, bnd_nodes, rho, mu, solver="direct",
+                 rtol=1e-10, pc="jacobi", reuse=True):
+        self.dim, self.dim_w = dim, (1 if dim == 2 else 3)
+        self.rho, self.mu, self.nu = rho, mu, mu / rho
+        self.coords = np.asarray(coords, dtype=np.float64)
+        nnodes = len(self.coords)
+        self.bnd = np.asarray(bnd_nodes, dtype=np.int64)
+        cls = np.zeros(nnodes * dim, np.uint8)
+        self.bdofs = (self.bnd[:, None] * dim + np.arange(dim)[None, :]).ravel()
+        cls[self.bdofs] = 1
+        self.bwdofs = self.bnd if dim == 2 else self.bdofs
+        tab = sem.SpectralTables(ngl, dim)
+        self.mats = assembly.assemble_kle(tab, corner_xyz, elem_nodes, nnodes, cls, "FS", reuse=reuse)
+        self.ops = assembly.assemble_ops(tab, corner_xyz, elem_nodes, nnodes, reuse=reuse)
+        self.solver, self.rtol, self.pc = solver, rtol, pc
+        self.K = self.mats["K"].tocsr()
+        if solver == "direct":
+            self._lu = spl.splu(self.K.tocsc())
+        else:
+            self._setup_pc()
+        a0 = tg_alpha(self.nu, 0.0, dim)
+        self.vel = tg_velocity(self.coords, a0)
+        self.vort = tg_vorticity(self.coords, a0)
+        self.iterations = 0
+        self.solves = 0
+
+    def _setup_pc(self):
+        n, d = self.K.shape[0], self.dim
+        if self.pc == "jacobi":
+            dinv = 1.0 / self.K.diagonal()
+            self._M = spl.LinearOperator((n, n), matvec=lambda r: dinv * r)
+        else:                       # node-block Jacobi
+            import scipy.sparse as sp
+            B = sp.bsr_matrix(self.K, blocksize=(d, d))
+            B.sort_indices()
+            nb = n // d
+            blk = np.zeros((nb, d, d))
+            rows = np.repeat(np.arange(nb), np.diff(B.indptr))
+            sel = B.indices == rows
+            blk[rows[sel]] = B.data[sel]
+            inv = np.linalg.inv(blk)
+            self._M = spl.LinearOperator((n, n), matvec=lambda r: np.einsum("nij,nj->ni", inv, r.reshape(nb, d)).ravel())
+
+    # ---- kle_solver.py:33-37 ---------------------------------------------------------------------
+    def solve_kle(self, vort):
+        b = self.mats["Rw"] @ vort + self.mats["Krhs"] @ self.vel
+        if self.solver == "direct":
+            self.vel = self._lu.solve(b)
+        else:
+            its = [0]
+
+            def cb(_):
+                its[0] += 1
+            # PETSc's default test is on the preconditioned residual; scipy tests the true
+            # residual against rtol*||b|| -- same order for this SPD system.
+            x, info = spl.cg(self.K, b, x0=self.vel, rtol=self.rtol, atol=0.0, maxiter=20000, M=self._M,
+                             callback=cb)
+            self.vel = x
+            self.iterations += its[0]
+        self.solves += 1
+        return self.vel
+
+    # ---- base_problem.py:111-136 ------------------------------------------------------------------
+    def eval_rhs(self, t, vort_stage=None):
+        a = tg_alpha(self.nu, t, self.dim)
+        Xb = self.coords[self.bnd]
+        self.vort[self.bwdofs] = tg_vorticity(Xb, a)          # :115
+        self.vel[self.bdofs] = tg_velocity(Xb, a)             # :116-117
+        vel = self.solve_kle(self.vort)                       # :125  (self.vort, not the stage)
+        aux = self.ops["SrT"] @ vel                           # :128
+        aux *= 2.0 * self.mu                                  # :129
+        aux += -1.0 * self.rho * vtensv(vel, self.dim)        # :127,130
+        rhs = self.ops["DivSrT"] @ aux                        # :133
+        rhs *= 1.0 / self.rho                                 # :134
+        return self.ops["Curl"] @ rhs                         # :136
+
+    # ---- TS rk 5bs, fixed step ---------------------------------------------------------------------
+    def step(self, t, h, k0=None):
+        """one step from self.vort at time t; returns the new time and the FSAL stage"""
+        s = len(RK5BS_B)
+        k = [None] * s
+        u = self.vort
+        for i in range(s):
+            if i == 0 and k0 is not None:
+                k[0] = k0
+                continue
+            # stage vector (unused by eval_rhs, like the reference; built for fidelity of the BC
+            # scatter which writes into self.vort, i.e. u itself)
+            k[i] = self.eval_rhs(t + RK5BS_C[i] * h)
+        unew = u.copy()
+        for j in range(s):
+            if RK5BS_B[j] != 0.0:
+                unew += h * RK5BS_B[j] * k[j]
+        self.vort = unew
+        return t + h, k[s - 1]

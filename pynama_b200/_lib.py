@@ -45,6 +45,10 @@ _PROTOS = {
     "pyn_launch_count": [vp, P(c_i64)],
     "pyn_flush_l2": [vp],
     "pyn_mem_used": [vp, P(c_i64)],
+    "pyn_prof_enable": [vp, c_int],
+    "pyn_prof_get": [vp, c_int, P(c_i64), P(c_dbl)],
+    "pyn_host_alloc": [c_i64, P(vp)],
+    "pyn_host_free": [vp],
     "pyn_mesh_create": [vp, c_int, c_int, c_i64, c_i64, vp, vp, P(vp)],
     "pyn_mesh_destroy": [vp],
     "pyn_mesh_graph_info": [vp, P(c_i64), P(c_i64), P(c_int)],

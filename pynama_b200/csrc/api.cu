@@ -29,11 +29,69 @@ struct PhaseTimer {
     cudaEventDestroy(b);
   }
 };
+
+constexpr int kProfPairs = 4096;
+void prof_drain(pyn_ctx* ctx) {
+  if (ctx->prof_pending == 0) return;
+  cudaEventSynchronize(ctx->prof_ev[2 * (ctx->prof_pending - 1) + 1]);
+  for (int i = 0; i < ctx->prof_pending; ++i) {
+    float ms = 0;
+    if (cudaEventElapsedTime(&ms, ctx->prof_ev[2 * i], ctx->prof_ev[2 * i + 1]) == cudaSuccess) {
+      ctx->prof_ms[ctx->prof_cls[i]] += ms;
+      ctx->prof_count[ctx->prof_cls[i]]++;
+    }
+  }
+  ctx->prof_pending = 0;
+}
+void prof_begin(pyn_ctx* ctx, int cls) {
+  if (!ctx->prof_on) return;
+  if (ctx->prof_ev.empty()) {
+    ctx->prof_ev.resize(2 * kProfPairs);
+    ctx->prof_cls.resize(kProfPairs);
+    for (auto& e : ctx->prof_ev) cudaEventCreate(&e);
+  }
+  if (ctx->prof_pending == kProfPairs) prof_drain(ctx);
+  ctx->prof_cls[ctx->prof_pending] = cls;
+  cudaEventRecord(ctx->prof_ev[2 * ctx->prof_pending], ctx->stream);
+}
+void prof_end(pyn_ctx* ctx) {
+  if (!ctx->prof_on) return;
+  cudaEventRecord(ctx->prof_ev[2 * ctx->prof_pending + 1], ctx->stream);
+  ctx->prof_pending++;
+}
 }  // namespace pyn
 
 using namespace pyn;
 
 extern "C" {
+
+int pyn_prof_enable(pyn_ctx* ctx, int on) {
+  PYN_REQUIRE(ctx, "null ctx");
+  prof_drain(ctx);
+  ctx->prof_on = on != 0;
+  if (on)
+    for (int i = 0; i < PROF_COUNT; ++i) {
+      ctx->prof_ms[i] = 0.0;
+      ctx->prof_count[i] = 0;
+    }
+  return PYN_OK;
+}
+int pyn_prof_get(pyn_ctx* ctx, int cls, int64_t* count, double* total_ms) {
+  PYN_REQUIRE(ctx && cls >= 0 && cls < PROF_COUNT && count && total_ms, "pyn_prof_get: bad argument");
+  prof_drain(ctx);
+  *count = ctx->prof_count[cls];
+  *total_ms = ctx->prof_ms[cls];
+  return PYN_OK;
+}
+int pyn_host_alloc(int64_t bytes, void** out) {
+  PYN_REQUIRE(out && bytes > 0, "pyn_host_alloc: bad argument");
+  PYN_CUDA(cudaMallocHost(out, (size_t)bytes));
+  return PYN_OK;
+}
+int pyn_host_free(void* p) {
+  if (p) PYN_CUDA(cudaFreeHost(p));
+  return PYN_OK;
+}
 
 int pyn_version(void) { return 100; }
 const char* pyn_last_error(void) { return pyn::get_error(); }
@@ -78,6 +136,8 @@ int pyn_finalize(pyn_ctx* ctx) {
   if (!ctx) return PYN_OK;
   cudaSetDevice(ctx->device);
   cudaStreamSynchronize(ctx->stream);
+  prof_drain(ctx);
+  for (auto& e : ctx->prof_ev) cudaEventDestroy(e);
   if (ctx->flush_buf) cudaFree(ctx->flush_buf);
   cudaFree(ctx->red_partials);
   cudaFree(ctx->red_ticket);

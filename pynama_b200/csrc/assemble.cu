@@ -196,8 +196,10 @@ int assemble_matrix(pyn_mesh* mesh, const MatSpec& sp, pyn_mat** out) {
       m->nbrows, m->rowptr.p, m->colidx.p, m->base_slot.p, sp.graph->cptr.p, sp.graph->csrc.p,    \
       sp.ebs, sp.ebs_pairs, 0, sp.pair_map, sp.sign, mesh->dofcls.p, sp.use_rowcls, sp.use_colcls, \
       sp.pairmask, sp.diagmask, da, sp.row_scale, m->val.p)
+    prof_begin(ctx, PROF_NUMERIC);
     PYN_DISPATCH_BLOCK(sp.br, sp.bc, CALL);
 #undef CALL
+    prof_end(ctx);
     PYN_LAUNCHED(ctx);
   }
   *out = m;

@@ -71,6 +71,13 @@ struct pyn_ctx {
   double* red_result_host = nullptr;  // pinned
   void* flush_buf = nullptr;
   size_t flush_bytes = 0;
+  // per-kernel-class CUDA-event profiler (bench.py's live roofline timing)
+  bool prof_on = false;
+  std::vector<cudaEvent_t> prof_ev;     // pairs (begin, end)
+  std::vector<int> prof_cls;            // class of pending pair i
+  int prof_pending = 0;
+  double prof_ms[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  int64_t prof_count[8] = {0, 0, 0, 0, 0, 0, 0, 0};
 };
 
 namespace pyn {
@@ -144,6 +151,14 @@ inline int grid_for(const pyn_ctx* ctx, int64_t work_items, int block, int ctas_
   if (need < 1) need = 1;
   return (int)(need < cap ? need : cap);
 }
+
+// Kernel-class profiler: brackets one launch with a CUDA-event pair on the
+// context's stream when enabled (pyn_prof_enable); no-ops otherwise.
+enum ProfClass { PROF_SPMV_KSP = 0, PROF_SPMV = 1, PROF_CG_UPDATE = 2, PROF_CG_DIR = 3,
+                 PROF_ELEM_KLE = 4, PROF_NUMERIC = 5, PROF_COUNT = 8 };
+void prof_begin(pyn_ctx* ctx, int cls);
+void prof_end(pyn_ctx* ctx);
+void prof_drain(pyn_ctx* ctx);
 
 // exclusive scan of int64 counts on the device (single CTA chained; symbolic phase only)
 int exclusive_scan_i64(pyn_ctx* ctx, const int64_t* in, int64_t* out, int64_t n, int64_t* total_host);

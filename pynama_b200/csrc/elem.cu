@@ -191,6 +191,7 @@ int launch_elem_kle(pyn_mesh* mesh, int64_t e0, int64_t ne, double* ebsK, double
   kle_launch_shape(mesh, &TA, &GC, &natiles, &smem);
   PYN_REQUIRE(ne * natiles < (int64_t)2147483647, "element batch too large for one launch");
   dim3 grid((unsigned)(ne * natiles)), block(256);
+  prof_begin(ctx, PROF_ELEM_KLE);
   if (mesh->dim == 2) {
     PYN_CUDA(cudaFuncSetAttribute(elem_kle_kernel<2, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     elem_kle_kernel<2, 2><<<grid, block, smem, ctx->stream>>>(mesh->dtab.p, mesh->corners.p, e0, natiles,
@@ -200,6 +201,7 @@ int launch_elem_kle(pyn_mesh* mesh, int64_t e0, int64_t ne, double* ebsK, double
     elem_kle_kernel<3, 2><<<grid, block, smem, ctx->stream>>>(mesh->dtab.p, mesh->corners.p, e0, natiles,
                                                               TA, GC, ebsK, ebsRw, ebsRd);
   }
+  prof_end(ctx);
   PYN_LAUNCHED(ctx);
   return PYN_OK;
 }

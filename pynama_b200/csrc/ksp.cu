@@ -304,11 +304,15 @@ static int ksp_solve_cg(pyn_ksp* k, const double* b, double* x, int* its, int* r
     for (int j = 0; j < todo; ++j, ++it) {
       const int parity = it & 1;
       PYN_CHECK(spmv_dot(k->A, k->p.p, k->w.p, S + S_PW, S + S_DONE));
+      prof_begin(ctx, PROF_CG_UPDATE);
       cg_update_kernel<B><<<gridn, 256, 0, ctx->stream>>>(k->pc, k->pcd.p, k->p.p, k->w.p, x, k->r.p,
                                                           k->z.p, nn, S, parity, k->maxit,
                                                           ctx->red_partials, ctx->red_ticket);
+      prof_end(ctx);
       PYN_LAUNCHED(ctx);
+      prof_begin(ctx, PROF_CG_DIR);
       cg_direction_kernel<<<grid_for(ctx, n, 256), 256, 0, ctx->stream>>>(k->z.p, k->p.p, n, S, parity);
+      prof_end(ctx);
       PYN_LAUNCHED(ctx);
     }
     const int slot = chunk & 1;

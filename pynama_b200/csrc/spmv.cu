@@ -102,9 +102,11 @@ static int spmv_launch(pyn_mat* m, double alpha, const double* x, double beta, c
       else LAUNCH(BR, BC, 8, false);                     \
     }                                                    \
   } while (0)
+  prof_begin(ctx, dot ? PROF_SPMV_KSP : PROF_SPMV);
   PYN_DISPATCH_BLOCK(m->br, m->bc, CALL);
 #undef CALL
 #undef LAUNCH
+  prof_end(ctx);
   PYN_LAUNCHED(ctx);
   return PYN_OK;
 }

@@ -158,6 +158,27 @@ class Context:
         call("pyn_mem_used", self.handle, ctypes.byref(n))
         return n.value
 
+    PROF_CLASSES = {"spmv_ksp": 0, "spmv": 1, "cg_update": 2, "cg_direction": 3, "elem_kle": 4,
+                    "numeric": 5}
+
+    def prof_enable(self, on=True):
+        call("pyn_prof_enable", self.handle, 1 if on else 0)
+
+    def prof_get(self, name):
+        """(launches, summed device ms) of a kernel class since prof_enable(True)"""
+        n, ms = c_i64(), c_dbl()
+        call("pyn_prof_get", self.handle, self.PROF_CLASSES[name], ctypes.byref(n), ctypes.byref(ms))
+        return n.value, ms.value
+
+    @staticmethod
+    def pinned_empty(n):
+        """page-locked host staging buffer of n doubles as a numpy array"""
+        p = vp()
+        call("pyn_host_alloc", int(n) * 8, ctypes.byref(p))
+        buf = (ctypes.c_double * int(n)).from_address(p.value)
+        a = np.frombuffer(buf, dtype=np.float64)
+        return a
+
 
 # ---- Vec ------------------------------------------------------------------------------------
 class Vec:
@@ -249,8 +270,9 @@ class Vec:
     assemblyBegin = assemblyEnd = assemble
 
     # -- host <-> device
-    def getArray(self, readonly=False):
-        out = np.empty(self._n)
+    def getArray(self, readonly=False, out=None):
+        if out is None:
+            out = np.empty(self._n)
         call("pyn_vec_to_host", self._h, ptr(out))
         return out
 
