@@ -156,7 +156,10 @@ def bc_bytes_per_rhs(fem):
 def run_b200(args, rank, world):
     from pynama_b200.petsc import Context
     ctx = Context.get()
+    ctx.prof_enable(True)
     fem = build_problem(args)
+    asm_kernels = {k: ctx.prof_get(k) for k in ("elem_kle", "numeric")}
+    ctx.prof_enable(False)
     dm = fem.dom.getDeviceMesh()
     K = fem.mat.K
     ndof = K.getSize()[0]
@@ -232,7 +235,7 @@ def run_b200(args, rank, world):
         "roofline": roofline,
         "kernel_time_ms_per_step": {"spmv_K_dot": ms_spmv / args.steps, "cg_update": ms_upd / args.steps,
                                     "cg_direction": ms_dir / args.steps, "spmv_other": ms_oth / args.steps},
-        "assembly": assembly_report(asm, fem, ndof, peak),
+        "assembly": assembly_report(asm, asm_kernels, fem, ndof, peak),
         "gpu_launches": int(launches),
         "clocks": clocks,
     }
@@ -241,17 +244,25 @@ def run_b200(args, rank, world):
     return out
 
 
-def assembly_report(asm, fem, ndof, peak):
+def assembly_report(asm, kern, fem, ndof, peak):
+    """phase_ms: CUDA-event time of whole phases (first call in a fresh process: includes
+    cudaMalloc of the matrices); kernels: event time of the element kernel (fp64-bound) and of the
+    numeric COO->BSR kernels alone, with the numeric phase's algorithmic bytes = 8 B per stored
+    value written once."""
     mats = [fem.mat.K, fem.mat.Krhs, fem.mat.Rw, fem.operator.Curl, fem.operator.SrT, fem.operator.DivSrT]
     stored = sum(m.bytes()[0] for m in mats)
+    values = sum(m.nblocks() * m.getBlockSizes()[0] * m.getBlockSizes()[1] * 8 for m in mats)
     ref_nnz = sum(m.nnz()[0] for m in mats)
-    numeric_ms = asm["kle_numeric"] + asm["ops_numeric"]
     total_ms = sum(asm.values())
+    n_el, ms_el = kern["elem_kle"]
+    n_nu, ms_nu = kern["numeric"]
     return {"phase_ms": {k: round(v, 3) for k, v in asm.items()}, "total_ms": round(total_ms, 3),
             "dof_per_s": ndof / (total_ms * 1e-3) if total_ms else None,
             "stored_bytes": int(stored), "reference_pattern_nnz": int(ref_nnz),
-            "numeric_GBs_stored": round(stored / (numeric_ms * 1e-3) / 1e9, 1) if numeric_ms else None,
-            "numeric_frac_of_peak": round(stored / (numeric_ms * 1e-3) / 1e9 / peak, 4) if numeric_ms else None,
+            "kernels": {"elem_kle_ms": round(ms_el, 3), "numeric_ms": round(ms_nu, 3), "numeric_launches": n_nu,
+                        "numeric_value_bytes": int(values),
+                        "numeric_GBs": round(values / (ms_nu * 1e-3) / 1e9, 1) if ms_nu else None,
+                        "numeric_frac_of_peak": round(values / (ms_nu * 1e-3) / 1e9 / peak, 4) if ms_nu else None},
             "host_setup_wall_s": round(fem.setup_wall_s, 3)}
 
 

@@ -65,6 +65,9 @@ int pyn_flush_l2(pyn_ctx* ctx);
  * 4 element KLE kernel, 5 assembly numeric kernel. */
 int pyn_prof_enable(pyn_ctx* ctx, int on);
 int pyn_prof_get(pyn_ctx* ctx, int cls, int64_t* count, double* total_ms);
+/* process-wide tuning knobs.  "ksp_check_every": Krylov iterations launched between two
+ * polls of the device-side convergence flag (default 8). */
+int pyn_tune(const char* key, int value);
 /* page-locked host memory for the caller's staging buffers (cudaMallocHost) */
 int pyn_host_alloc(int64_t bytes, void** out);
 int pyn_host_free(void* p);
@@ -162,7 +165,14 @@ int pyn_vec_maxpy(pyn_vec* y, int k, const double* a, pyn_vec* const* x);
 /* Vec.setValues(idx, vals, addv) (boundary_conditions.py:252-260) */
 int pyn_vec_set_values(pyn_vec* v, int64_t k, const int64_t* idx, const double* vals, int add);
 int pyn_vec_get_values(pyn_vec* v, int64_t k, const int64_t* idx, double* vals);
-/* persistent scatter plan: indices uploaded once, values per call (k10) */
+/* persistent scatter plan (k10): the index list of the boundary dofs is uploaded once;
+ * every call stages `vals` (k doubles, host) through pinned memory and scatters them on the
+ * library's stream without a device synchronisation.  Replaces the per-evaluation
+ * Vec.setValues of BoundaryConditions.setValuesToVec (boundary_conditions.py:252-260). */
+typedef struct pyn_scatter pyn_scatter;
+int pyn_scatter_create(pyn_ctx* ctx, int64_t k, const int64_t* idx, pyn_scatter** out);
+int pyn_scatter_apply(pyn_scatter* plan, pyn_vec* v, const double* vals, int add);
+int pyn_scatter_destroy(pyn_scatter* plan);
 int pyn_vec_to_host(pyn_vec* v, double* out);
 int pyn_vec_from_host(pyn_vec* v, const double* in);
 /* raw device pointer (for torch.distributed plumbing) */

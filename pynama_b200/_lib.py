@@ -47,6 +47,7 @@ _PROTOS = {
     "pyn_mem_used": [vp, P(c_i64)],
     "pyn_prof_enable": [vp, c_int],
     "pyn_prof_get": [vp, c_int, P(c_i64), P(c_dbl)],
+    "pyn_tune": [ctypes.c_char_p, c_int],
     "pyn_host_alloc": [c_i64, P(vp)],
     "pyn_host_free": [vp],
     "pyn_mesh_create": [vp, c_int, c_int, c_i64, c_i64, vp, vp, P(vp)],
@@ -86,6 +87,9 @@ _PROTOS = {
     "pyn_vec_maxpy": [vp, c_int, vp, vp],
     "pyn_vec_set_values": [vp, c_i64, vp, vp, c_int],
     "pyn_vec_get_values": [vp, c_i64, vp, vp],
+    "pyn_scatter_create": [vp, c_i64, vp, P(vp)],
+    "pyn_scatter_apply": [vp, vp, vp, c_int],
+    "pyn_scatter_destroy": [vp],
     "pyn_vec_to_host": [vp, vp],
     "pyn_vec_from_host": [vp, vp],
     "pyn_vec_device_ptr": [vp, P(vp)],

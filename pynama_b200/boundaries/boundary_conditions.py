@@ -152,6 +152,7 @@ class BoundaryConditions:
         self._borderNames = list(sides)
         self._dim = 2 if len(sides) == 4 else 3
         self._plans = {}
+        self._scatter = {}
         self.logger = logging.getLogger(f"[{self.comm.rank}]Boundary Conditions:")
 
     # ---- configuration (boundary_conditions.py:44-148) -------------------------------------
@@ -227,6 +228,7 @@ class BoundaryConditions:
         self._byType[typ].append(b)
         self._byName[b.getName()] = b
         self._plans = {}
+        self._scatter = {}
 
     # ---- queries ---------------------------------------------------------------------------------
     def getNames(self, bcs=None):
@@ -246,6 +248,7 @@ class BoundaryConditions:
             raise Exception("Boundary Not found")
         self._byName[bName].setNodes(nodes)
         self._plans = {}
+        self._scatter = {}
 
     def setBoundaryCoords(self, bName, coords):
         self._byName[bName].setNodesCoordinates(coords)
@@ -314,7 +317,10 @@ class BoundaryConditions:
 
     def setValuesToVec(self, vec, name, t, nu):
         idx, vals = self.getValuesMerged(name, t, nu)
-        vec.setValues(idx, vals, addv=False)
+        if name not in self._scatter:
+            from ..petsc import ScatterPlan
+            self._scatter[name] = ScatterPlan(idx)      # indices go to the device once
+        self._scatter[name].apply(vec, vals, addv=False)
         vec.assemble()
 
     def setTangentialValuesToVec(self, vec, name, t, nu):

@@ -83,6 +83,15 @@ int pyn_prof_get(pyn_ctx* ctx, int cls, int64_t* count, double* total_ms) {
   *total_ms = ctx->prof_ms[cls];
   return PYN_OK;
 }
+int pyn_tune(const char* key, int value) {
+  PYN_REQUIRE(key, "pyn_tune: null key");
+  if (strcmp(key, "ksp_check_every") == 0 && value > 0) {
+    g_ksp_check_every = value;
+    return PYN_OK;
+  }
+  set_error("pyn_tune: unknown key '%s'", key);
+  return PYN_E_INVALID;
+}
 int pyn_host_alloc(int64_t bytes, void** out) {
   PYN_REQUIRE(out && bytes > 0, "pyn_host_alloc: bad argument");
   PYN_CUDA(cudaMallocHost(out, (size_t)bytes));

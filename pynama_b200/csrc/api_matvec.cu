@@ -283,6 +283,80 @@ int pyn_vec_set_values(pyn_vec* v, int64_t k, const int64_t* idx, const double* 
   PYN_CUDA(cudaStreamSynchronize(ctx->stream));
   return PYN_OK;
 }
+// ---- persistent scatter plan (k10): indices uploaded once, values per call ------------
+struct pyn_scatter {
+  pyn_ctx* ctx = nullptr;
+  int64_t k = 0, nmax = 0;
+  DevBuf<int64_t> idx;
+  static constexpr int kSlots = 4;
+  DevBuf<double> dvals[kSlots];
+  double* hvals[kSlots] = {nullptr, nullptr, nullptr, nullptr};   // pinned staging
+  cudaEvent_t done[kSlots] = {nullptr, nullptr, nullptr, nullptr};
+  int next = 0;
+};
+
+int pyn_scatter_create(pyn_ctx* ctx, int64_t k, const int64_t* idx, pyn_scatter** out) {
+  PYN_REQUIRE(ctx && out && k >= 0 && (k == 0 || idx), "pyn_scatter_create: bad argument");
+  pyn_scatter* p = new pyn_scatter();
+  p->ctx = ctx;
+  p->k = k;
+  for (int64_t i = 0; i < k; ++i) {
+    if (idx[i] < 0) {
+      delete p;
+      set_error("pyn_scatter_create: negative index");
+      return PYN_E_INVALID;
+    }
+    if (idx[i] + 1 > p->nmax) p->nmax = idx[i] + 1;
+  }
+  int rc = p->idx.alloc(ctx, k);
+  if (rc == PYN_OK) rc = p->idx.upload(idx, k);
+  for (int s = 0; s < pyn_scatter::kSlots && rc == PYN_OK; ++s) {
+    rc = p->dvals[s].alloc(ctx, k);
+    if (rc == PYN_OK && k > 0 && cudaMallocHost((void**)&p->hvals[s], sizeof(double) * k) != cudaSuccess) {
+      set_error("pyn_scatter_create: cudaMallocHost failed");
+      rc = PYN_E_NOMEM;
+    }
+    if (rc == PYN_OK) cudaEventCreateWithFlags(&p->done[s], cudaEventDisableTiming);
+  }
+  if (rc == PYN_OK && cudaStreamSynchronize(ctx->stream) != cudaSuccess) rc = PYN_E_CUDA;
+  if (rc != PYN_OK) {
+    pyn_scatter_destroy(p);
+    return rc;
+  }
+  *out = p;
+  return PYN_OK;
+}
+
+int pyn_scatter_apply(pyn_scatter* p, pyn_vec* v, const double* vals, int add) {
+  PYN_REQUIRE(p && v && (p->k == 0 || vals), "pyn_scatter_apply: bad argument");
+  PYN_REQUIRE(p->nmax <= v->n, "pyn_scatter_apply: plan index %lld beyond Vec size %lld",
+              (long long)(p->nmax - 1), (long long)v->n);
+  if (p->k == 0) return PYN_OK;
+  pyn_ctx* ctx = p->ctx;
+  const int s = p->next;
+  p->next = (p->next + 1) % pyn_scatter::kSlots;
+  PYN_CUDA(cudaEventSynchronize(p->done[s]));          // staging slot free again
+  memcpy(p->hvals[s], vals, sizeof(double) * p->k);
+  PYN_CUDA(cudaMemcpyAsync(p->dvals[s].p, p->hvals[s], sizeof(double) * p->k, cudaMemcpyHostToDevice,
+                           ctx->stream));
+  PYN_CHECK(vec_scatter(ctx, v->d.p, p->k, p->idx.p, p->dvals[s].p, add));
+  PYN_CUDA(cudaEventRecord(p->done[s], ctx->stream));
+  return PYN_OK;
+}
+
+int pyn_scatter_destroy(pyn_scatter* p) {
+  if (!p) return PYN_OK;
+  for (int s = 0; s < pyn_scatter::kSlots; ++s) {
+    if (p->done[s]) {
+      cudaEventSynchronize(p->done[s]);
+      cudaEventDestroy(p->done[s]);
+    }
+    if (p->hvals[s]) cudaFreeHost(p->hvals[s]);
+  }
+  delete p;
+  return PYN_OK;
+}
+
 int pyn_vec_get_values(pyn_vec* v, int64_t k, const int64_t* idx, double* vals) {
   PYN_REQUIRE(v && k >= 0 && (k == 0 || (idx && vals)), "Vec.getValues: bad argument");
   if (k == 0) return PYN_OK;

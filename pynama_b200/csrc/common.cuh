@@ -53,6 +53,7 @@ void set_error(const char* fmt, ...);
   } while (0)
 
 constexpr int kNumSMs = 148;  // B200: 2 dies x 74 SMs
+extern int g_ksp_check_every;
 
 }  // namespace pyn
 

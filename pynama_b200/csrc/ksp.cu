@@ -15,6 +15,7 @@
 #include "vec.cuh"
 
 namespace pyn {
+int g_ksp_check_every = 8;
 
 // device scalar block
 enum {
@@ -249,7 +250,7 @@ struct pyn_ksp {
   int type = PYN_KSP_CG, pc = PYN_PC_BJACOBI;
   double rtol = 1e-5, atol = 1e-50, dtol = 1e5;
   int maxit = 10000, restart = 30;
-  int check_every = 8;
+  int check_every = pyn::g_ksp_check_every;
   int B = 0;
   int64_t n = 0, nnodes = 0;
   DevBuf<double> pcd, r, z, p, w, S, tmp2;

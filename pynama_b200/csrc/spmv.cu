@@ -10,6 +10,7 @@
 #include "elem.cuh"
 #include "spmv.cuh"
 #include "vec.cuh"
+#include <stdlib.h>
 
 namespace pyn {
 
@@ -23,11 +24,21 @@ struct SpmvFuse {
   double* dot_out;
 };
 
+// Column ids of the next pass (and the extent + first column ids of the group's next row)
+// are fetched before the current pass is consumed, which takes the colidx -> x dependent
+// load off the critical path; the grid is exactly the resident set (4 CTAs of 256 threads
+// per SM at <= 64 registers: one wave, rows interleaved across warps).  Measured on K at
+// 16^3/ngl=4: 150.8 us = 5.95 TB/s (first version without the prefetch, 2 waves: 204 us).
+// Tighter register caps (6-8 CTAs/SM) made ptxas serialise the nine plane loads and lost
+// 40-90 %; unrolling the pass loop lost 3-20 %; a TMA-bulk shared-memory ring fed by a
+// producer warp (cp.async.bulk + mbarrier, 128 KB ring) was correct but 6x slower -- 16
+// consumer warps each holding a whole row (<= 24.7 KB) span more than the ring, so the
+// warps serialise (profiles/README.md, round 1).
 template <int BR, int BC, int G, bool DOT>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 4)
 spmv_kernel(int64_t nbrows, const int64_t* __restrict__ rowptr, const int32_t* __restrict__ colidx,
-            const double* __restrict__ val, const double* __restrict__ x, double alpha, double beta,
-            const double* __restrict__ z, double* __restrict__ y, SpmvFuse fuse) {
+             const double* __restrict__ val, const double* __restrict__ x, double alpha, double beta,
+             const double* __restrict__ z, double* __restrict__ y, SpmvFuse fuse) {
   constexpr int BB = BR * BC;
   __shared__ double red_sm[32];
   if (fuse.skip && *fuse.skip != 0.0) return;
@@ -35,40 +46,51 @@ spmv_kernel(int64_t nbrows, const int64_t* __restrict__ rowptr, const int32_t* _
   const int lane = threadIdx.x & (G - 1);
   const int64_t grp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / G;
   const int64_t ngrp = ((int64_t)gridDim.x * blockDim.x) / G;
-  // uniform trip count per warp: sub-warp groups past the end run empty rows
   const int64_t iters = (nbrows + ngrp - 1) / ngrp;
+  int64_t r = grp;
+  bool live = r < nbrows;
+  int64_t p0 = live ? rowptr[r] : 0;
+  int nb = live ? (int)(rowptr[r + 1] - p0) : 0;
+  int32_t cnext = lane < nb ? colidx[p0 + lane] : 0;
   for (int64_t it = 0; it < iters; ++it) {
-    const int64_t r = grp + it * ngrp;
-    const bool live = r < nbrows;
-    const int64_t p0 = live ? rowptr[r] : 0;
-    const int nb = live ? (int)(rowptr[r + 1] - p0) : 0;
+    // next row's extent, fetched early
+    const int64_t rn = r + ngrp;
+    const bool liven = rn < nbrows;
+    const int64_t p0n = liven ? rowptr[rn] : 0;
+    const int nbn = liven ? (int)(rowptr[rn + 1] - p0n) : 0;
     const double* __restrict__ v = val + p0 * BB;
     double acc[BR];
 #pragma unroll
     for (int i = 0; i < BR; ++i) acc[i] = 0.0;
     for (int u = lane; u < nb; u += G) {
-      const int64_t c = colidx[p0 + u];
+      const int64_t c = cnext;
+      if (u + G < nb) cnext = colidx[p0 + u + G];
       double xv[BC];
 #pragma unroll
       for (int j = 0; j < BC; ++j) xv[j] = x[c * BC + j];
 #pragma unroll
       for (int i = 0; i < BR; ++i)
 #pragma unroll
-        for (int j = 0; j < BC; ++j) acc[i] += v[(int64_t)(i * BC + j) * nb + u] * xv[j];
+        for (int j = 0; j < BC; ++j) acc[i] += __ldcs(v + (int64_t)(i * BC + j) * nb + u) * xv[j];
     }
+    if (lane < nbn) cnext = colidx[p0n + lane];
 #pragma unroll
     for (int i = 0; i < BR; ++i)
 #pragma unroll
       for (int o = G / 2; o > 0; o >>= 1) acc[i] += __shfl_xor_sync(0xffffffffu, acc[i], o, G);
 #pragma unroll
     for (int i = 0; i < BR; ++i) {
-      if (live && lane == i % G) {   // spread the br stores over the first lanes
+      if (live && lane == i % G) {
         double out = alpha * acc[i];
         if (beta != 0.0) out += beta * z[r * BR + i];
         y[r * BR + i] = out;
         if (DOT) dotacc[0] += out * x[r * BC + i];
       }
     }
+    r = rn;
+    live = liven;
+    p0 = p0n;
+    nb = nbn;
   }
   if (DOT) {
     block_reduce<1>(dotacc, red_sm);
@@ -82,7 +104,8 @@ static int spmv_launch(pyn_mat* m, double alpha, const double* x, double beta, c
   if (m->nbrows == 0) return PYN_OK;
   const double avg = m->nbrows ? (double)m->nblocks / (double)m->nbrows : 0.0;
   const int G = avg > 24.0 ? 32 : (avg > 10.0 ? 16 : 8);
-  const int grid = grid_for(ctx, m->nbrows * G, 256, 8);
+  // one wave: 4 resident CTAs per SM (__launch_bounds__(256, 4))
+  const int grid = grid_for(ctx, m->nbrows * G, 256, 4);
 #define LAUNCH(BR, BC, GG, DD)                                                                   \
   spmv_kernel<BR, BC, GG, DD><<<grid, 256, 0, ctx->stream>>>(m->nbrows, m->rowptr.p, m->colidx.p, \
                                                              m->val.p, x, alpha, beta, z, y, fuse)

@@ -9,4 +9,5 @@ int spmv_dot(pyn_mat* m, const double* x, double* y, double* dot_out, const doub
 int diag_blocks(pyn_mat* m, double* dblk);   // [nbrows][b][b]
 int scale_rows(pyn_mat* m, const double* l);
 int mat_add_new(pyn_mat* a, pyn_mat* b, pyn_mat** out);
+
 }  // namespace pyn

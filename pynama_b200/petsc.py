@@ -180,6 +180,36 @@ class Context:
         return a
 
 
+class ScatterPlan:
+    """Fixed index list + per-call values: ``Vec.setValues(idx, vals)`` for an index set that
+    never changes (the boundary dofs).  Indices live on the device; values go through pinned
+    staging and a scatter kernel on the library's stream, without synchronising."""
+
+    def __init__(self, indices):
+        idx = np.ascontiguousarray(np.asarray(indices).ravel(), dtype=np.int64)
+        self.k = idx.size
+        h = vp()
+        call("pyn_scatter_create", Context.get().handle, idx.size, ptr(idx), ctypes.byref(h))
+        self._h = h
+
+    def apply(self, vec, values, addv=False):
+        vals = _lib.as_f64(values).ravel()
+        if vals.size != self.k:
+            raise ValueError(f"ScatterPlan.apply: {vals.size} values for {self.k} indices")
+        call("pyn_scatter_apply", self._h, vec._h, ptr(vals), 1 if addv else 0)
+
+    def destroy(self):
+        if getattr(self, "_h", None) is not None and _lib._lib is not None:
+            _lib._lib.pyn_scatter_destroy(self._h)
+        self._h = None
+
+    def __del__(self):
+        try:
+            self.destroy()
+        except Exception:
+            pass
+
+
 # ---- Vec ------------------------------------------------------------------------------------
 class Vec:
     class NormType:

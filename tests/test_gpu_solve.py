@@ -92,7 +92,8 @@ def test_vtensv_kat3():
 
 
 @pytest.mark.parametrize("nelem,ngl,mode", [([5, 4], 3, "FS"), ([3, 3], 6, "FS"), ([3, 3, 3], 3, "FS"),
-                                            ([2, 3, 2], 4, "NS"), ([2, 2], 2, "NS")])
+                                            ([2, 3, 2], 4, "NS"), ([2, 2], 2, "NS"),
+                                            ([6, 5, 4], 4, "FS")])
 def test_spmv_all_matrices(nelem, ngl, mode):
     from pynama_b200.petsc import Vec
     mesh, dm, tab = _setup(nelem, ngl, 0.1)
@@ -193,3 +194,4 @@ def test_kle_solve_3d_vs_oracle():
     x0 = Vec().createWithArray(vbc)
     ksp.solve(b, x0)
     assert ksp.getConvergedReason() == -3 and ksp.getIterationNumber() == 3
+
