@@ -31,6 +31,7 @@ typedef struct pyn_mesh pyn_mesh;
 typedef struct pyn_mat pyn_mat;
 typedef struct pyn_vec pyn_vec;
 typedef struct pyn_ksp pyn_ksp;
+typedef struct pyn_halo pyn_halo;
 
 int pyn_version(void);
 const char* pyn_last_error(void);
@@ -73,6 +74,35 @@ int pyn_host_alloc(int64_t bytes, void** out);
 int pyn_host_free(void* p);
 /* device memory in use by library objects of this context */
 int pyn_mem_used(pyn_ctx* ctx, int64_t* bytes);
+
+/* ---- multi-GPU: one process per GPU, row-partitioned mesh ------------------------------
+ * Replaces PETSc/MPI under `mpiexec -n N` (makefile:2; DMPlex.distribute, dmplex.py:21): the
+ * ghost update PETSc's VecScatter does inside MatMult and the MPI_Allreduce of every
+ * VecDot/VecNorm in the KSP.  NCCL is loaded with dlopen (nccl_lib: path of libnccl.so.2, or
+ * NULL for the default search), so single-GPU use needs no NCCL at all.
+ * Rank 0 makes the 128-byte id; the host layer ships it to the other ranks. */
+int pyn_comm_unique_id(const char* nccl_lib, void* id128);
+int pyn_comm_init(pyn_ctx* ctx, const char* nccl_lib, int rank, int nranks, const void* id128);
+int pyn_comm_info(pyn_ctx* ctx, int* rank, int* nranks, int* nccl_version, int64_t* collectives);
+/* small host-value collective for the drivers: op 0 sum, 1 max; vals[n] in/out, n <= 64 */
+int pyn_comm_allreduce(pyn_ctx* ctx, double* vals, int n, int op);
+int pyn_comm_finalize(pyn_ctx* ctx);
+/* Node layout of this rank: owned nodes [0, n_own), ghost nodes [n_own, n_loc) grouped by
+ * owner.  Per neighbour i: ranks[i]; the owned nodes it needs send_nodes[send_ptr[i]:
+ * send_ptr[i+1]] (local ids); the run of the ghost section it fills, recv_off[i] (nodes past
+ * n_own) and recv_cnt[i]. */
+int pyn_halo_create(pyn_ctx* ctx, int64_t n_own, int64_t n_loc, int nneigh, const int32_t* ranks,
+                    const int64_t* send_ptr, const int32_t* send_nodes, const int64_t* recv_off,
+                    const int64_t* recv_cnt, pyn_halo** out);
+int pyn_halo_destroy(pyn_halo* h);
+/* ghost entries of v (n_loc*bs) <- the owners' values (pack kernel + grouped ncclSend/ncclRecv) */
+int pyn_halo_exchange(pyn_halo* h, pyn_vec* v, int bs);
+/* Mat of a partitioned mesh: products refresh the ghosts of x first and compute the owned
+ * rows only; a KSP on it sums its inner products over ranks. */
+int pyn_mat_set_halo(pyn_mat* m, pyn_halo* h);
+/* Vec of a partitioned mesh: entries [0, owned) are this rank's; dot/norm/sum run over them and
+ * are summed over ranks.  owned < 0 (default): plain local Vec. */
+int pyn_vec_set_owned(pyn_vec* v, int64_t owned);
 
 /* ---- mesh tables (inputs A0: dmplex.py:93-100,193-196; domain.py:233-250) ----
  * corner_xyz: nel * 2^dim * dim, DMPlex closure-vertex order;
@@ -175,6 +205,9 @@ int pyn_scatter_apply(pyn_scatter* plan, pyn_vec* v, const double* vals, int add
 int pyn_scatter_destroy(pyn_scatter* plan);
 int pyn_vec_to_host(pyn_vec* v, double* out);
 int pyn_vec_from_host(pyn_vec* v, const double* in);
+/* first n entries only (the owned part of a row-partitioned Vec) */
+int pyn_vec_to_host_n(pyn_vec* v, double* out, int64_t n);
+int pyn_vec_from_host_n(pyn_vec* v, const double* in, int64_t n);
 /* raw device pointer (for torch.distributed plumbing) */
 int pyn_vec_device_ptr(pyn_vec* v, void** ptr);
 

@@ -50,6 +50,16 @@ _PROTOS = {
     "pyn_tune": [ctypes.c_char_p, c_int],
     "pyn_host_alloc": [c_i64, P(vp)],
     "pyn_host_free": [vp],
+    "pyn_comm_unique_id": [ctypes.c_char_p, vp],
+    "pyn_comm_init": [vp, ctypes.c_char_p, c_int, c_int, vp],
+    "pyn_comm_info": [vp, P(c_int), P(c_int), P(c_int), P(c_i64)],
+    "pyn_comm_allreduce": [vp, vp, c_int, c_int],
+    "pyn_comm_finalize": [vp],
+    "pyn_halo_create": [vp, c_i64, c_i64, c_int, vp, vp, vp, vp, vp, P(vp)],
+    "pyn_halo_destroy": [vp],
+    "pyn_halo_exchange": [vp, vp, c_int],
+    "pyn_mat_set_halo": [vp, vp],
+    "pyn_vec_set_owned": [vp, c_i64],
     "pyn_mesh_create": [vp, c_int, c_int, c_i64, c_i64, vp, vp, P(vp)],
     "pyn_mesh_destroy": [vp],
     "pyn_mesh_graph_info": [vp, P(c_i64), P(c_i64), P(c_int)],
@@ -92,6 +102,8 @@ _PROTOS = {
     "pyn_scatter_destroy": [vp],
     "pyn_vec_to_host": [vp, vp],
     "pyn_vec_from_host": [vp, vp],
+    "pyn_vec_to_host_n": [vp, vp, c_i64],
+    "pyn_vec_from_host_n": [vp, vp, c_i64],
     "pyn_vec_device_ptr": [vp, P(vp)],
     "pyn_ksp_create": [vp, vp, c_int, c_int, P(vp)],
     "pyn_ksp_set_tolerances": [vp, c_dbl, c_dbl, c_int, c_int],

@@ -4,6 +4,7 @@
 #include "elem.cuh"
 #include "spmv.cuh"
 #include "vec.cuh"
+#include "comm.cuh"
 
 namespace pyn {
 int vtensv(pyn_ctx* ctx, const double* vel, double* out, int64_t nnodes, int dim);
@@ -197,6 +198,20 @@ int pyn_vec_destroy(pyn_vec* v) {
   delete v;
   return PYN_OK;
 }
+int pyn_vec_set_owned(pyn_vec* v, int64_t owned) {
+  PYN_REQUIRE(v && owned <= v->n, "pyn_vec_set_owned: %lld owned entries of %lld", (long long)owned,
+              v ? (long long)v->n : -1LL);
+  v->owned = owned;
+  return PYN_OK;
+}
+int pyn_mat_set_halo(pyn_mat* m, pyn_halo* h) {
+  PYN_REQUIRE(m, "null mat");
+  PYN_REQUIRE(!h || (h->n_loc == m->nbrows && h->n_loc == m->nbcols),
+              "pyn_mat_set_halo: layout has %lld local nodes, matrix is %lld x %lld", h ? (long long)h->n_loc : 0LL,
+              (long long)m->nbrows, (long long)m->nbcols);
+  m->halo = h;
+  return PYN_OK;
+}
 int pyn_vec_size(pyn_vec* v, int64_t* n) {
   PYN_REQUIRE(v && n, "null argument");
   *n = v->n;
@@ -243,18 +258,18 @@ int pyn_vec_reciprocal(pyn_vec* v) {
 }
 int pyn_vec_dot(pyn_vec* x, pyn_vec* y, double* out) {
   PYN_REQUIRE(x && y && out && x->n == y->n, "Vec.dot: size mismatch");
-  return vec_dot(x->ctx, x->d.p, y->d.p, x->n, out);
+  return vec_dot(x->ctx, x->d.p, y->d.p, x->owned >= 0 ? x->owned : x->n, out, x->owned >= 0);
 }
 int pyn_vec_norm2(pyn_vec* x, double* out) {
   PYN_REQUIRE(x && out, "null argument");
   double s = 0;
-  PYN_CHECK(vec_dot(x->ctx, x->d.p, x->d.p, x->n, &s));
+  PYN_CHECK(vec_dot(x->ctx, x->d.p, x->d.p, x->owned >= 0 ? x->owned : x->n, &s, x->owned >= 0));
   *out = sqrt(s);
   return PYN_OK;
 }
 int pyn_vec_sum(pyn_vec* x, double* out) {
   PYN_REQUIRE(x && out, "null argument");
-  return vec_sum(x->ctx, x->d.p, x->n, out);
+  return vec_sum(x->ctx, x->d.p, x->owned >= 0 ? x->owned : x->n, out, x->owned >= 0);
 }
 int pyn_vec_maxpy(pyn_vec* y, int k, const double* a, pyn_vec* const* x) {
   PYN_REQUIRE(y && k >= 0 && (k == 0 || (a && x)), "Vec.maxpy: bad argument");
@@ -379,6 +394,16 @@ int pyn_vec_to_host(pyn_vec* v, double* out) {
 int pyn_vec_from_host(pyn_vec* v, const double* in) {
   PYN_REQUIRE(v && (in || v->n == 0), "null argument");
   PYN_CHECK(v->d.upload(in, v->n));
+  PYN_CUDA(cudaStreamSynchronize(v->ctx->stream));
+  return PYN_OK;
+}
+int pyn_vec_to_host_n(pyn_vec* v, double* out, int64_t n) {
+  PYN_REQUIRE(v && n >= 0 && n <= v->n && (out || n == 0), "pyn_vec_to_host_n: bad argument");
+  return v->d.download(out, n);
+}
+int pyn_vec_from_host_n(pyn_vec* v, const double* in, int64_t n) {
+  PYN_REQUIRE(v && n >= 0 && n <= v->n && (in || n == 0), "pyn_vec_from_host_n: bad argument");
+  PYN_CHECK(v->d.upload(in, n));
   PYN_CUDA(cudaStreamSynchronize(v->ctx->stream));
   return PYN_OK;
 }

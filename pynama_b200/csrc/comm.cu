@@ -1,0 +1,252 @@
+// comm.cu -- NCCL (dlopen'ed) communicator, halo exchange, scalar allreduce.
+#include "comm.cuh"
+
+#include <dlfcn.h>
+
+namespace pyn {
+
+// Minimal NCCL ABI (stable across 2.x): declared here so no NCCL header/library is needed at
+// build or load time of the single-GPU path.
+typedef struct { char internal[128]; } nccl_uid_t;
+typedef void* nccl_comm_t;
+enum { NCCL_SUCCESS = 0 };
+enum { NCCL_FLOAT64 = 8 };   // ncclDataType_t: ncclFloat64 / ncclDouble
+enum { NCCL_SUM = 0 };       // ncclRedOp_t
+
+struct NcclApi {
+  void* lib = nullptr;
+  int (*GetUniqueId)(nccl_uid_t*) = nullptr;
+  int (*CommInitRank)(nccl_comm_t*, int, nccl_uid_t, int) = nullptr;
+  int (*CommDestroy)(nccl_comm_t) = nullptr;
+  int (*AllReduce)(const void*, void*, size_t, int, int, nccl_comm_t, cudaStream_t) = nullptr;
+  int (*Send)(const void*, size_t, int, int, nccl_comm_t, cudaStream_t) = nullptr;
+  int (*Recv)(void*, size_t, int, int, nccl_comm_t, cudaStream_t) = nullptr;
+  int (*GroupStart)() = nullptr;
+  int (*GroupEnd)() = nullptr;
+  const char* (*GetErrorString)(int) = nullptr;
+  int (*GetVersion)(int*) = nullptr;
+};
+
+static NcclApi g_nccl;
+
+static int load_nccl(const char* path) {
+  if (g_nccl.lib) return PYN_OK;
+  const char* cands[3] = {path && path[0] ? path : nullptr, "libnccl.so.2", "libnccl.so"};
+  void* lib = nullptr;
+  for (int i = 0; i < 3 && !lib; ++i)
+    if (cands[i]) lib = dlopen(cands[i], RTLD_NOW | RTLD_LOCAL);
+  if (!lib) {
+    set_error("cannot load NCCL (%s): %s", path ? path : "libnccl.so.2", dlerror());
+    return PYN_E_NCCL;
+  }
+#define SYM(field, name)                                        \
+  *(void**)(&g_nccl.field) = dlsym(lib, name);                  \
+  if (!g_nccl.field) {                                          \
+    set_error("NCCL symbol %s not found", name);                \
+    return PYN_E_NCCL;                                          \
+  }
+  SYM(GetUniqueId, "ncclGetUniqueId");
+  SYM(CommInitRank, "ncclCommInitRank");
+  SYM(CommDestroy, "ncclCommDestroy");
+  SYM(AllReduce, "ncclAllReduce");
+  SYM(Send, "ncclSend");
+  SYM(Recv, "ncclRecv");
+  SYM(GroupStart, "ncclGroupStart");
+  SYM(GroupEnd, "ncclGroupEnd");
+  SYM(GetErrorString, "ncclGetErrorString");
+  SYM(GetVersion, "ncclGetVersion");
+#undef SYM
+  g_nccl.lib = lib;
+  return PYN_OK;
+}
+
+#define PYN_NCCL(call)                                                                        \
+  do {                                                                                        \
+    int _e = (call);                                                                          \
+    if (_e != NCCL_SUCCESS) {                                                                 \
+      pyn::set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #call, g_nccl.GetErrorString(_e)); \
+      return PYN_E_NCCL;                                                                      \
+    }                                                                                         \
+  } while (0)
+
+int comm_allreduce_sum(pyn_ctx* ctx, double* dev, int n) {
+  if (ctx->nranks <= 1) return PYN_OK;
+  PYN_NCCL(g_nccl.AllReduce(dev, dev, (size_t)n, NCCL_FLOAT64, NCCL_SUM, (nccl_comm_t)ctx->nccl_comm,
+                            ctx->stream));
+  ctx->collectives++;
+  return PYN_OK;
+}
+
+__global__ void halo_pack_kernel(const double* __restrict__ v, const int32_t* __restrict__ nodes,
+                                 int64_t n, int bs, double* __restrict__ out) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n * bs;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t k = i / bs;
+    const int c = (int)(i - k * bs);
+    out[i] = v[(int64_t)nodes[k] * bs + c];
+  }
+}
+
+int halo_exchange(pyn_halo* h, double* v, int bs) {
+  pyn_ctx* ctx = h->ctx;
+  if (ctx->nranks <= 1 || h->nneigh == 0) return PYN_OK;
+  const int64_t nsend = h->send_ptr[h->nneigh];
+  if (h->sendbuf_bs < bs) {
+    PYN_CHECK(h->sendbuf.alloc(ctx, nsend * bs > 0 ? nsend * bs : 1));
+    h->sendbuf_bs = bs;
+  }
+  if (nsend > 0) {
+    halo_pack_kernel<<<grid_for(ctx, nsend * bs, 256), 256, 0, ctx->stream>>>(v, h->send_nodes.p, nsend, bs,
+                                                                              h->sendbuf.p);
+    PYN_LAUNCHED(ctx);
+  }
+  PYN_NCCL(g_nccl.GroupStart());
+  for (int i = 0; i < h->nneigh; ++i) {
+    const int64_t ns = h->send_ptr[i + 1] - h->send_ptr[i];
+    if (ns > 0)
+      PYN_NCCL(g_nccl.Send(h->sendbuf.p + h->send_ptr[i] * bs, (size_t)(ns * bs), NCCL_FLOAT64, h->ranks[i],
+                           (nccl_comm_t)ctx->nccl_comm, ctx->stream));
+    if (h->recv_cnt[i] > 0)
+      PYN_NCCL(g_nccl.Recv(v + (h->n_own + h->recv_off[i]) * bs, (size_t)(h->recv_cnt[i] * bs), NCCL_FLOAT64,
+                           h->ranks[i], (nccl_comm_t)ctx->nccl_comm, ctx->stream));
+  }
+  PYN_NCCL(g_nccl.GroupEnd());
+  ctx->collectives++;
+  return PYN_OK;
+}
+
+}  // namespace pyn
+
+using namespace pyn;
+
+extern "C" {
+
+int pyn_comm_unique_id(const char* nccl_lib, void* id128) {
+  PYN_REQUIRE(id128, "pyn_comm_unique_id: null id");
+  PYN_CHECK(load_nccl(nccl_lib));
+  nccl_uid_t id;
+  PYN_NCCL(g_nccl.GetUniqueId(&id));
+  memcpy(id128, &id, sizeof(id));
+  return PYN_OK;
+}
+
+int pyn_comm_init(pyn_ctx* ctx, const char* nccl_lib, int rank, int nranks, const void* id128) {
+  PYN_REQUIRE(ctx && nranks >= 1 && rank >= 0 && rank < nranks, "pyn_comm_init: bad rank %d of %d", rank,
+              nranks);
+  ctx->rank = rank;
+  ctx->nranks = nranks;
+  if (nranks == 1) return PYN_OK;
+  PYN_REQUIRE(id128, "pyn_comm_init: null id");
+  PYN_CHECK(load_nccl(nccl_lib));
+  PYN_CUDA(cudaSetDevice(ctx->device));
+  nccl_uid_t id;
+  memcpy(&id, id128, sizeof(id));
+  nccl_comm_t comm = nullptr;
+  PYN_NCCL(g_nccl.CommInitRank(&comm, nranks, id, rank));
+  ctx->nccl_comm = comm;
+  // first collective builds the channels; do it here, not inside a timed region
+  DevBuf<double> one;
+  PYN_CHECK(one.alloc(ctx, 1));
+  PYN_CHECK(one.zero());
+  PYN_CHECK(comm_allreduce_sum(ctx, one.p, 1));
+  PYN_CUDA(cudaStreamSynchronize(ctx->stream));
+  return PYN_OK;
+}
+
+int pyn_comm_info(pyn_ctx* ctx, int* rank, int* nranks, int* nccl_version, int64_t* collectives) {
+  PYN_REQUIRE(ctx, "null ctx");
+  if (rank) *rank = ctx->rank;
+  if (nranks) *nranks = ctx->nranks;
+  if (nccl_version) {
+    *nccl_version = 0;
+    if (g_nccl.lib) g_nccl.GetVersion(nccl_version);
+  }
+  if (collectives) *collectives = ctx->collectives;
+  return PYN_OK;
+}
+
+int pyn_comm_allreduce(pyn_ctx* ctx, double* vals, int n, int op) {
+  PYN_REQUIRE(ctx && vals && n > 0 && n <= 64 && (op == 0 || op == 1), "pyn_comm_allreduce: bad argument");
+  if (ctx->nranks <= 1) return PYN_OK;
+  // op 0: sum; op 1: max (as a sum of one-hot slots: every rank writes its values into its own
+  // row of an nranks x n table, the table is summed, the host takes the max)
+  const int rows = op == 1 ? ctx->nranks : 1;
+  std::vector<double> host((size_t)rows * n, 0.0);
+  for (int i = 0; i < n; ++i) host[(size_t)(op == 1 ? ctx->rank : 0) * n + i] = vals[i];
+  DevBuf<double> d;
+  PYN_CHECK(d.alloc(ctx, rows * n));
+  PYN_CHECK(d.upload(host.data(), rows * n));
+  PYN_CHECK(comm_allreduce_sum(ctx, d.p, rows * n));
+  PYN_CHECK(d.download(host.data(), rows * n));
+  for (int i = 0; i < n; ++i) {
+    double v = host[i];
+    for (int r = 1; r < rows; ++r) v = host[(size_t)r * n + i] > v ? host[(size_t)r * n + i] : v;
+    vals[i] = v;
+  }
+  return PYN_OK;
+}
+
+int pyn_comm_finalize(pyn_ctx* ctx) {
+  if (ctx && ctx->nccl_comm && g_nccl.lib) {
+    cudaStreamSynchronize(ctx->stream);
+    g_nccl.CommDestroy((nccl_comm_t)ctx->nccl_comm);
+    ctx->nccl_comm = nullptr;
+  }
+  return PYN_OK;
+}
+
+int pyn_halo_create(pyn_ctx* ctx, int64_t n_own, int64_t n_loc, int nneigh, const int32_t* ranks,
+                    const int64_t* send_ptr, const int32_t* send_nodes, const int64_t* recv_off,
+                    const int64_t* recv_cnt, pyn_halo** out) {
+  PYN_REQUIRE(ctx && out && n_own >= 0 && n_loc >= n_own && nneigh >= 0, "pyn_halo_create: bad argument");
+  PYN_REQUIRE(nneigh == 0 || (ranks && send_ptr && recv_off && recv_cnt), "pyn_halo_create: null table");
+  pyn_halo* h = new pyn_halo();
+  h->ctx = ctx;
+  h->n_own = n_own;
+  h->n_loc = n_loc;
+  h->nneigh = nneigh;
+  h->send_ptr.assign(1, 0);
+  for (int i = 0; i < nneigh; ++i) {
+    bool ok = ranks[i] >= 0 && ranks[i] < ctx->nranks && ranks[i] != ctx->rank &&
+              send_ptr[i + 1] >= send_ptr[i] && recv_off[i] >= 0 && recv_cnt[i] >= 0 &&
+              recv_off[i] + recv_cnt[i] <= n_loc - n_own;
+    if (!ok) {
+      delete h;
+      set_error("pyn_halo_create: inconsistent table for neighbour %d", i);
+      return PYN_E_INVALID;
+    }
+    h->ranks.push_back(ranks[i]);
+    h->send_ptr.push_back(send_ptr[i + 1]);
+    h->recv_off.push_back(recv_off[i]);
+    h->recv_cnt.push_back(recv_cnt[i]);
+  }
+  const int64_t nsend = nneigh ? send_ptr[nneigh] : 0;
+  for (int64_t i = 0; i < nsend; ++i)
+    if (send_nodes[i] < 0 || send_nodes[i] >= n_own) {
+      delete h;
+      set_error("pyn_halo_create: send node %lld is not an owned node", (long long)send_nodes[i]);
+      return PYN_E_INVALID;
+    }
+  int rc = h->send_nodes.alloc(ctx, nsend > 0 ? nsend : 1);
+  if (rc == PYN_OK && nsend > 0) rc = h->send_nodes.upload(send_nodes, nsend);
+  if (rc == PYN_OK && cudaStreamSynchronize(ctx->stream) != cudaSuccess) rc = PYN_E_CUDA;
+  if (rc != PYN_OK) {
+    delete h;
+    return rc;
+  }
+  *out = h;
+  return PYN_OK;
+}
+
+int pyn_halo_destroy(pyn_halo* h) {
+  delete h;
+  return PYN_OK;
+}
+
+int pyn_halo_exchange(pyn_halo* h, pyn_vec* v, int bs) {
+  PYN_REQUIRE(h && v && bs > 0 && v->n == h->n_loc * bs, "pyn_halo_exchange: Vec has %lld entries, layout %lld x %d",
+              v ? (long long)v->n : -1LL, h ? (long long)h->n_loc : -1LL, bs);
+  return halo_exchange(h, v->d.p, bs);
+}
+
+}  // extern "C"

@@ -72,6 +72,10 @@ struct pyn_ctx {
   double* red_result_host = nullptr;  // pinned
   void* flush_buf = nullptr;
   size_t flush_bytes = 0;
+  // multi-GPU (comm.cu): one process per GPU
+  int rank = 0, nranks = 1;
+  void* nccl_comm = nullptr;
+  int64_t collectives = 0;
   // per-kernel-class CUDA-event profiler (bench.py's live roofline timing)
   bool prof_on = false;
   std::vector<cudaEvent_t> prof_ev;     // pairs (begin, end)
@@ -170,5 +174,8 @@ int exclusive_scan_i32_to_i64(pyn_ctx* ctx, const int32_t* in, int64_t* out, int
 struct pyn_vec {
   pyn_ctx* ctx = nullptr;
   int64_t n = 0;
+  // row-partitioned Vec: entries [0, owned) belong to this rank (reductions run over them and
+  // are summed over ranks), [owned, n) are ghost copies.  owned < 0: not distributed.
+  int64_t owned = -1;
   pyn::DevBuf<double> d;
 };

@@ -13,6 +13,7 @@
 // iterations launched after convergence return immediately.
 #include "ksp.cuh"
 #include "vec.cuh"
+#include "comm.cuh"
 
 namespace pyn {
 int g_ksp_check_every = 8;
@@ -29,6 +30,8 @@ enum {
   S_REASON = 7,
   S_RNORM = 8,
   S_DTOL = 9,
+  S_LRZ = 10,  // this rank's r.z / z.z partials (row-partitioned runs), summed in place by
+  S_LZZ = 11,  // an allreduce before the bookkeeping kernel
   S_COUNT = 16
 };
 
@@ -77,13 +80,43 @@ pc_apply_dots_kernel(int pc, const double* __restrict__ pcd, const double* __res
   grid_reduce_finish<2>(v, partials, ticket, out);
 }
 
+// scalar bookkeeping of one iteration: new r.z, residual norm, convergence / breakdown test
+__device__ __forceinline__ void cg_bookkeeping(double* S, double rz_new, double zz, int parity, int maxit) {
+  const double pw = S[S_PW];
+  S[parity ? S_RZ0 : S_RZ1] = rz_new;
+  S[S_ZZ] = zz;
+  const double its = S[S_ITS] + 1.0;
+  S[S_ITS] = its;
+  const double rn = sqrt(zz);
+  S[S_RNORM] = rn;
+  if (!(rn == rn) || !(pw == pw) || pw == 0.0) {       // NaN / breakdown
+    S[S_REASON] = -9.0;
+    S[S_DONE] = 1.0;
+  } else if (rn <= S[S_TTOL]) {
+    S[S_REASON] = S[S_REASON] == 0.0 ? 2.0 : S[S_REASON];
+    S[S_DONE] = 1.0;
+  } else if (rn >= S[S_DTOL]) {
+    S[S_REASON] = -4.0;                                  // DIVERGED_DTOL
+    S[S_DONE] = 1.0;
+  } else if (its >= (double)maxit) {
+    S[S_REASON] = -3.0;                                  // DIVERGED_ITS
+    S[S_DONE] = 1.0;
+  }
+}
+
+// row-partitioned runs: the partials S_LRZ/S_LZZ were summed over ranks by an allreduce
+__global__ void cg_scalars_kernel(double* S, int parity, int maxit) {
+  if (S[S_DONE] != 0.0) return;
+  cg_bookkeeping(S, S[S_LRZ], S[S_LZZ], parity, maxit);
+}
+
 // step (2) of the iteration + convergence test in the last CTA
 template <int B>
 __global__ void __launch_bounds__(256)
 cg_update_kernel(int pc, const double* __restrict__ pcd, const double* __restrict__ p,
                  const double* __restrict__ w, double* __restrict__ x, double* __restrict__ r,
                  double* __restrict__ z, int64_t nnodes, double* S, int parity, int maxit,
-                 double* partials, unsigned int* ticket) {
+                 double* partials, unsigned int* ticket, int dist) {
   __shared__ double sm[64];
   __shared__ bool is_last;
   if (S[S_DONE] != 0.0) return;
@@ -130,25 +163,11 @@ cg_update_kernel(int pc, const double* __restrict__ pcd, const double* __restric
   __syncthreads();
   if (threadIdx.x == 0) {
     *ticket = 0u;
-    const double rz_new = sm[0], zz = sm[1];
-    S[parity ? S_RZ0 : S_RZ1] = rz_new;
-    S[S_ZZ] = zz;
-    const double its = S[S_ITS] + 1.0;
-    S[S_ITS] = its;
-    const double rn = sqrt(zz);
-    S[S_RNORM] = rn;
-    if (!(rn == rn) || !(pw == pw) || pw == 0.0) {       // NaN / breakdown
-      S[S_REASON] = -9.0;
-      S[S_DONE] = 1.0;
-    } else if (rn <= S[S_TTOL]) {
-      S[S_REASON] = S[S_REASON] == 0.0 ? 2.0 : S[S_REASON];
-      S[S_DONE] = 1.0;
-    } else if (rn >= S[S_DTOL]) {
-      S[S_REASON] = -4.0;                                  // DIVERGED_DTOL
-      S[S_DONE] = 1.0;
-    } else if (its >= (double)maxit) {
-      S[S_REASON] = -3.0;                                  // DIVERGED_ITS
-      S[S_DONE] = 1.0;
+    if (dist) {                    // partial sums of this rank; allreduce + cg_scalars_kernel follow
+      S[S_LRZ] = sm[0];
+      S[S_LZZ] = sm[1];
+    } else {
+      cg_bookkeeping(S, sm[0], sm[1], parity, maxit);
     }
   }
 }
@@ -280,9 +299,12 @@ static int ksp_setup_pc(pyn_ksp* k) {
 template <int B>
 static int ksp_solve_cg(pyn_ksp* k, const double* b, double* x, int* its, int* reason, double* rnorm) {
   pyn_ctx* ctx = k->ctx;
-  const int64_t n = k->n, nn = k->nnodes;
+  const int dist = k->A->halo != nullptr && ctx->nranks > 1;
+  // row-partitioned: Krylov vectors hold owned + ghost entries, the kernels touch the owned ones
+  const int64_t nn = k->A->halo ? k->A->halo->n_own : k->nnodes;
+  const int64_t n = nn * B;
   double* S = k->S.p;
-  const int gridn = grid_for(ctx, nn, 256);
+  const int gridn = grid_for(ctx, nn > 0 ? nn : 1, 256);
   if (!k->pc_ready) PYN_CHECK(ksp_setup_pc<B>(k));
   // ||M^-1 b|| for the threshold (KSPConvergedDefault with the preconditioned norm)
   pc_apply_dots_kernel<B><<<gridn, 256, 0, ctx->stream>>>(k->pc, k->pcd.p, b, k->z.p, nn, ctx->red_partials,
@@ -293,6 +315,7 @@ static int ksp_solve_cg(pyn_ksp* k, const double* b, double* x, int* its, int* r
   pc_apply_dots_kernel<B><<<gridn, 256, 0, ctx->stream>>>(k->pc, k->pcd.p, k->r.p, k->z.p, nn,
                                                           ctx->red_partials, ctx->red_ticket, k->tmp2.p);
   PYN_LAUNCHED(ctx);
+  if (dist) PYN_CHECK(comm_allreduce_sum(ctx, k->tmp2.p, 4));
   cg_init_scalars_kernel<<<1, 1, 0, ctx->stream>>>(S, k->tmp2.p, k->tmp2.p + 2, k->rtol, k->atol, k->dtol, 0);
   PYN_LAUNCHED(ctx);
   PYN_CUDA(cudaMemcpyAsync(k->p.p, k->z.p, sizeof(double) * n, cudaMemcpyDeviceToDevice, ctx->stream));
@@ -305,14 +328,20 @@ static int ksp_solve_cg(pyn_ksp* k, const double* b, double* x, int* its, int* r
     for (int j = 0; j < todo; ++j, ++it) {
       const int parity = it & 1;
       PYN_CHECK(spmv_dot(k->A, k->p.p, k->w.p, S + S_PW, S + S_DONE));
+      if (dist) PYN_CHECK(comm_allreduce_sum(ctx, S + S_PW, 1));
       prof_begin(ctx, PROF_CG_UPDATE);
       cg_update_kernel<B><<<gridn, 256, 0, ctx->stream>>>(k->pc, k->pcd.p, k->p.p, k->w.p, x, k->r.p,
                                                           k->z.p, nn, S, parity, k->maxit,
-                                                          ctx->red_partials, ctx->red_ticket);
+                                                          ctx->red_partials, ctx->red_ticket, dist);
       prof_end(ctx);
       PYN_LAUNCHED(ctx);
+      if (dist) {
+        PYN_CHECK(comm_allreduce_sum(ctx, S + S_LRZ, 2));
+        cg_scalars_kernel<<<1, 1, 0, ctx->stream>>>(S, parity, k->maxit);
+        PYN_LAUNCHED(ctx);
+      }
       prof_begin(ctx, PROF_CG_DIR);
-      cg_direction_kernel<<<grid_for(ctx, n, 256), 256, 0, ctx->stream>>>(k->z.p, k->p.p, n, S, parity);
+      cg_direction_kernel<<<grid_for(ctx, n > 0 ? n : 1, 256), 256, 0, ctx->stream>>>(k->z.p, k->p.p, n, S, parity);
       prof_end(ctx);
       PYN_LAUNCHED(ctx);
     }

@@ -1,6 +1,7 @@
 // mesh.cuh -- mesh tables on the device, node graphs, block matrices.
 #pragma once
 #include "tables.cuh"
+struct pyn_halo;
 
 namespace pyn {
 
@@ -65,6 +66,9 @@ struct pyn_mat {
   uint32_t pairmask = 0xFFFF;
   uint32_t diagmask = 0;
   bool ref_dense = true;           // reference pattern lives on the dense graph
+  // row-partitioned run: rows [0, halo->n_own) are this rank's; x gets its ghost entries
+  // refreshed before every product (comm.cu)
+  pyn_halo* halo = nullptr;
 };
 
 #define PYN_DISPATCH_BLOCK(br, bc, CALL)                        \

@@ -10,6 +10,7 @@
 #include "elem.cuh"
 #include "spmv.cuh"
 #include "vec.cuh"
+#include "comm.cuh"
 #include <stdlib.h>
 
 namespace pyn {
@@ -102,12 +103,18 @@ static int spmv_launch(pyn_mat* m, double alpha, const double* x, double beta, c
                        double* y, bool dot, SpmvFuse fuse) {
   pyn_ctx* ctx = m->ctx;
   if (m->nbrows == 0) return PYN_OK;
+  int64_t nrows = m->nbrows;
+  if (m->halo) {                       // distributed: refresh the ghosts of x, own rows only
+    PYN_CHECK(halo_exchange(m->halo, const_cast<double*>(x), m->bc));
+    nrows = m->halo->n_own;
+    if (nrows == 0) return PYN_OK;
+  }
   const double avg = m->nbrows ? (double)m->nblocks / (double)m->nbrows : 0.0;
   const int G = avg > 24.0 ? 32 : (avg > 10.0 ? 16 : 8);
   // one wave: 4 resident CTAs per SM (__launch_bounds__(256, 4))
-  const int grid = grid_for(ctx, m->nbrows * G, 256, 4);
+  const int grid = grid_for(ctx, nrows * G, 256, 4);
 #define LAUNCH(BR, BC, GG, DD)                                                                   \
-  spmv_kernel<BR, BC, GG, DD><<<grid, 256, 0, ctx->stream>>>(m->nbrows, m->rowptr.p, m->colidx.p, \
+  spmv_kernel<BR, BC, GG, DD><<<grid, 256, 0, ctx->stream>>>(nrows, m->rowptr.p, m->colidx.p, \
                                                              m->val.p, x, alpha, beta, z, y, fuse)
 #define CALL(BR, BC)                                     \
   do {                                                   \
@@ -264,6 +271,7 @@ int mat_add_new(pyn_mat* a, pyn_mat* b, pyn_mat** out) {
     return rc;
   }
   c->ref_dense = a->ref_dense;
+  c->halo = a->halo;
   DevBuf<int64_t> apos, bpos;
   const int64_t ns = a->graph->nslots;
   rc = apos.alloc(ctx, ns);

@@ -1,6 +1,7 @@
 // vec.cu -- device Vec operations (PETSc.Vec surface of the hot path)
 // and the pointwise pieces of the vorticity-transport RHS (k8, k9, k10).
 #include "vec.cuh"
+#include "comm.cuh"
 
 namespace pyn {
 
@@ -42,15 +43,17 @@ static int fetch_scalar(pyn_ctx* ctx, double* out_host) {
   return PYN_OK;
 }
 
-int vec_dot(pyn_ctx* ctx, const double* x, const double* y, int64_t n, double* out_host) {
+int vec_dot(pyn_ctx* ctx, const double* x, const double* y, int64_t n, double* out_host, bool dist) {
   PYN_CHECK(vec_dot_dev(ctx, x, y, n, ctx->red_result_dev));
+  if (dist) PYN_CHECK(comm_allreduce_sum(ctx, ctx->red_result_dev, 1));
   return fetch_scalar(ctx, out_host);
 }
 
-int vec_sum(pyn_ctx* ctx, const double* x, int64_t n, double* out_host) {
+int vec_sum(pyn_ctx* ctx, const double* x, int64_t n, double* out_host, bool dist) {
   sum_kernel<<<grid_for(ctx, n, 256 * 4), 256, 0, ctx->stream>>>(x, n, ctx->red_partials,
                                                                  ctx->red_ticket, ctx->red_result_dev);
   PYN_LAUNCHED(ctx);
+  if (dist) PYN_CHECK(comm_allreduce_sum(ctx, ctx->red_result_dev, 1));
   return fetch_scalar(ctx, out_host);
 }
 

@@ -58,8 +58,9 @@ __device__ __forceinline__ void grid_reduce_finish(double (&v)[NV], double* part
 }
 
 int vec_dot_dev(pyn_ctx* ctx, const double* x, const double* y, int64_t n, double* out_dev);
-int vec_dot(pyn_ctx* ctx, const double* x, const double* y, int64_t n, double* out_host);
-int vec_sum(pyn_ctx* ctx, const double* x, int64_t n, double* out_host);
+// dist: n counts the owned entries; the result is summed over ranks
+int vec_dot(pyn_ctx* ctx, const double* x, const double* y, int64_t n, double* out_host, bool dist = false);
+int vec_sum(pyn_ctx* ctx, const double* x, int64_t n, double* out_host, bool dist = false);
 int vec_set(pyn_ctx* ctx, double* x, int64_t n, double a);
 int vec_scale(pyn_ctx* ctx, double* x, int64_t n, double a);
 // y = a*x + b*y

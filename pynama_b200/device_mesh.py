@@ -18,7 +18,11 @@ PHASES = {"symbolic": 0, "elem_kle": 1, "kle_numeric": 2, "elem_ops": 3, "ops_nu
 
 
 class DeviceMesh:
-    def __init__(self, dim, ngl, corner_xyz, elem_nodes, nnodes):
+    def __init__(self, dim, ngl, corner_xyz, elem_nodes, nnodes, layout=None):
+        """layout: petsc.Layout of a row-partitioned run -- the tables are then this rank's local
+        ones (owned + halo elements, local node ids) and every assembled matrix computes only
+        the owned rows."""
+        self.layout = layout
         self.dim, self.ngl = int(dim), int(ngl)
         self.nn = self.ngl ** self.dim
         self.dim_w = 1 if dim == 2 else 3
@@ -90,6 +94,8 @@ class DeviceMesh:
             if out[i]:
                 mats[name] = Mat(vp(out[i]), name=name)
                 mats[name]._keep = self          # matrices point into the mesh's graphs
+                if self.layout is not None:
+                    mats[name]._setLayout(self.layout)
         return mats
 
     def assemble_ops(self, compact=True):
@@ -100,4 +106,9 @@ class DeviceMesh:
         mats = [Mat(c, "Curl"), Mat(s, "SrT"), Mat(d, "DivSrT")]
         for m in mats:
             m._keep = self
-        return mats[0], mats[1], mats[2], Vec(handle=w, name="lumped-mass")
+            if self.layout is not None:
+                m._setLayout(self.layout)
+        wv = Vec(handle=w, name="lumped-mass")
+        if self.layout is not None:
+            wv._setLayout(self.layout, 1)
+        return mats[0], mats[1], mats[2], wv

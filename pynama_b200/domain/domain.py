@@ -211,8 +211,21 @@ class Domain:
         if self._dmesh is None:
             from ..device_mesh import DeviceMesh
             m = self._mesh
-            self._dmesh = DeviceMesh(m.dim, m.ngl, m.corner_xyz, m.elem_nodes, m.nnodes)
-            self._dmesh.set_dof_class(self.getDofClasses())
+            cls = self.getDofClasses()
+            if self.comm.size > 1:
+                # row partition over the GPUs of the box (replaces DMPlex.distribute, dmplex.py:21)
+                from ..parallel import Partition
+                from ..petsc import Layout
+                part = Partition(m, self.comm.rank, self.comm.size)
+                self._partition = part
+                layout = Layout(part, m.nnodes)
+                self._dmesh = DeviceMesh(m.dim, m.ngl, part.corner_xyz, part.elem_nodes, part.n_loc,
+                                         layout=layout)
+                ldofs = (part.l2g[:, None] * m.dim + np.arange(m.dim)[None, :]).ravel()
+                cls = cls[ldofs]
+            else:
+                self._dmesh = DeviceMesh(m.dim, m.ngl, m.corner_xyz, m.elem_nodes, m.nnodes)
+            self._dmesh.set_dof_class(cls)
         return self._dmesh
 
     def computeLocalKLEMats(self, cell):

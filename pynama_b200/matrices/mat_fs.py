@@ -87,7 +87,8 @@ class Operators(MatFS):
         # the reciprocal lumped mass, repeated per vorticity component, alive
         self.lumpedMass = w
         wc = w.getArray().repeat(self.dim_w)
-        self.weigCurl = Vec().createWithArray(1.0 / wc)
+        self.weigCurl = self.Curl.createVecLeft()
+        self.weigCurl.setArray(1.0 / wc)
 
     def assembleAll(self):
         pass

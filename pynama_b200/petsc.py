@@ -127,6 +127,39 @@ class Context:
         call("pyn_init", device, ctypes.byref(h))
         self.handle = h
         self.device = device
+        self.rank, self.size = COMM_WORLD.rank, COMM_WORLD.size
+        if self.size > 1:
+            self._init_comm()
+
+    def _init_comm(self):
+        """NCCL communicator over the GPUs of the box: rank 0 makes the unique id, the host-side
+        rendezvous (torch.distributed, gloo, 127.0.0.1) ships it."""
+        import torch.distributed as dist
+        if not dist.is_initialized():
+            os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+            os.environ.setdefault("MASTER_PORT", "29511")
+            dist.init_process_group("gloo", rank=self.rank, world_size=self.size)
+        lib = _nccl_library()
+        libb = lib.encode() if lib else None
+        uid = ctypes.create_string_buffer(128)
+        if self.rank == 0:
+            call("pyn_comm_unique_id", libb, uid)
+        box = [bytes(uid.raw)]
+        dist.broadcast_object_list(box, src=0)
+        uid = ctypes.create_string_buffer(box[0], 128)
+        call("pyn_comm_init", self.handle, libb, self.rank, self.size, uid)
+
+    def allreduce(self, values, op="sum"):
+        """small host-value collective over the ranks (sum | max)"""
+        a = _lib.as_f64(np.atleast_1d(values)).copy()
+        if self.size > 1:
+            call("pyn_comm_allreduce", self.handle, ptr(a), a.size, {"sum": 0, "max": 1}[op])
+        return a
+
+    def collectives(self):
+        n = c_i64()
+        call("pyn_comm_info", self.handle, None, None, None, ctypes.byref(n))
+        return n.value
 
     @classmethod
     def get(cls):
@@ -180,14 +213,58 @@ class Context:
         return a
 
 
+def _nccl_library():
+    """path of the NCCL shipped with torch's wheels (newer than the system one), else None"""
+    override = os.environ.get("PYN_NCCL_LIB")
+    if override:
+        return override
+    try:
+        import importlib.util
+        spec = importlib.util.find_spec("nvidia.nccl")
+        for base in (spec.submodule_search_locations if spec else []):
+            cand = os.path.join(base, "lib", "libnccl.so.2")
+            if os.path.exists(cand):
+                return cand
+    except Exception:
+        pass
+    return None
+
+
+class Layout:
+    """Node layout of a row-partitioned mesh on this rank (pynama_b200/parallel.py) + the device
+    halo-exchange plan.  Vecs/Mats of a partitioned run carry one."""
+
+    def __init__(self, part, n_global_nodes):
+        self.part = part
+        self.n_own, self.n_loc, self.n_glob = part.n_own, part.n_loc, int(n_global_nodes)
+        ranks, send_ptr, send_nodes, recv_off, recv_cnt = part.halo_tables()
+        h = vp()
+        call("pyn_halo_create", Context.get().handle, self.n_own, self.n_loc, len(ranks), ptr(ranks),
+             ptr(send_ptr), ptr(send_nodes), ptr(recv_off), ptr(recv_cnt), ctypes.byref(h))
+        self._h = h
+        self.neighbors = [int(r) for r in ranks]
+        self.halo_nodes = int(send_ptr[-1]), int(recv_cnt.sum())
+
+    def exchange(self, vec):
+        call("pyn_halo_exchange", self._h, vec._h, vec._bs)
+
+
 class ScatterPlan:
     """Fixed index list + per-call values: ``Vec.setValues(idx, vals)`` for an index set that
     never changes (the boundary dofs).  Indices live on the device; values go through pinned
     staging and a scatter kernel on the library's stream, without synchronising."""
 
     def __init__(self, indices):
-        idx = np.ascontiguousarray(np.asarray(indices).ravel(), dtype=np.int64)
-        self.k = idx.size
+        self._idx = np.ascontiguousarray(np.asarray(indices).ravel(), dtype=np.int64)
+        self.k = self._idx.size
+        self._h = None
+        self._keep = None
+
+    def _bind(self, vec):
+        idx = self._idx
+        if vec._layout is not None:          # global dof ids -> the ones this rank holds
+            self._keep, idx = vec._layout.part.local_dofs(idx, vec._bs)
+            idx = np.ascontiguousarray(idx, dtype=np.int64)
         h = vp()
         call("pyn_scatter_create", Context.get().handle, idx.size, ptr(idx), ctypes.byref(h))
         self._h = h
@@ -196,6 +273,10 @@ class ScatterPlan:
         vals = _lib.as_f64(values).ravel()
         if vals.size != self.k:
             raise ValueError(f"ScatterPlan.apply: {vals.size} values for {self.k} indices")
+        if self._h is None:
+            self._bind(vec)
+        if self._keep is not None:
+            vals = np.ascontiguousarray(vals[self._keep])
         call("pyn_scatter_apply", self._h, vec._h, ptr(vals), 1 if addv else 0)
 
     def destroy(self):
@@ -221,6 +302,7 @@ class Vec:
         self._h = None
         self._name = name
         self._n = 0
+        self._layout, self._bs = None, 1
         if handle is not None:
             self._h = handle
             m = c_i64()
@@ -248,17 +330,38 @@ class Vec:
         call("pyn_vec_from_host", self._h, ptr(array))
         return self
 
+    def _setLayout(self, layout, bs):
+        """row-partitioned Vec: n_loc*bs local entries, the first n_own*bs owned"""
+        self._layout, self._bs = layout, int(bs)
+        if layout is not None:
+            call("pyn_vec_set_owned", self._h, layout.n_own * self._bs)
+        return self
+
+    def _like(self, name=""):
+        v = Vec(self._n, name=name)
+        if self._layout is not None:
+            v._setLayout(self._layout, self._bs)
+        return v
+
+    def _owned(self):
+        return self._n if self._layout is None else self._layout.n_own * self._bs
+
     def duplicate(self, array=None):
-        v = Vec(self._n)
+        v = self._like()
         if array is not None:
             v.setArray(array)
         return v
 
     def copy(self, result=None):
         if result is None:
-            result = Vec(self._n, name=self._name)
+            result = self._like(self._name)
         call("pyn_vec_copy", self._h, result._h)
         return result
+
+    def ghostUpdate(self):
+        """refresh the ghost entries from their owners (VecGhostUpdate)"""
+        if self._layout is not None:
+            self._layout.exchange(self)
 
     def destroy(self):
         if getattr(self, "_h", None) is not None and _lib._lib is not None:
@@ -280,13 +383,13 @@ class Vec:
         return self._name
 
     def getSize(self):
-        return self._n
+        return self._n if self._layout is None else self._layout.n_glob * self._bs
 
     def getLocalSize(self):
-        return self._n
+        return self._owned()
 
     def getSizes(self):
-        return (self._n, self._n)
+        return (self.getLocalSize(), self.getSize())
 
     def getOwnershipRange(self):
         return (0, self._n)
@@ -301,18 +404,41 @@ class Vec:
 
     # -- host <-> device
     def getArray(self, readonly=False, out=None):
+        """host copy of the local (owned) part, as PETSc's Vec.getArray"""
+        n = self._owned()
         if out is None:
-            out = np.empty(self._n)
+            out = np.empty(n)
+        call("pyn_vec_to_host_n", self._h, ptr(out), n)
+        return out
+
+    def getLocalArray(self):
+        """owned + ghost entries"""
+        out = np.empty(self._n)
         call("pyn_vec_to_host", self._h, ptr(out))
+        return out
+
+    def getGlobalArray(self):
+        """the whole distributed Vec in global numbering, on every rank (tests / output)"""
+        if self._layout is None:
+            return self.getArray()
+        lay = self._layout
+        parts = COMM_WORLD.allgather((lay.part.owned, self.getArray()))
+        out = np.zeros(lay.n_glob * self._bs)
+        for nodes, vals in parts:
+            idx = (nodes[:, None] * self._bs + np.arange(self._bs)[None, :]).ravel()
+            out[idx] = vals
         return out
 
     array = property(getArray)
 
     def setArray(self, array):
         array = _lib.as_f64(array).ravel()
-        if len(array) != self._n:
-            raise ValueError(f"Vec.setArray: {len(array)} values for a Vec of size {self._n}")
-        call("pyn_vec_from_host", self._h, ptr(array))
+        if len(array) == self._n:
+            call("pyn_vec_from_host", self._h, ptr(array))
+        elif len(array) == self._owned():
+            call("pyn_vec_from_host_n", self._h, ptr(array), len(array))
+        else:
+            raise ValueError(f"Vec.setArray: {len(array)} values for a Vec of local size {self._owned()}")
 
     def __array__(self, dtype=None, copy=None):
         a = self.getArray()
@@ -325,6 +451,9 @@ class Vec:
             vals = np.full(idx.size, vals[0])
         if idx.size != vals.size:
             raise ValueError(f"Vec.setValues: {idx.size} indices but {vals.size} values")
+        if self._layout is not None:         # global ids; entries of nodes held elsewhere are dropped
+            keep, idx = self._layout.part.local_dofs(idx, self._bs)
+            idx, vals = np.ascontiguousarray(idx, dtype=np.int64), np.ascontiguousarray(vals[keep])
         call("pyn_vec_set_values", self._h, idx.size, ptr(idx), ptr(vals), 1 if addv else 0)
 
     def setValue(self, index, value, addv=None):
@@ -332,6 +461,11 @@ class Vec:
 
     def getValues(self, indices):
         idx = np.ascontiguousarray(np.asarray(indices).ravel(), dtype=np.int64)
+        if self._layout is not None:
+            keep, lidx = self._layout.part.local_dofs(idx, self._bs)
+            if len(keep) != idx.size:
+                raise PynamaError("Vec.getValues: some of the requested entries live on another rank")
+            idx = np.ascontiguousarray(lidx, dtype=np.int64)
         out = np.empty(idx.size)
         call("pyn_vec_get_values", self._h, idx.size, ptr(idx), ptr(out))
         return out
@@ -391,7 +525,7 @@ class Vec:
         return out.value
 
     def __mul__(self, other):
-        r = Vec(self._n)
+        r = self._like()
         if isinstance(other, Vec):
             r.pointwiseMult(self, other)
         else:
@@ -408,12 +542,12 @@ class Vec:
         return self
 
     def __add__(self, other):
-        r = Vec(self._n)
+        r = self._like()
         r.waxpy(1.0, self, other)
         return r
 
     def __sub__(self, other):
-        r = Vec(self._n)
+        r = self._like()
         r.waxpy(-1.0, other, self)
         return r
 
@@ -440,6 +574,13 @@ class Mat:
         self._h = handle
         self._name = name
         self._shape = None
+        self._layout = None
+
+    def _setLayout(self, layout):
+        """matrix of a row-partitioned mesh: owned rows only, ghost refresh before each product"""
+        self._layout = layout
+        call("pyn_mat_set_halo", self._h, layout._h if layout is not None else None)
+        return self
 
     def _info(self):
         if self._shape is None:
@@ -457,11 +598,19 @@ class Mat:
 
     def getSize(self):
         s = self._info()
+        if self._layout is not None:
+            return (self._layout.n_glob * s[2], self._layout.n_glob * s[3])
+        return (s[0], s[1])
+
+    def getLocalSize(self):
+        s = self._info()
+        if self._layout is not None:
+            return (self._layout.n_own * s[2], self._layout.n_own * s[3])
         return (s[0], s[1])
 
     def getSizes(self):
-        s = self._info()
-        return ((s[0], s[0]), (s[1], s[1]))
+        g, l = self.getSize(), self.getLocalSize()
+        return ((l[0], g[0]), (l[1], g[1]))
 
     def getBlockSizes(self):
         s = self._info()
@@ -471,10 +620,12 @@ class Mat:
         return (0, self._info()[0])
 
     def createVecRight(self):
-        return Vec(self._info()[1])
+        s = self._info()
+        return Vec(s[1])._setLayout(self._layout, s[3])
 
     def createVecLeft(self):
-        return Vec(self._info()[0])
+        s = self._info()
+        return Vec(s[0])._setLayout(self._layout, s[2])
 
     def createVecs(self):
         return self.createVecRight(), self.createVecLeft()
@@ -503,6 +654,7 @@ class Mat:
         call("pyn_mat_add_new", self._h, other._h, ctypes.byref(h))
         m = Mat(h, name=f"{self._name}+{other._name}")
         m._keep = (self, other, getattr(self, "_keep", None))
+        m._layout = self._layout            # the library copies the halo plan of the left operand
         return m
 
     def getDiagonal(self, result=None):

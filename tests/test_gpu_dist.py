@@ -1,0 +1,38 @@
+"""GPU: the row-partitioned (one process per GPU) path against the oracle.  The single-rank
+run of the same script always executes; the 2-rank run needs two visible GPUs."""
+import os
+import subprocess
+import sys
+
+import pytest
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+SCRIPT = os.path.join(ROOT, "tests", "dist_check.py")
+
+
+def _ngpus():
+    out = subprocess.run(["nvidia-smi", "-L"], capture_output=True, text=True)
+    return len([l for l in out.stdout.splitlines() if l.startswith("GPU ")]) if out.returncode == 0 else 0
+
+
+def _run(nproc, port, env_extra=None):
+    env = dict(os.environ)
+    env.update(env_extra or {})
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}",
+           "--master-addr", "127.0.0.1", "--master-port", str(port), SCRIPT]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env)
+    assert r.returncode == 0, r.stdout[-3000:] + "\n" + r.stderr[-3000:]
+    assert "OK" in r.stdout
+
+
+def test_single_rank_script():
+    r = subprocess.run([sys.executable, SCRIPT], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + "\n" + r.stderr[-3000:]
+
+
+@pytest.mark.parametrize("nproc", [2, 4, 8])
+def test_partitioned_run_matches_oracle(nproc):
+    if _ngpus() < nproc:
+        pytest.skip(f"needs {nproc} GPUs")
+    _run(nproc, 29540 + nproc, {"DIST_NELEM": "4,4,4" if nproc < 8 else "4,4,6"})
