@@ -222,15 +222,17 @@ def run_b200(args, rank, world):
         e2e = run_e2e(args, fem, ctx, world, ndof, nvort)
 
     out = {
-        "metric": METRIC, "value": ndof * world / (ms_per_step * 1e-3), "unit": UNIT, "n_gpus": world,
+        "metric": METRIC, "value": ndof / (ms_per_step * 1e-3), "unit": UNIT, "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": f"3-D Taylor-Green vortex, {args.nelem}^3 elements, ngl={args.ngl}, unit box "
                                "(BASELINE.json configs[1]); one RK5BS time step = 7 evalRHS",
                    "dofs": int(ndof), "nodes": int(ndof // 3), "ksp": f"cg+{args.pc}", "ksp_rtol": args.rtol,
                    "dt": args.dt, "rhs_evals_per_step": evals / args.steps,
                    "ksp_iterations_per_step": its / args.steps, "ksp_solves_per_step": solves / args.steps,
-                   "parallelism": "1 GPU" if world == 1 else f"{world} independent replicas (one per GPU)",
+                   "parallelism": "1 GPU" if world == 1 else
+                   f"row partition over {world} GPUs ({'x'.join(str(p) for p in fem.dom._partition.pgrid)} element "
+                   f"blocks), halo exchange + allreduce over NCCL, {ctx.collectives()} collectives so far on rank 0",
                    "l2": "inputs larger than L2 (K = %.2f GB per SpMV)" % (spmv_bytes / 1e9)},
         "roofline": roofline,
         "kernel_time_ms_per_step": {"spmv_K_dot": ms_spmv / args.steps, "cg_update": ms_upd / args.steps,
@@ -270,7 +272,7 @@ def run_e2e(args, fem, ctx, world, ndof, nvort):
     """public-API time step with HOST-resident fields: upload vorticity+velocity from pinned memory,
     ts.step(), read both back."""
     vel = fem.solverKLE.getSolution()
-    h_vort, h_vel = ctx.pinned_empty(nvort), ctx.pinned_empty(ndof)
+    h_vort, h_vel = ctx.pinned_empty(fem.vort.getLocalSize()), ctx.pinned_empty(vel.getLocalSize())
     fem.vort.getArray(out=h_vort)
     vel.getArray(out=h_vel)
     bcb = bc_bytes_per_rhs(fem)
@@ -293,9 +295,10 @@ def run_e2e(args, fem, ctx, world, ndof, nvort):
     ms = ctx.timer_stop()
     ms = max_over_ranks(ms, world)
     evals = (fem.ts.rhs_evals - evals0) / args.steps
-    return {"value": ndof * world / (ms / args.steps * 1e-3), "unit": UNIT, "ms_per_step": ms / args.steps,
-            "h2d_bytes_per_step": int((nvort + ndof) * 8 + evals * bcb),
-            "d2h_bytes_per_step": int((nvort + ndof) * 8)}
+    nloc = h_vort.size + h_vel.size
+    return {"value": ndof / (ms / args.steps * 1e-3), "unit": UNIT, "ms_per_step": ms / args.steps,
+            "h2d_bytes_per_step": int(nloc * 8 + evals * bcb),
+            "d2h_bytes_per_step": int(nloc * 8), "bytes_are": "per rank (rank 0)" if world > 1 else "total"}
 
 
 def read_traffic():
@@ -347,7 +350,7 @@ def run_reference(args, rank, world):
     v, ms, sample = cpu_timestep(args, steps, warmup)
     return {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": f"3-D Taylor-Green vortex, {args.nelem}^3 elements, ngl={args.ngl}, unit box "
                                    "(BASELINE.json configs[1]); one RK5BS time step = 7 evalRHS",
                        "note": "petsc4py/PETSc/mpirun are not installed: the reference's own modules cannot be "
@@ -358,39 +361,28 @@ def run_reference(args, rank, world):
 
 
 # ---------------------------------------------------------------------------------------------
-_DIST = None
-
-
 def init_dist():
+    """rank / world size from the torchrun environment; the rendezvous itself (gloo on 127.0.0.1,
+    used once to ship the NCCL id) happens in pynama_b200.petsc.Context"""
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
-    global _DIST
-    if world > 1:
-        import torch
-        import torch.distributed as dist
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        use_cuda = torch.cuda.is_available()
-        if use_cuda:
-            torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", "0")))
-        dist.init_process_group("nccl" if use_cuda else "gloo")
-        _DIST = (dist, torch, use_cuda)
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
     return rank, world
 
 
 def barrier(world):
-    if world > 1 and _DIST:
-        dist, torch, use_cuda = _DIST
-        dist.barrier()
-        if use_cuda:
-            torch.cuda.synchronize()
+    if world > 1:
+        from pynama_b200.petsc import Context
+        ctx = Context.get()
+        ctx.sync()
+        ctx.allreduce([0.0], "sum")          # NCCL allreduce + host read-back: all ranks arrived
+        ctx.sync()
 
 
 def max_over_ranks(x, world):
-    if world > 1 and _DIST:
-        dist, torch, use_cuda = _DIST
-        t = torch.tensor([x], dtype=torch.float64, device="cuda" if use_cuda else "cpu")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
+    if world > 1:
+        from pynama_b200.petsc import Context
+        return float(Context.get().allreduce([x], "max")[0])
     return x
 
 
@@ -406,9 +398,14 @@ def main():
             out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": 1, "kind": "port", "sample": sample}
     if rank == 0 and out is not None:
         print(json.dumps(out), flush=True)
-    if _DIST:
-        _DIST[0].barrier()
-        _DIST[0].destroy_process_group()
+    if world > 1:
+        try:
+            import torch.distributed as dist
+            if dist.is_initialized():
+                dist.barrier()
+                dist.destroy_process_group()
+        except Exception:
+            pass
 
 
 if __name__ == "__main__":
