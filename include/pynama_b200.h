@@ -87,6 +87,18 @@ int pyn_comm_info(pyn_ctx* ctx, int* rank, int* nranks, int* nccl_version, int64
 /* small host-value collective for the drivers: op 0 sum, 1 max; vals[n] in/out, n <= 64 */
 int pyn_comm_allreduce(pyn_ctx* ctx, double* vals, int n, int op);
 int pyn_comm_finalize(pyn_ctx* ctx);
+/* Peer-memory collectives over NVLink/NVSwitch (CUDA IPC): every rank exports a small window,
+ * the host layer gathers the 64-byte handles, every rank maps its peers.  Once attached, the
+ * Krylov inner products are all-reduced INSIDE the SpMV / update kernels (remote stores + flags)
+ * and the halo exchange stores straight into the receiver's window -- no NCCL call per
+ * iteration.  handles: nranks x 64 bytes (comm) / nneigh x 64 bytes in neighbour order (halo);
+ * peer_off[i] / peer_nghost[i]: where this rank's run starts in neighbour i's ghost section and
+ * that neighbour's ghost-node count. */
+int pyn_comm_window_export(pyn_ctx* ctx, void* handle64);
+int pyn_comm_window_attach(pyn_ctx* ctx, const void* handles);
+int pyn_halo_window_export(pyn_halo* h, int max_bs, void* handle64);
+int pyn_halo_window_attach(pyn_halo* h, const void* handles, const int64_t* peer_off, const int64_t* peer_nghost);
+int pyn_comm_p2p_status(pyn_ctx* ctx, int* enabled, int* timed_out);
 /* Node layout of this rank: owned nodes [0, n_own), ghost nodes [n_own, n_loc) grouped by
  * owner.  Per neighbour i: ranks[i]; the owned nodes it needs send_nodes[send_ptr[i]:
  * send_ptr[i+1]] (local ids); the run of the ghost section it fills, recv_off[i] (nodes past
@@ -221,6 +233,10 @@ int pyn_vec_device_ptr(pyn_vec* v, void** ptr);
 #define PYN_PC_BJACOBI 2 /* node-block (br x br) Jacobi */
 int pyn_ksp_create(pyn_ctx* ctx, pyn_mat* a, int type, int pc, pyn_ksp** out);
 int pyn_ksp_set_tolerances(pyn_ksp* k, double rtol, double atol, int maxit, int restart);
+/* KSPSetUseFischerGuess / -ksp_fischer_guess <model>,<size>: model 1 (A-conjugate projection
+ * of the new right-hand side on the last <size> <= 8 solution increments) forms the initial
+ * guess; size 0 switches it off (default, as in PETSc). */
+int pyn_ksp_set_fischer_guess(pyn_ksp* k, int model, int size);
 /* x: initial guess in, solution out (KSP.__call__(b, x), kle_solver.py:35).
  * reason > 0 converged (2 rtol, 3 atol), < 0 diverged (-3 max iterations). */
 int pyn_ksp_solve(pyn_ksp* k, pyn_vec* b, pyn_vec* x, int* its, int* reason, double* rnorm);

@@ -78,7 +78,7 @@ class OracleProblem:
     """Free-slip Taylor-Green problem on given mesh tables, CPU only."""
 
     def __init__(self, dim, ngl, corner_xyz, elem_nodes, coords, bnd_nodes, rho, mu, solver="direct",
-                 rtol=1e-10, pc="jacobi", reuse=True):
+                 rtol=1e-10, pc="jacobi", reuse=True, fischer=0):
         self.dim, self.dim_w = dim, (1 if dim == 2 else 3)
         self.rho, self.mu, self.nu = rho, mu, mu / rho
         self.coords = np.asarray(coords, dtype=np.float64)
@@ -102,6 +102,8 @@ class OracleProblem:
         self.vort = tg_vorticity(self.coords, a0)
         self.iterations = 0
         self.solves = 0
+        # PETSc -ksp_fischer_guess 1,<fischer>: A-orthonormal basis of solution increments
+        self.fischer, self._fx, self._fax = int(fischer), [], []
 
     def _setup_pc(self):
         n, d = self.K.shape[0], self.dim
@@ -130,10 +132,31 @@ class OracleProblem:
 
             def cb(_):
                 its[0] += 1
+            x0 = self.vel
+            if self.fischer:                 # the guess REPLACES the incoming one (zero for an empty basis)
+                x0 = sum(((fx @ b) * fx for fx in self._fx), np.zeros_like(b))
+            r0 = b - self.K @ x0
             # PETSc's default test is on the preconditioned residual; scipy tests the true
             # residual against rtol*||b|| -- same order for this SPD system.
-            x, info = spl.cg(self.K, b, x0=self.vel, rtol=self.rtol, atol=0.0, maxiter=20000, M=self._M,
+            x, info = spl.cg(self.K, b, x0=x0, rtol=self.rtol, atol=0.0, maxiter=20000, M=self._M,
                              callback=cb)
+            if self.fischer:
+                if len(self._fx) == self.fischer:          # restart with the current solution
+                    self._fx, self._fax = [], []
+                    d, ad = x.copy(), self.K @ x
+                else:
+                    d, ad = x - x0, r0 - (b - self.K @ x)
+                a0 = d @ ad
+                for fx, fax in zip(self._fx, self._fax):
+                    c = fx @ ad
+                    d = d - c * fx
+                    ad = ad - c * fax
+                a = d @ ad
+                # keep the direction only if it is well above the solver's noise floor
+                tol = max(100.0 * self.rtol, 1e-12)
+                if a > 0 and a0 > 0 and a > tol * tol * abs(x @ (self.K @ x)):
+                    self._fx.append(d / np.sqrt(a))
+                    self._fax.append(ad / np.sqrt(a))
             self.vel = x
             self.iterations += its[0]
         self.solves += 1

@@ -55,6 +55,11 @@ _PROTOS = {
     "pyn_comm_info": [vp, P(c_int), P(c_int), P(c_int), P(c_i64)],
     "pyn_comm_allreduce": [vp, vp, c_int, c_int],
     "pyn_comm_finalize": [vp],
+    "pyn_comm_window_export": [vp, vp],
+    "pyn_comm_window_attach": [vp, vp],
+    "pyn_halo_window_export": [vp, c_int, vp],
+    "pyn_halo_window_attach": [vp, vp, vp, vp],
+    "pyn_comm_p2p_status": [vp, P(c_int), P(c_int)],
     "pyn_halo_create": [vp, c_i64, c_i64, c_int, vp, vp, vp, vp, vp, P(vp)],
     "pyn_halo_destroy": [vp],
     "pyn_halo_exchange": [vp, vp, c_int],
@@ -107,6 +112,7 @@ _PROTOS = {
     "pyn_vec_device_ptr": [vp, P(vp)],
     "pyn_ksp_create": [vp, vp, c_int, c_int, P(vp)],
     "pyn_ksp_set_tolerances": [vp, c_dbl, c_dbl, c_int, c_int],
+    "pyn_ksp_set_fischer_guess": [vp, c_int, c_int],
     "pyn_ksp_solve": [vp, vp, vp, P(c_int), P(c_int), P(c_dbl)],
     "pyn_ksp_destroy": [vp],
     "pyn_vtensv": [vp, vp, c_int],

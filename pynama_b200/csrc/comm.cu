@@ -87,9 +87,108 @@ __global__ void halo_pack_kernel(const double* __restrict__ v, const int32_t* __
   }
 }
 
+// ---- peer-memory halo: senders store straight into the receiver's window -------------------
+constexpr int kHaloHdr = 256;   // bytes: flag[2][kMaxRanks] u64, padded
+__device__ __forceinline__ unsigned long long* halo_flag(unsigned char* win, int par, int src) {
+  return reinterpret_cast<unsigned long long*>(win) + par * kMaxRanks + src;
+}
+__device__ __forceinline__ double* halo_buf(unsigned char* win, int par, int64_t nghost, int max_bs) {
+  return reinterpret_cast<double*>(win + kHaloHdr) + (int64_t)par * nghost * max_bs;
+}
+
+__global__ void halo_push_kernel(const double* __restrict__ v, const int32_t* __restrict__ send_nodes,
+                                 const int64_t* __restrict__ send_ptr, int nneigh,
+                                 const unsigned long long* __restrict__ peer_win,
+                                 const int64_t* __restrict__ peer_off, const int64_t* __restrict__ peer_nghost,
+                                 int bs, int max_bs, int my_rank, unsigned long long seq, unsigned int* ticket) {
+  const int par = (int)(seq & 1ull);
+  const int64_t nsend = send_ptr[nneigh];
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nsend * bs;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t k = i / bs;
+    const int c = (int)(i - k * bs);
+    int nb = 0;
+    while (k >= send_ptr[nb + 1]) ++nb;                    // <= 26 neighbours
+    double* dst = halo_buf(reinterpret_cast<unsigned char*>(peer_win[nb]), par, peer_nghost[nb], max_bs);
+    dst[(peer_off[nb] + (k - send_ptr[nb])) * bs + c] = v[(int64_t)send_nodes[k] * bs + c];
+  }
+  // all stores of this CTA visible system-wide, then the last CTA releases the flags
+  __threadfence_system();
+  __shared__ bool is_last;
+  __syncthreads();
+  if (threadIdx.x == 0) is_last = (atomicAdd(ticket, 1u) == gridDim.x - 1);
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence_system();
+  if (threadIdx.x < nneigh)
+    st_release_sys(halo_flag(reinterpret_cast<unsigned char*>(peer_win[threadIdx.x]), par, my_rank), seq);
+  if (threadIdx.x == 0) *ticket = 0u;
+}
+
+// CTAs [i*cpn, (i+1)*cpn) wait for neighbour i's flag, then copy its run into the ghost section
+__global__ void halo_wait_kernel(double* __restrict__ v, unsigned char* win, int64_t n_own, int64_t nghost,
+                                 const int32_t* __restrict__ ranks, const int64_t* __restrict__ recv_off,
+                                 const int64_t* __restrict__ recv_cnt, int cpn, int bs, int max_bs,
+                                 unsigned long long seq, int* timeout_flag) {
+  const int par = (int)(seq & 1ull);
+  const int nb = blockIdx.x / cpn, sub = blockIdx.x % cpn;
+  __shared__ bool ok;
+  if (threadIdx.x == 0) {
+    long long spins = 0;
+    ok = true;
+    while (ld_acquire_sys(halo_flag(win, par, ranks[nb])) < seq)
+      if (++spins > kSpinMax) {
+        ok = false;
+        *timeout_flag = 1;
+        break;
+      }
+  }
+  __syncthreads();
+  if (!ok) return;
+  const double* src = halo_buf(win, par, nghost, max_bs) + recv_off[nb] * bs;
+  double* dst = v + (n_own + recv_off[nb]) * bs;
+  const int64_t n = recv_cnt[nb] * bs;
+  for (int64_t i = (int64_t)sub * blockDim.x + threadIdx.x; i < n; i += (int64_t)cpn * blockDim.x)
+    dst[i] = __ldcv(src + i);
+}
+
+static int halo_exchange_p2p(pyn_halo* h, double* v, int bs) {
+  pyn_ctx* ctx = h->ctx;
+  PYN_REQUIRE(bs <= h->max_bs, "halo_exchange: block size %d exceeds the window (%d)", bs, h->max_bs);
+  const unsigned long long seq = ++h->seq;
+  const int64_t nsend = h->send_ptr[h->nneigh];
+  const int gridp = grid_for(ctx, nsend * bs > 0 ? nsend * bs : 1, 256);
+  halo_push_kernel<<<gridp, 256, 0, ctx->stream>>>(v, h->send_nodes.p, h->d_send_ptr.p, h->nneigh, h->d_peer_win.p,
+                                                   h->d_peer_off.p, h->d_peer_nghost.p, bs, h->max_bs, ctx->rank,
+                                                   seq, ctx->red_ticket);
+  PYN_LAUNCHED(ctx);
+  const int cpn = 4;
+  halo_wait_kernel<<<h->nneigh * cpn, 256, 0, ctx->stream>>>(v, h->win, h->n_own, h->n_loc - h->n_own, h->d_ranks.p,
+                                                             h->d_recv_off.p, h->d_recv_cnt.p, cpn, bs, h->max_bs,
+                                                             seq, ctx->p2p_timeout);
+  PYN_LAUNCHED(ctx);
+  ctx->collectives++;
+  return PYN_OK;
+}
+
+P2PRed p2p_next(pyn_ctx* ctx) {
+  P2PRed c;
+  memset(&c, 0, sizeof(c));
+  c.rank = ctx->rank;
+  c.nranks = 1;
+  if (!ctx->p2p_on) return c;
+  c.nranks = ctx->nranks;
+  for (int t = 0; t < ctx->nranks; ++t) c.win[t] = reinterpret_cast<RedWindow*>(ctx->red_peer[t]);
+  c.seq = ++ctx->p2p_seq;
+  ctx->collectives++;
+  return c;
+}
+bool p2p_enabled(const pyn_ctx* ctx) { return ctx->p2p_on && ctx->nranks > 1; }
+
 int halo_exchange(pyn_halo* h, double* v, int bs) {
   pyn_ctx* ctx = h->ctx;
   if (ctx->nranks <= 1 || h->nneigh == 0) return PYN_OK;
+  if (h->p2p) return halo_exchange_p2p(h, v, bs);
   const int64_t nsend = h->send_ptr[h->nneigh];
   if (h->sendbuf_bs < bs) {
     PYN_CHECK(h->sendbuf.alloc(ctx, nsend * bs > 0 ? nsend * bs : 1));
@@ -118,6 +217,12 @@ int halo_exchange(pyn_halo* h, double* v, int bs) {
 }  // namespace pyn
 
 using namespace pyn;
+
+pyn_halo::~pyn_halo() {
+  for (unsigned char* p : peer_win)
+    if (p) cudaIpcCloseMemHandle(p);
+  if (win) cudaFree(win);
+}
 
 extern "C" {
 
@@ -187,6 +292,12 @@ int pyn_comm_allreduce(pyn_ctx* ctx, double* vals, int n, int op) {
 }
 
 int pyn_comm_finalize(pyn_ctx* ctx) {
+  if (ctx && ctx->p2p_on) {
+    cudaStreamSynchronize(ctx->stream);
+    for (int t = 0; t < ctx->nranks; ++t)
+      if (t != ctx->rank && ctx->red_peer[t]) cudaIpcCloseMemHandle(ctx->red_peer[t]);
+    ctx->p2p_on = false;
+  }
   if (ctx && ctx->nccl_comm && g_nccl.lib) {
     cudaStreamSynchronize(ctx->stream);
     g_nccl.CommDestroy((nccl_comm_t)ctx->nccl_comm);
@@ -240,6 +351,107 @@ int pyn_halo_create(pyn_ctx* ctx, int64_t n_own, int64_t n_loc, int nneigh, cons
 
 int pyn_halo_destroy(pyn_halo* h) {
   delete h;
+  return PYN_OK;
+}
+
+// ---- peer windows (CUDA IPC) ---------------------------------------------------------------
+int pyn_comm_window_export(pyn_ctx* ctx, void* handle64) {
+  PYN_REQUIRE(ctx && handle64, "pyn_comm_window_export: null argument");
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+  if (!ctx->red_win) {
+    PYN_CUDA(cudaMalloc(&ctx->red_win, sizeof(RedWindow)));
+    PYN_CUDA(cudaMemset(ctx->red_win, 0, sizeof(RedWindow)));
+    PYN_CUDA(cudaMalloc((void**)&ctx->p2p_timeout, sizeof(int)));
+    PYN_CUDA(cudaMemset(ctx->p2p_timeout, 0, sizeof(int)));
+    PYN_CUDA(cudaDeviceSynchronize());
+  }
+  cudaIpcMemHandle_t hdl;
+  PYN_CUDA(cudaIpcGetMemHandle(&hdl, ctx->red_win));
+  memcpy(handle64, &hdl, 64);
+  return PYN_OK;
+}
+
+int pyn_comm_window_attach(pyn_ctx* ctx, const void* handles) {
+  PYN_REQUIRE(ctx && handles && ctx->red_win, "pyn_comm_window_attach: export first");
+  PYN_REQUIRE(ctx->nranks <= kMaxRanks, "peer-memory collectives support up to %d ranks", kMaxRanks);
+  for (int t = 0; t < ctx->nranks; ++t) {
+    if (t == ctx->rank) {
+      ctx->red_peer[t] = ctx->red_win;
+      continue;
+    }
+    cudaIpcMemHandle_t hdl;
+    memcpy(&hdl, (const char*)handles + 64 * t, 64);
+    PYN_CUDA(cudaIpcOpenMemHandle(&ctx->red_peer[t], hdl, cudaIpcMemLazyEnablePeerAccess));
+  }
+  ctx->p2p_on = true;
+  return PYN_OK;
+}
+
+int pyn_halo_window_export(pyn_halo* h, int max_bs, void* handle64) {
+  PYN_REQUIRE(h && handle64 && max_bs > 0, "pyn_halo_window_export: bad argument");
+  if (!h->win) {
+    const int64_t nghost = h->n_loc - h->n_own;
+    const size_t bytes = kHaloHdr + (size_t)2 * (nghost > 0 ? nghost : 1) * max_bs * 8;
+    PYN_CUDA(cudaMalloc((void**)&h->win, bytes));
+    PYN_CUDA(cudaMemset(h->win, 0, bytes));
+    PYN_CUDA(cudaDeviceSynchronize());
+    h->max_bs = max_bs;
+    h->ctx->bytes_in_use += (int64_t)bytes;
+  }
+  cudaIpcMemHandle_t hdl;
+  PYN_CUDA(cudaIpcGetMemHandle(&hdl, h->win));
+  memcpy(handle64, &hdl, 64);
+  return PYN_OK;
+}
+
+int pyn_halo_window_attach(pyn_halo* h, const void* handles, const int64_t* peer_off, const int64_t* peer_nghost) {
+  PYN_REQUIRE(h && h->win && (h->nneigh == 0 || (handles && peer_off && peer_nghost)),
+              "pyn_halo_window_attach: export first");
+  PYN_REQUIRE(h->ctx->p2p_on, "pyn_halo_window_attach: the context's reduction windows are not attached");
+  PYN_REQUIRE(h->nneigh <= 256, "too many neighbours");
+  pyn_ctx* ctx = h->ctx;
+  std::vector<unsigned long long> addr(h->nneigh > 0 ? h->nneigh : 1, 0ull);
+  std::vector<int32_t> ranks(h->ranks.begin(), h->ranks.end());
+  for (int i = 0; i < h->nneigh; ++i) {
+    cudaIpcMemHandle_t hdl;
+    memcpy(&hdl, (const char*)handles + 64 * i, 64);
+    void* p = nullptr;
+    PYN_CUDA(cudaIpcOpenMemHandle(&p, hdl, cudaIpcMemLazyEnablePeerAccess));
+    h->peer_win.push_back((unsigned char*)p);
+    h->peer_off.push_back(peer_off[i]);
+    h->peer_nghost.push_back(peer_nghost[i]);
+    addr[i] = (unsigned long long)p;
+  }
+  const int n1 = h->nneigh > 0 ? h->nneigh : 1;
+  PYN_CHECK(h->d_send_ptr.alloc(ctx, h->nneigh + 1));
+  PYN_CHECK(h->d_send_ptr.upload(h->send_ptr.data(), h->nneigh + 1));
+  PYN_CHECK(h->d_peer_off.alloc(ctx, n1));
+  PYN_CHECK(h->d_peer_nghost.alloc(ctx, n1));
+  PYN_CHECK(h->d_recv_off.alloc(ctx, n1));
+  PYN_CHECK(h->d_recv_cnt.alloc(ctx, n1));
+  PYN_CHECK(h->d_ranks.alloc(ctx, n1));
+  PYN_CHECK(h->d_peer_win.alloc(ctx, n1));
+  PYN_CHECK(h->d_peer_off.upload(h->peer_off.data(), h->nneigh));
+  PYN_CHECK(h->d_peer_nghost.upload(h->peer_nghost.data(), h->nneigh));
+  PYN_CHECK(h->d_recv_off.upload(h->recv_off.data(), h->nneigh));
+  PYN_CHECK(h->d_recv_cnt.upload(h->recv_cnt.data(), h->nneigh));
+  PYN_CHECK(h->d_ranks.upload(ranks.data(), h->nneigh));
+  PYN_CHECK(h->d_peer_win.upload(addr.data(), h->nneigh));
+  PYN_CUDA(cudaStreamSynchronize(ctx->stream));
+  h->p2p = true;
+  return PYN_OK;
+}
+
+int pyn_comm_p2p_status(pyn_ctx* ctx, int* enabled, int* timed_out) {
+  PYN_REQUIRE(ctx, "null ctx");
+  if (enabled) *enabled = ctx->p2p_on ? 1 : 0;
+  if (timed_out) {
+    *timed_out = 0;
+    if (ctx->p2p_timeout) {
+      PYN_CUDA(cudaMemcpyAsync(timed_out, ctx->p2p_timeout, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+      PYN_CUDA(cudaStreamSynchronize(ctx->stream));
+    }
+  }
   return PYN_OK;
 }
 

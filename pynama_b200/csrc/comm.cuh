@@ -8,6 +8,112 @@
 #pragma once
 #include "common.cuh"
 
+namespace pyn {
+constexpr int kMaxRanks = 8;            // GPUs of one box
+constexpr long long kSpinMax = 40000000LL;   // bounded spin (~ seconds): a lost peer must not hang the GPU
+
+// ---- peer-memory collectives (NVLink/NVSwitch, CUDA IPC) -----------------------------------
+// Every rank owns a small "window" in its HBM that all peers map.  A reduction is: the last
+// CTA of the producing kernel stores this rank's partial into EVERY peer's window (remote
+// stores over NVLink), fences, then releases a sequence-numbered flag; consumers spin on the
+// flags in their OWN memory and add the partials in rank order, so every rank gets the same
+// bits.  Slots are double-buffered by sequence parity.  No NCCL call, no extra launch: the
+// collective rides inside the compute kernels.
+struct RedWindow {                      // device layout of one rank's reduction window
+  double val[2][2][kMaxRanks][2];       // [kind][parity][source rank][value]
+  unsigned long long flag[2][2][kMaxRanks];
+};
+struct P2PRed {                         // by-value kernel argument
+  RedWindow* win[kMaxRanks];            // win[t] = rank t's window (win[rank] = own)
+  int rank, nranks;                     // nranks <= 1: disabled
+  unsigned long long seq;               // sequence number of this collective (> 0)
+};
+
+#ifdef __CUDACC__
+__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+// Called by ONE warp.  Lane t < nranks stores this rank's NV partials into rank t's window
+// and releases the flag.
+template <int NV>
+__device__ __forceinline__ void p2p_push(const P2PRed& c, int kind, const double* v) {
+  const int lane = threadIdx.x & 31;
+  const int par = (int)(c.seq & 1ull);
+  if (lane < c.nranks) {
+    RedWindow* w = c.win[lane];
+#pragma unroll
+    for (int k = 0; k < NV; ++k) w->val[kind][par][c.rank][k] = v[k];
+    __threadfence_system();
+    st_release_sys(&w->flag[kind][par][c.rank], c.seq);
+  }
+}
+// Called by ONE warp.  Waits for every rank's partial of collective c.seq and returns the
+// sums (rank order) in out[0..NV) on all lanes; returns false on spin timeout.
+template <int NV>
+__device__ __forceinline__ bool p2p_wait_sum(const P2PRed& c, int kind, double* out) {
+  const int lane = threadIdx.x & 31;
+  const int par = (int)(c.seq & 1ull);
+  RedWindow* w = c.win[c.rank];
+  bool ok = true;
+  if (lane < c.nranks) {
+    long long spins = 0;
+    while (ld_acquire_sys(&w->flag[kind][par][lane]) < c.seq)
+      if (++spins > kSpinMax) {
+        ok = false;
+        break;
+      }
+  }
+  ok = __all_sync(0xffffffffu, ok);
+#pragma unroll
+  for (int k = 0; k < NV; ++k) {
+    double s = 0.0;
+    for (int r = 0; r < c.nranks; ++r) s += __ldcv(&w->val[kind][par][r][k]);
+    out[k] = s;
+  }
+  return ok;
+}
+// Grid reduction whose result goes to every rank: CTAs deposit NV partials, the last CTA to
+// arrive folds them in block order and pushes this rank's totals into all peers' windows.
+// v[] must hold the CTA totals in warp 0 (after block_reduce); call with all threads.
+template <int NV>
+__device__ __forceinline__ void grid_reduce_push(double (&v)[NV], double* partials, unsigned int* ticket,
+                                                 const P2PRed& red, int kind) {
+  __shared__ bool is_last_p;
+  __shared__ double tot_p[NV];
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int k = 0; k < NV; ++k) partials[(size_t)blockIdx.x * NV + k] = v[k];
+    __threadfence();
+    is_last_p = (atomicAdd(ticket, 1u) == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!is_last_p) return;
+  __threadfence();
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  if (wid < NV) {
+    double t = 0.0;
+    for (unsigned int b = lane; b < gridDim.x; b += 32) t += partials[(size_t)b * NV + wid];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+    if (lane == 0) tot_p[wid] = t;
+  }
+  __syncthreads();
+  if (wid == 0) {
+    double t[NV];
+#pragma unroll
+    for (int k = 0; k < NV; ++k) t[k] = tot_p[k];
+    p2p_push<NV>(red, kind, t);
+  }
+  if (threadIdx.x == 0) *ticket = 0u;
+}
+#endif
+}  // namespace pyn
+
 struct pyn_halo {
   pyn_ctx* ctx = nullptr;
   int64_t n_own = 0, n_loc = 0;          // nodes
@@ -18,6 +124,19 @@ struct pyn_halo {
   pyn::DevBuf<int32_t> send_nodes;       // local ids of owned nodes, grouped by neighbour
   pyn::DevBuf<double> sendbuf;           // [total_send * bs], grown on demand
   int64_t sendbuf_bs = 0;
+  // peer-memory path: this rank's receive window (flags + 2 x n_ghost*max_bs doubles) and the
+  // neighbours' windows mapped through CUDA IPC; senders store straight into the receiver
+  bool p2p = false;
+  int max_bs = 0;
+  unsigned char* win = nullptr;                 // own window
+  std::vector<unsigned char*> peer_win;         // [nneigh]
+  std::vector<int64_t> peer_off;                // [nneigh] my run's node offset in neighbour i's ghost section
+  std::vector<int64_t> peer_nghost;             // [nneigh] neighbour i's ghost count (window stride)
+  pyn::DevBuf<int64_t> d_send_ptr, d_peer_off, d_peer_nghost, d_recv_off, d_recv_cnt;
+  pyn::DevBuf<int32_t> d_ranks;
+  pyn::DevBuf<unsigned long long> d_peer_win;   // device array of the neighbours' window addresses
+  unsigned long long seq = 0;
+  ~pyn_halo();
 };
 
 namespace pyn {
@@ -25,4 +144,8 @@ namespace pyn {
 int comm_allreduce_sum(pyn_ctx* ctx, double* dev, int n);
 // ghost entries of v (n_loc*bs doubles) <- owners' values
 int halo_exchange(pyn_halo* h, double* v, int bs);
+// reduction descriptor for the next fused collective (advances the sequence); disabled
+// (nranks = 1) unless the peer windows are attached
+P2PRed p2p_next(pyn_ctx* ctx);
+bool p2p_enabled(const pyn_ctx* ctx);
 }  // namespace pyn

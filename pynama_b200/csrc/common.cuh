@@ -76,6 +76,12 @@ struct pyn_ctx {
   int rank = 0, nranks = 1;
   void* nccl_comm = nullptr;
   int64_t collectives = 0;
+  // peer-memory reduction windows (comm.cuh): own + peers' (CUDA IPC), sequence counter
+  void* red_win = nullptr;
+  void* red_peer[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  bool p2p_on = false;
+  unsigned long long p2p_seq = 0;
+  int* p2p_timeout = nullptr;         // device flag: a bounded spin on a peer flag ran out
   // per-kernel-class CUDA-event profiler (bench.py's live roofline timing)
   bool prof_on = false;
   std::vector<cudaEvent_t> prof_ev;     // pairs (begin, end)

@@ -116,12 +116,35 @@ __global__ void __launch_bounds__(256)
 cg_update_kernel(int pc, const double* __restrict__ pcd, const double* __restrict__ p,
                  const double* __restrict__ w, double* __restrict__ x, double* __restrict__ r,
                  double* __restrict__ z, int64_t nnodes, double* S, int parity, int maxit,
-                 double* partials, unsigned int* ticket, int dist) {
+                 double* partials, unsigned int* ticket, int dist, P2PRed red) {
   __shared__ double sm[64];
   __shared__ bool is_last;
+  __shared__ double s_pw;
+  __shared__ int s_ok;
   if (S[S_DONE] != 0.0) return;
   const double rz = S[parity ? S_RZ1 : S_RZ0];
-  const double pw = S[S_PW];
+  double pw;
+  if (red.nranks > 1) {                    // p.Ap partials of all ranks arrive in this rank's window
+    if (threadIdx.x < 32) {
+      double o[1];
+      const bool ok = p2p_wait_sum<1>(red, 0, o);
+      if (threadIdx.x == 0) {
+        s_pw = o[0];
+        s_ok = ok ? 1 : 0;
+      }
+    }
+    __syncthreads();
+    pw = s_pw;
+    if (!s_ok) {
+      if (threadIdx.x == 0 && blockIdx.x == 0) {
+        S[S_REASON] = -100.0;              // a peer never answered
+        S[S_DONE] = 1.0;
+      }
+      return;
+    }
+  } else {
+    pw = S[S_PW];
+  }
   const double alpha = rz / pw;
   double v[2] = {0.0, 0.0};
   for (int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; n < nnodes;
@@ -161,6 +184,24 @@ cg_update_kernel(int pc, const double* __restrict__ pcd, const double* __restric
     if (lane == 0) sm[wid] = t;
   }
   __syncthreads();
+  if (red.nranks > 1) {            // fused allreduce over peer memory, then the bookkeeping
+    if (threadIdx.x < 32) {
+      double t[2] = {sm[0], sm[1]}, g[2];
+      p2p_push<2>(red, 1, t);
+      const bool ok = p2p_wait_sum<2>(red, 1, g);
+      if (threadIdx.x == 0) {
+        *ticket = 0u;
+        S[S_PW] = pw;
+        if (ok) {
+          cg_bookkeeping(S, g[0], g[1], parity, maxit);
+        } else {
+          S[S_REASON] = -100.0;
+          S[S_DONE] = 1.0;
+        }
+      }
+    }
+    return;
+  }
   if (threadIdx.x == 0) {
     *ticket = 0u;
     if (dist) {                    // partial sums of this rank; allreduce + cg_scalars_kernel follow
@@ -259,6 +300,79 @@ __global__ void pc_setup_kernel(int pc, const double* __restrict__ dblk, double*
   }
 }
 
+// ---- Fischer initial guess (KSPSetUseFischerGuess model 1: A-conjugate projection) ---------
+// PETSc option -ksp_fischer_guess 1,<size>.  The last <size> solution increments are kept
+// A-orthonormal (x~_i, A x~_i); the guess for a new right-hand side b is sum_i (x~_i . b) x~_i,
+// the A-norm-optimal element of their span.  Successive KLE systems differ only through
+// time-dependent boundary values and the slowly changing vorticity, so most of the solution is
+// recovered before the first Krylov iteration.
+constexpr int kFischerMax = 8;
+struct BasisPtrs {
+  const double* v[kFischerMax];
+  int k;
+};
+
+// out[i] = basis_i . y, i < k (one pass over y and the k basis vectors)
+__global__ void __launch_bounds__(256)
+multi_dot_kernel(BasisPtrs b, const double* __restrict__ y, int64_t n, double* partials,
+                 unsigned int* ticket, double* out) {
+  __shared__ double sm[kFischerMax * 32];
+  double v[kFischerMax];
+#pragma unroll
+  for (int i = 0; i < kFischerMax; ++i) v[i] = 0.0;
+  for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < n; j += (int64_t)gridDim.x * blockDim.x) {
+    const double yj = y[j];
+#pragma unroll
+    for (int i = 0; i < kFischerMax; ++i)
+      if (i < b.k) v[i] += b.v[i][j] * yj;
+  }
+  block_reduce<kFischerMax>(v, sm);
+  grid_reduce_finish<kFischerMax>(v, partials, ticket, out);
+}
+
+// y = (keep ? y : 0) + sign * sum_i coef[i] * basis_i
+__global__ void lincomb_kernel(double* __restrict__ y, BasisPtrs b, const double* __restrict__ coef, double sign,
+                               int keep, int64_t n) {
+  double c[kFischerMax];
+#pragma unroll
+  for (int i = 0; i < kFischerMax; ++i) c[i] = i < b.k ? sign * coef[i] : 0.0;
+  for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < n; j += (int64_t)gridDim.x * blockDim.x) {
+    double s = keep ? y[j] : 0.0;
+#pragma unroll
+    for (int i = 0; i < kFischerMax; ++i)
+      if (i < b.k) s += c[i] * b.v[i][j];
+    y[j] = s;
+  }
+}
+
+// d = x - x0 ; ad = r0 - r      (A d = A x - A x0 = (b - r) - (b - r0))
+__global__ void fischer_delta_kernel(const double* __restrict__ x, const double* __restrict__ x0,
+                                     const double* __restrict__ r0, const double* __restrict__ r,
+                                     double* __restrict__ d, double* __restrict__ ad, int64_t n) {
+  for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < n; j += (int64_t)gridDim.x * blockDim.x) {
+    d[j] = x[j] - x0[j];
+    ad[j] = r0[j] - r[j];
+  }
+}
+
+// nrm2[0] = d.Ad after the orthogonalisation, nrm2[1] = d.Ad before it, nrm2[2] = x.b ~ x.Ax.
+// Keep the new direction only if its A-norm is well above the solver's noise floor (tol
+// relative to the solution's A-norm): a direction made of round-off would be scaled up to unit
+// norm and poison every later guess.  Scale to unit A-norm.
+__global__ void fischer_append_kernel(const double* __restrict__ d, const double* __restrict__ ad,
+                                      const double* __restrict__ nrm2, double tol2, double* __restrict__ bx,
+                                      double* __restrict__ bax, int64_t n, double* accepted) {
+  const double a = nrm2[0], a0 = nrm2[1];
+  const bool ok = a > 0.0 && a0 > 0.0 && a > tol2 * fabs(nrm2[2]) && a == a;
+  if (blockIdx.x == 0 && threadIdx.x == 0) *accepted = ok ? 1.0 : 0.0;
+  if (!ok) return;
+  const double s = 1.0 / sqrt(a);
+  for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < n; j += (int64_t)gridDim.x * blockDim.x) {
+    bx[j] = s * d[j];
+    bax[j] = s * ad[j];
+  }
+}
+
 }  // namespace pyn
 
 using namespace pyn;
@@ -276,6 +390,11 @@ struct pyn_ksp {
   double* status_host = nullptr;  // pinned [2][S_COUNT]
   cudaEvent_t ev[2] = {nullptr, nullptr};
   bool pc_ready = false;
+  // Fischer guess: basis of <= fischer_m A-orthonormal increments and their images
+  int fischer_m = 0, fischer_n = 0;
+  DevBuf<double> fx[kFischerMax], fax[kFischerMax];
+  DevBuf<double> x0, r0, fd, fad, fcoef;     // fcoef: [kFischerMax + 4]
+  int64_t fischer_used = 0, fischer_restarts = 0;
 };
 
 template <int B>
@@ -300,18 +419,42 @@ template <int B>
 static int ksp_solve_cg(pyn_ksp* k, const double* b, double* x, int* its, int* reason, double* rnorm) {
   pyn_ctx* ctx = k->ctx;
   const int dist = k->A->halo != nullptr && ctx->nranks > 1;
+  const bool p2p = dist && p2p_enabled(ctx);     // fused peer-memory allreduce instead of NCCL
+  P2PRed red_off;
+  memset(&red_off, 0, sizeof(red_off));
+  red_off.nranks = 1;
   // row-partitioned: Krylov vectors hold owned + ghost entries, the kernels touch the owned ones
   const int64_t nn = k->A->halo ? k->A->halo->n_own : k->nnodes;
   const int64_t n = nn * B;
   double* S = k->S.p;
   const int gridn = grid_for(ctx, nn > 0 ? nn : 1, 256);
   if (!k->pc_ready) PYN_CHECK(ksp_setup_pc<B>(k));
+  const bool fischer = k->fischer_m > 0;
+  const int gridv = grid_for(ctx, n > 0 ? n : 1, 256);
+  if (fischer && k->fischer_n > 0) {        // x <- sum_i (x~_i . b) x~_i
+    BasisPtrs bp;
+    bp.k = k->fischer_n;
+    for (int i = 0; i < bp.k; ++i) bp.v[i] = k->fx[i].p;
+    multi_dot_kernel<<<gridv, 256, 0, ctx->stream>>>(bp, b, n, ctx->red_partials, ctx->red_ticket, k->fcoef.p);
+    PYN_LAUNCHED(ctx);
+    if (dist) PYN_CHECK(comm_allreduce_sum(ctx, k->fcoef.p, kFischerMax));
+    lincomb_kernel<<<gridv, 256, 0, ctx->stream>>>(x, bp, k->fcoef.p, 1.0, 0, n);
+    PYN_LAUNCHED(ctx);
+    k->fischer_used++;
+  } else if (fischer) {
+    // empty basis: start from zero so that the increments span the solutions themselves
+    PYN_CHECK(vec_set(ctx, x, n, 0.0));
+  }
   // ||M^-1 b|| for the threshold (KSPConvergedDefault with the preconditioned norm)
   pc_apply_dots_kernel<B><<<gridn, 256, 0, ctx->stream>>>(k->pc, k->pcd.p, b, k->z.p, nn, ctx->red_partials,
                                                           ctx->red_ticket, k->tmp2.p + 2);
   PYN_LAUNCHED(ctx);
   // r = b - A x ; z = M^-1 r ; p = z
   PYN_CHECK(spmv(k->A, -1.0, x, 1.0, b, k->r.p));
+  if (fischer) {                            // keep the guess and its residual for the basis update
+    PYN_CUDA(cudaMemcpyAsync(k->x0.p, x, sizeof(double) * n, cudaMemcpyDeviceToDevice, ctx->stream));
+    PYN_CUDA(cudaMemcpyAsync(k->r0.p, k->r.p, sizeof(double) * n, cudaMemcpyDeviceToDevice, ctx->stream));
+  }
   pc_apply_dots_kernel<B><<<gridn, 256, 0, ctx->stream>>>(k->pc, k->pcd.p, k->r.p, k->z.p, nn,
                                                           ctx->red_partials, ctx->red_ticket, k->tmp2.p);
   PYN_LAUNCHED(ctx);
@@ -327,15 +470,16 @@ static int ksp_solve_cg(pyn_ksp* k, const double* b, double* x, int* its, int* r
     const int todo = (k->maxit - it) < k->check_every ? (k->maxit - it) : k->check_every;
     for (int j = 0; j < todo; ++j, ++it) {
       const int parity = it & 1;
-      PYN_CHECK(spmv_dot(k->A, k->p.p, k->w.p, S + S_PW, S + S_DONE));
-      if (dist) PYN_CHECK(comm_allreduce_sum(ctx, S + S_PW, 1));
+      P2PRed red = p2p ? p2p_next(ctx) : red_off;
+      PYN_CHECK(spmv_dot(k->A, k->p.p, k->w.p, S + S_PW, S + S_DONE, &red));
+      if (dist && !p2p) PYN_CHECK(comm_allreduce_sum(ctx, S + S_PW, 1));
       prof_begin(ctx, PROF_CG_UPDATE);
       cg_update_kernel<B><<<gridn, 256, 0, ctx->stream>>>(k->pc, k->pcd.p, k->p.p, k->w.p, x, k->r.p,
                                                           k->z.p, nn, S, parity, k->maxit,
-                                                          ctx->red_partials, ctx->red_ticket, dist);
+                                                          ctx->red_partials, ctx->red_ticket, dist, red);
       prof_end(ctx);
       PYN_LAUNCHED(ctx);
-      if (dist) {
+      if (dist && !p2p) {
         PYN_CHECK(comm_allreduce_sum(ctx, S + S_LRZ, 2));
         cg_scalars_kernel<<<1, 1, 0, ctx->stream>>>(S, parity, k->maxit);
         PYN_LAUNCHED(ctx);
@@ -355,9 +499,50 @@ static int ksp_solve_cg(pyn_ksp* k, const double* b, double* x, int* its, int* r
     }
     if (it >= k->maxit) break;
   }
+  if (fischer) {
+    // d = x - x0, A d = r0 - r; A-orthogonalise against the basis; append (restart when full)
+    fischer_delta_kernel<<<gridv, 256, 0, ctx->stream>>>(x, k->x0.p, k->r0.p, k->r.p, k->fd.p, k->fad.p, n);
+    PYN_LAUNCHED(ctx);
+    if (k->fischer_n == k->fischer_m) {     // restart: keep only the current solution (A x = b - r)
+      k->fischer_n = 0;
+      k->fischer_restarts++;
+      PYN_CUDA(cudaMemcpyAsync(k->fd.p, x, sizeof(double) * n, cudaMemcpyDeviceToDevice, ctx->stream));
+      PYN_CHECK(vec_waxpy(ctx, k->fad.p, -1.0, k->r.p, b, n));
+    }
+    double* nrm2 = k->fcoef.p + kFischerMax;
+    PYN_CHECK(vec_dot_dev(ctx, k->fd.p, k->fad.p, n, nrm2 + 1));
+    if (k->fischer_n > 0) {
+      BasisPtrs bp, bap;
+      bp.k = bap.k = k->fischer_n;
+      for (int i = 0; i < bp.k; ++i) {
+        bp.v[i] = k->fx[i].p;
+        bap.v[i] = k->fax[i].p;
+      }
+      multi_dot_kernel<<<gridv, 256, 0, ctx->stream>>>(bp, k->fad.p, n, ctx->red_partials, ctx->red_ticket,
+                                                       k->fcoef.p);
+      PYN_LAUNCHED(ctx);
+      if (dist) PYN_CHECK(comm_allreduce_sum(ctx, k->fcoef.p, kFischerMax));
+      lincomb_kernel<<<gridv, 256, 0, ctx->stream>>>(k->fd.p, bp, k->fcoef.p, -1.0, 1, n);
+      PYN_LAUNCHED(ctx);
+      lincomb_kernel<<<gridv, 256, 0, ctx->stream>>>(k->fad.p, bap, k->fcoef.p, -1.0, 1, n);
+      PYN_LAUNCHED(ctx);
+    }
+    PYN_CHECK(vec_dot_dev(ctx, k->fd.p, k->fad.p, n, nrm2));
+    PYN_CHECK(vec_dot_dev(ctx, x, b, n, nrm2 + 2));
+    if (dist) PYN_CHECK(comm_allreduce_sum(ctx, nrm2, 3));
+    const double ftol = k->rtol * 100.0 > 1e-12 ? k->rtol * 100.0 : 1e-12;
+    fischer_append_kernel<<<gridv, 256, 0, ctx->stream>>>(k->fd.p, k->fad.p, nrm2, ftol * ftol,
+                                                          k->fx[k->fischer_n].p, k->fax[k->fischer_n].p, n,
+                                                          nrm2 + 3);
+    PYN_LAUNCHED(ctx);
+  }
   PYN_CUDA(cudaStreamSynchronize(ctx->stream));
   PYN_CUDA(cudaMemcpyAsync(k->status_host, S, sizeof(double) * S_COUNT, cudaMemcpyDeviceToHost, ctx->stream));
+  if (fischer)
+    PYN_CUDA(cudaMemcpyAsync(k->status_host + S_COUNT, k->fcoef.p + kFischerMax + 3, sizeof(double),
+                             cudaMemcpyDeviceToHost, ctx->stream));
   PYN_CUDA(cudaStreamSynchronize(ctx->stream));
+  if (fischer && k->status_host[S_COUNT] != 0.0) k->fischer_n++;
   const double* st = k->status_host;
   if (its) *its = (int)st[S_ITS];
   if (reason) *reason = st[S_DONE] != 0.0 ? (int)st[S_REASON] : -3;
@@ -412,6 +597,27 @@ int pyn_ksp_set_tolerances(pyn_ksp* k, double rtol, double atol, int maxit, int 
   if (atol >= 0) k->atol = atol;
   if (maxit > 0) k->maxit = maxit;
   if (restart > 0) k->restart = restart;
+  return PYN_OK;
+}
+
+int pyn_ksp_set_fischer_guess(pyn_ksp* k, int model, int size) {
+  PYN_REQUIRE(k, "null ksp");
+  PYN_REQUIRE(size == 0 || model == 1, "KSP Fischer guess: only model 1 (A-conjugate projection) is implemented");
+  PYN_REQUIRE(size >= 0 && size <= kFischerMax, "KSP Fischer guess: size %d (max %d)", size, kFischerMax);
+  pyn_ctx* ctx = k->ctx;
+  k->fischer_m = size;
+  k->fischer_n = 0;
+  if (size == 0) return PYN_OK;
+  for (int i = 0; i < size; ++i) {
+    PYN_CHECK(k->fx[i].alloc(ctx, k->n));
+    PYN_CHECK(k->fax[i].alloc(ctx, k->n));
+  }
+  PYN_CHECK(k->x0.alloc(ctx, k->n));
+  PYN_CHECK(k->r0.alloc(ctx, k->n));
+  PYN_CHECK(k->fd.alloc(ctx, k->n));
+  PYN_CHECK(k->fad.alloc(ctx, k->n));
+  PYN_CHECK(k->fcoef.alloc(ctx, kFischerMax + 4));
+  PYN_CHECK(k->fcoef.zero());
   return PYN_OK;
 }
 

@@ -23,6 +23,7 @@ struct SpmvFuse {
   double* partials;
   unsigned int* ticket;
   double* dot_out;
+  P2PRed red;          // nranks > 1: push the dot partial to every rank's window instead
 };
 
 // Column ids of the next pass (and the extent + first column ids of the group's next row)
@@ -95,7 +96,10 @@ spmv_kernel(int64_t nbrows, const int64_t* __restrict__ rowptr, const int32_t* _
   }
   if (DOT) {
     block_reduce<1>(dotacc, red_sm);
-    grid_reduce_finish<1>(dotacc, fuse.partials, fuse.ticket, fuse.dot_out);
+    if (fuse.red.nranks > 1)
+      grid_reduce_push<1>(dotacc, fuse.partials, fuse.ticket, fuse.red, 0);
+    else
+      grid_reduce_finish<1>(dotacc, fuse.partials, fuse.ticket, fuse.dot_out);
   }
 }
 
@@ -142,14 +146,21 @@ static int spmv_launch(pyn_mat* m, double alpha, const double* x, double beta, c
 }
 
 int spmv(pyn_mat* m, double alpha, const double* x, double beta, const double* z, double* y) {
-  SpmvFuse f = {nullptr, nullptr, nullptr, nullptr};
+  SpmvFuse f;
+  memset(&f, 0, sizeof(f));
   return spmv_launch(m, alpha, x, beta, z, y, false, f);
 }
 
 // y = A x and dot_out = x . y in one pass; no-op when *skip != 0
-int spmv_dot(pyn_mat* m, const double* x, double* y, double* dot_out, const double* skip) {
+int spmv_dot(pyn_mat* m, const double* x, double* y, double* dot_out, const double* skip, const P2PRed* red) {
   pyn_ctx* ctx = m->ctx;
-  SpmvFuse f = {skip, ctx->red_partials, ctx->red_ticket, dot_out};
+  SpmvFuse f;
+  memset(&f, 0, sizeof(f));
+  f.skip = skip;
+  f.partials = ctx->red_partials;
+  f.ticket = ctx->red_ticket;
+  f.dot_out = dot_out;
+  if (red) f.red = *red;
   return spmv_launch(m, 1.0, x, 0.0, nullptr, y, true, f);
 }
 

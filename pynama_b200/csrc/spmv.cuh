@@ -1,11 +1,14 @@
 // spmv.cuh -- SpMV and Mat helpers shared with the KSP.
 #pragma once
 #include "mesh.cuh"
+#include "comm.cuh"
 
 namespace pyn {
 // y = alpha*A*x + beta*z (z may be NULL when beta == 0; z may alias y)
 int spmv(pyn_mat* m, double alpha, const double* x, double beta, const double* z, double* y);
-int spmv_dot(pyn_mat* m, const double* x, double* y, double* dot_out, const double* skip);
+// red != NULL with nranks > 1: the dot partial is pushed to every rank's window (kind 0) instead of dot_out
+int spmv_dot(pyn_mat* m, const double* x, double* y, double* dot_out, const double* skip,
+             const P2PRed* red = nullptr);
 int diag_blocks(pyn_mat* m, double* dblk);   // [nbrows][b][b]
 int scale_rows(pyn_mat* m, const double* l);
 int mat_add_new(pyn_mat* a, pyn_mat* b, pyn_mat** out);

@@ -148,6 +148,18 @@ class Context:
         dist.broadcast_object_list(box, src=0)
         uid = ctypes.create_string_buffer(box[0], 128)
         call("pyn_comm_init", self.handle, libb, self.rank, self.size, uid)
+        # peer-memory windows over NVLink (CUDA IPC): fused in-kernel allreduce / halo stores
+        self.p2p = os.environ.get("PYN_P2P", "1") != "0" and self.size <= 8
+        if self.p2p:
+            h = ctypes.create_string_buffer(64)
+            call("pyn_comm_window_export", self.handle, h)
+            allh = COMM_WORLD.allgather(bytes(h.raw))
+            call("pyn_comm_window_attach", self.handle, ctypes.create_string_buffer(b"".join(allh), 64 * self.size))
+
+    def p2p_status(self):
+        en, to = c_int(), c_int()
+        call("pyn_comm_p2p_status", self.handle, ctypes.byref(en), ctypes.byref(to))
+        return bool(en.value), bool(to.value)
 
     def allreduce(self, values, op="sum"):
         """small host-value collective over the ranks (sum | max)"""
@@ -244,6 +256,22 @@ class Layout:
         self._h = h
         self.neighbors = [int(r) for r in ranks]
         self.halo_nodes = int(send_ptr[-1]), int(recv_cnt.sum())
+        ctx = Context.get()
+        if getattr(ctx, "p2p", False):
+            # every rank exports its receive window; senders store straight into it
+            hb = ctypes.create_string_buffer(64)
+            call("pyn_halo_window_export", h, 6, hb)
+            info = COMM_WORLD.allgather((bytes(hb.raw), [int(r) for r in ranks], [int(o) for o in recv_off],
+                                         int(part.n_ghost)))
+            handles, peer_off, peer_ng = [], [], []
+            for q in self.neighbors:
+                qh, qranks, qoff, qng = info[q]
+                handles.append(qh)
+                peer_off.append(qoff[qranks.index(part.rank)])
+                peer_ng.append(qng)
+            po, pn = np.asarray(peer_off, dtype=np.int64), np.asarray(peer_ng, dtype=np.int64)
+            call("pyn_halo_window_attach", h, ctypes.create_string_buffer(b"".join(handles), 64 * max(len(handles), 1)),
+                 ptr(po), ptr(pn))
 
     def exchange(self, vec):
         call("pyn_halo_exchange", self._h, vec._h, vec._bs)
@@ -765,6 +793,7 @@ class KSP:
         self.rtol, self.atol, self.max_it, self.restart = 1e-5, 1e-50, 10000, 30
         self._its, self._reason, self._rnorm = 0, 0, 0.0
         self._guess_nonzero = True
+        self._fischer = (0, 0)              # (model, size); KSPSetUseFischerGuess, off by default
         self._log = logging.getLogger("KSP")
 
     def create(self, comm=None):
@@ -805,6 +834,11 @@ class KSP:
     def setInitialGuessNonzero(self, flag):
         self._guess_nonzero = bool(flag)
 
+    def setUseFischerGuess(self, model, size):
+        """KSPSetUseFischerGuess: model 1 = A-conjugate projection on the last `size` solutions"""
+        self._fischer = (int(model), int(size))
+        self._drop()
+
     def setFromOptions(self):
         o = Options()
         self._type = o.getString("ksp_type", self._type)
@@ -816,6 +850,10 @@ class KSP:
         g = o.getBool("ksp_initial_guess_nonzero", None)
         if g is not None:
             self._guess_nonzero = g
+        fg = o.getString("ksp_fischer_guess", None)          # -ksp_fischer_guess <model>,<size>
+        if fg:
+            parts = [int(p) for p in str(fg).replace(" ", "").split(",") if p]
+            self._fischer = (parts[0], parts[1] if len(parts) > 1 else 10)
         self._drop()
 
     def _drop(self):
@@ -848,10 +886,12 @@ class KSP:
         self._h = h
         call("pyn_ksp_set_tolerances", h, float(rtol), float(self.atol), int(self.max_it),
              int(self.restart))
+        if self._fischer[1] > 0:
+            call("pyn_ksp_set_fischer_guess", h, self._fischer[0], min(self._fischer[1], 8))
 
     def solve(self, b, x):
         self.setUp()
-        if not self._guess_nonzero:
+        if not self._guess_nonzero and self._fischer[1] == 0:
             x.set(0.0)
         its, reason, rn = c_int(), c_int(), c_dbl()
         call("pyn_ksp_solve", self._h, b._h, x._h, ctypes.byref(its), ctypes.byref(reason),

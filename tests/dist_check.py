@@ -30,6 +30,8 @@ def main():
     for k, v in (("ksp_type", "cg"), ("pc_type", "bjacobi"), ("ksp_rtol", 1e-13), ("ksp_max_it", 20000),
                  ("ts_adapt_type", "none"), ("ts_dt", 1e-3)):
         o.setValue(k, v)
+    if os.environ.get("DIST_FISCHER", "0") != "0":
+        o.setValue("ksp_fischer_guess", "1," + os.environ["DIST_FISCHER"])
     cfg = bench.case_config(nelem[0], ngl)
     cfg["domain"]["box-mesh"]["nelem"] = nelem
     fem = BaseProblem(cfg, case="taylor-green3d")

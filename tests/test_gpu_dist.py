@@ -26,9 +26,18 @@ def _run(nproc, port, env_extra=None):
     assert "OK" in r.stdout
 
 
-def test_single_rank_script():
-    r = subprocess.run([sys.executable, SCRIPT], capture_output=True, text=True, timeout=600)
+@pytest.mark.parametrize("fischer", ["0", "4"])
+def test_single_rank_script(fischer):
+    env = dict(os.environ, DIST_FISCHER=fischer)
+    r = subprocess.run([sys.executable, SCRIPT], capture_output=True, text=True, timeout=600, env=env)
     assert r.returncode == 0, r.stdout[-3000:] + "\n" + r.stderr[-3000:]
+
+
+def test_partitioned_run_nccl_and_fischer():
+    """2 ranks, NCCL collectives instead of the peer-memory windows, Fischer guess on"""
+    if _ngpus() < 2:
+        pytest.skip("needs 2 GPUs")
+    _run(2, 29549, {"PYN_P2P": "0", "DIST_FISCHER": "4"})
 
 
 @pytest.mark.parametrize("nproc", [2, 4, 8])

@@ -195,3 +195,38 @@ def test_kle_solve_3d_vs_oracle():
     ksp.solve(b, x0)
     assert ksp.getConvergedReason() == -3 and ksp.getIterationNumber() == 3
 
+
+
+def test_fischer_guess_on_a_family_of_right_hand_sides():
+    """-ksp_fischer_guess 1,4 (KSPSetUseFischerGuess): same solutions as the direct solve, far
+    fewer iterations once the right-hand sides repeat inside a low-dimensional family"""
+    from pynama_b200.petsc import KSP, PC, Vec
+    mesh, dm, tab = _setup([3, 3, 3], 3, 0.1)
+    cls = fs_classes(mesh)
+    dm.set_dof_class(cls)
+    mats = dm.assemble_kle("FS")
+    want = assembly.assemble_kle(tab, mesh.corner_xyz, mesh.elem_nodes, mesh.nnodes, cls, "FS")
+    lu = spl.splu(want["K"].tocsc())
+    rng = np.random.default_rng(5)
+    b0, b1 = rng.uniform(-1, 1, mesh.nnodes * 3), rng.uniform(-1, 1, mesh.nnodes * 3)
+    its = {}
+    for fischer in (0, 4):
+        ksp = KSP().create()
+        ksp.setType("cg")
+        p = PC().create()
+        p.setType("bjacobi")
+        ksp.setPC(p)
+        ksp.setOperators(mats["K"])
+        ksp.setTolerances(rtol=1e-11, max_it=5000)
+        if fischer:
+            ksp.setUseFischerGuess(1, fischer)
+        x = Vec(mesh.nnodes * 3)
+        its[fischer] = []
+        for a in (1.0, 0.9, 0.8, 0.7, 0.6, 0.5, 0.45, 0.4, 0.35, 0.3):
+            b = b0 + a * b1
+            ksp.solve(Vec().createWithArray(b), x)
+            assert ksp.getConvergedReason() > 0
+            ref = lu.solve(b)
+            assert np.linalg.norm(x.getArray() - ref) <= 1e-8 * np.linalg.norm(ref), (fischer, a)
+            its[fischer].append(ksp.getIterationNumber())
+    assert sum(its[4][2:]) < 0.3 * sum(its[0][2:]), its
