@@ -153,6 +153,8 @@ class BoundaryConditions:
         self._dim = 2 if len(sides) == 4 else 3
         self._plans = {}
         self._scatter = {}
+        self._prefetched = {}
+        self._pool = getattr(self, "_pool", None)
         self.logger = logging.getLogger(f"[{self.comm.rank}]Boundary Conditions:")
 
     # ---- configuration (boundary_conditions.py:44-148) -------------------------------------
@@ -229,6 +231,8 @@ class BoundaryConditions:
         self._byName[b.getName()] = b
         self._plans = {}
         self._scatter = {}
+        self._prefetched = {}
+        self._pool = getattr(self, "_pool", None)
 
     # ---- queries ---------------------------------------------------------------------------------
     def getNames(self, bcs=None):
@@ -249,6 +253,8 @@ class BoundaryConditions:
         self._byName[bName].setNodes(nodes)
         self._plans = {}
         self._scatter = {}
+        self._prefetched = {}
+        self._pool = getattr(self, "_pool", None)
 
     def setBoundaryCoords(self, bName, coords):
         self._byName[bName].setNodesCoordinates(coords)
@@ -309,11 +315,36 @@ class BoundaryConditions:
             self._plans[name] = (allidx[keep].astype(np.int64), keep)
         return self._plans[name]
 
-    def getValuesMerged(self, name, t, nu):
+    def _evalMerged(self, name, t, nu):
         idx, keep = self._plan(name)
         vals = [np.asarray(b.getValues(name, t, nu), dtype=np.float64).ravel() for b in self._boundaries]
         vals = np.concatenate(vals) if vals else np.zeros(0)
         return idx, vals[keep]
+
+    def getValuesMerged(self, name, t, nu):
+        """(indices, values) of all sides for variable `name` at time t.  Values requested
+        ahead of time with prefetch() are picked up from the worker thread."""
+        key = (name, t, nu)
+        fut = self._prefetched.pop(key, None)
+        if fut is not None:
+            return fut.result()
+        return self._evalMerged(name, t, nu)
+
+    def prefetch(self, names, t, nu):
+        """Evaluate the (host, numpy) boundary functions for a FUTURE time on a worker thread
+        while the device runs the current Krylov solve -- the TS knows the next stage time."""
+        if t is None:
+            return
+        if self._pool is None:
+            from concurrent.futures import ThreadPoolExecutor
+            self._pool = ThreadPoolExecutor(max_workers=2, thread_name_prefix="bc-prefetch")
+        for name in names:
+            key = (name, t, nu)
+            if key not in self._prefetched:
+                if len(self._prefetched) > 8:               # stale requests (rejected steps)
+                    self._prefetched.clear()
+                self._plan(name)                            # build the index plan on this thread
+                self._prefetched[key] = self._pool.submit(self._evalMerged, name, t, nu)
 
     def setValuesToVec(self, vec, name, t, nu):
         idx, vals = self.getValuesMerged(name, t, nu)

@@ -111,6 +111,8 @@ class BaseProblem(object):
     def evalRHS(self, ts, t, vort, f):
         """Evaluate the KLE right hand side."""
         w = vort if self.rhsUsesStage else self.vort
+        # boundary values of the NEXT evaluation are computed on a host thread during this solve
+        self.dom.prefetchBoundaryConditions(("vorticity", "velocity"), getattr(ts, "next_rhs_time", None), self.nu)
         self.dom.applyBoundaryConditions(w, "vorticity", t, self.nu)
         vel = self.solverKLE.getSolution()
         self.dom.applyBoundaryConditions(vel, "velocity", t, self.nu)

@@ -249,6 +249,10 @@ class Domain:
         assert self._bc, "Boundary conditions not defined"
         self._bc.setValuesToVec(vec, varName, t, nu)
 
+    def prefetchBoundaryConditions(self, varNames, t, nu):
+        if self._bc is not None and t is not None:
+            self._bc.prefetch(varNames, t, nu)
+
     def applyBoundaryConditionsNS(self, vec, varName, t=None, nu=None):
         assert self._bc, "Boundary conditions not defined"
         self._bc.setTangentialValuesToVec(vec, varName, t, nu)

@@ -70,6 +70,7 @@ class TS:
         self._fsal_valid = False
         self.rejections = 0
         self.rhs_evals = 0
+        self.next_rhs_time = None
 
     def create(self, comm=None):
         self._init_fields()
@@ -199,6 +200,12 @@ class TS:
                     nz = [(cf, k[j]) for j, cf in enumerate(coef) if cf != 0.0]
                     y.maxpy([cf for cf, _ in nz], [v for _, v in nz])
                     stage = y
+                # time of the next RHS evaluation (next stage, or the first new stage of the next
+                # step), so that the callback can prepare time-dependent host data ahead
+                if i + 1 < s:
+                    self.next_rhs_time = t + c[i + 1] * h
+                else:
+                    self.next_rhs_time = t + h + c[1 if tab["fsal"] else 0] * self._dt
                 self._rhs(self, t + c[i] * h, stage, k[i])
                 self.rhs_evals += 1
             # u_new = u + h sum b_j k_j  (into y, so a rejected step leaves u untouched)
