@@ -254,7 +254,9 @@ def run_b200(args, rank, world):
                    "ksp_iterations_per_step": its / args.steps, "ksp_solves_per_step": solves / args.steps,
                    "parallelism": "1 GPU" if world == 1 else
                    f"row partition over {world} GPUs ({'x'.join(str(p) for p in fem.dom._partition.pgrid)} element "
-                   f"blocks), halo exchange + allreduce over NCCL, {ctx.collectives()} collectives so far on rank 0",
+                   f"blocks), halo exchange + Krylov allreduces " +
+                   ("fused into the kernels over peer memory (CUDA IPC / NVLink)" if ctx.p2p_status()[0]
+                    else "over NCCL") + f", {ctx.collectives()} collectives so far on rank 0",
                    "l2": "inputs larger than L2 (K = %.2f GB per SpMV)" % (spmv_bytes / 1e9)},
         "roofline": roofline,
         "kernel_time_ms_per_step": {"spmv_K_dot": ms_spmv / args.steps, "cg_update": ms_upd / args.steps,

@@ -14,6 +14,8 @@
 #include "ksp.cuh"
 #include "vec.cuh"
 #include "comm.cuh"
+#include <memory>
+#include <algorithm>
 
 namespace pyn {
 int g_ksp_check_every = 8;
@@ -395,6 +397,10 @@ struct pyn_ksp {
   DevBuf<double> fx[kFischerMax], fax[kFischerMax];
   DevBuf<double> x0, r0, fd, fad, fcoef;     // fcoef: [kFischerMax + 4]
   int64_t fischer_used = 0, fischer_restarts = 0;
+  // work vectors of BiCGStab / GMRES(m)
+  DevBuf<double> kv[4];
+  std::vector<std::unique_ptr<DevBuf<double>>> gv;
+  DevBuf<double> gcoef;
 };
 
 template <int B>
@@ -550,14 +556,253 @@ static int ksp_solve_cg(pyn_ksp* k, const double* b, double* x, int* its, int* r
   return PYN_OK;
 }
 
+
+// ---- BiCGStab and GMRES(m) ------------------------------------------------------------------
+// The KLE operator is SPD, so CG is the production solver; these two exist because the
+// reference's KspSolver defaults to gmres (kle_solver.py:58) and honours -ksp_type from the
+// options database.  Both are left-preconditioned like PETSc's defaults and test the
+// preconditioned residual norm against max(rtol*||M^-1 b||, atol).  Vector work runs on the
+// device (SpMV, fused multi-dot / linear-combination kernels); the handful of recurrence
+// scalars is kept on the host (one small read-back per dot group).
+template <int B>
+__global__ void pc_apply_kernel(int pc, const double* __restrict__ pcd, const double* __restrict__ r,
+                                double* __restrict__ z, int64_t nnodes) {
+  for (int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; n < nnodes;
+       n += (int64_t)gridDim.x * blockDim.x) {
+    double rr[B], zz[B];
+#pragma unroll
+    for (int i = 0; i < B; ++i) rr[i] = r[n * B + i];
+    apply_pc_node<B>(pc, pcd, n, rr, zz);
+#pragma unroll
+    for (int i = 0; i < B; ++i) z[n * B + i] = zz[i];
+  }
+}
+
+template <int B>
+struct KrylovOps {
+  pyn_ksp* k;
+  pyn_ctx* ctx;
+  int64_t nn, n;
+  bool dist;
+  int gridn;
+  // z = M^-1 (A x)     (tmp = k->w)
+  int apply(const double* x, double* z) {
+    PYN_CHECK(spmv(k->A, 1.0, x, 0.0, nullptr, k->w.p));
+    return pc(k->w.p, z);
+  }
+  int pc(const double* r, double* z) {
+    pc_apply_kernel<B><<<gridn, 256, 0, ctx->stream>>>(k->pc, k->pcd.p, r, z, nn);
+    PYN_LAUNCHED(ctx);
+    return PYN_OK;
+  }
+  int dot(const double* a, const double* b, double* out) { return vec_dot(ctx, a, b, n, out, dist); }
+};
+
+template <int B>
+static int ksp_solve_bcgs(pyn_ksp* k, const double* b, double* x, int* its, int* reason, double* rnorm) {
+  pyn_ctx* ctx = k->ctx;
+  KrylovOps<B> op;
+  op.k = k;
+  op.ctx = ctx;
+  op.dist = k->A->halo != nullptr && ctx->nranks > 1;
+  op.nn = k->A->halo ? k->A->halo->n_own : k->nnodes;
+  op.n = op.nn * B;
+  op.gridn = grid_for(ctx, op.nn > 0 ? op.nn : 1, 256);
+  const int64_t n = op.n;
+  if (!k->pc_ready) PYN_CHECK(ksp_setup_pc<B>(k));
+  for (DevBuf<double>* v : {&k->kv[0], &k->kv[1], &k->kv[2], &k->kv[3]})
+    if (v->n != k->n) PYN_CHECK(v->alloc(ctx, k->n));
+  double *r = k->r.p, *rh = k->kv[0].p, *p = k->p.p, *v = k->kv[1].p, *s = k->kv[2].p, *t = k->kv[3].p;
+  double bn2 = 0, rn2 = 0;
+  PYN_CHECK(op.pc(b, k->z.p));
+  PYN_CHECK(op.dot(k->z.p, k->z.p, &bn2));
+  PYN_CHECK(spmv(k->A, -1.0, x, 1.0, b, k->w.p));          // w = b - A x
+  PYN_CHECK(op.pc(k->w.p, r));
+  PYN_CHECK(op.dot(r, r, &rn2));
+  double ttol = k->rtol * sqrt(bn2);
+  int why_ok = 2;
+  if (k->atol > ttol) {
+    ttol = k->atol;
+    why_ok = 3;
+  }
+  const double dtol = k->dtol * (bn2 > 0 ? sqrt(bn2) : 1.0);
+  PYN_CUDA(cudaMemcpyAsync(rh, r, sizeof(double) * n, cudaMemcpyDeviceToDevice, ctx->stream));
+  PYN_CHECK(vec_set(ctx, p, n, 0.0));
+  PYN_CHECK(vec_set(ctx, v, n, 0.0));
+  double rho = 1, alpha = 1, omega = 1, rn = sqrt(rn2);
+  int it = 0, why = 0;
+  if (rn <= ttol) why = why_ok;
+  while (!why) {
+    double rho1 = 0, rhv = 0, ts[2] = {0, 0};
+    PYN_CHECK(op.dot(rh, r, &rho1));
+    if (rho1 == 0.0 || omega == 0.0) {
+      why = -9;
+      break;
+    }
+    const double beta = (rho1 / rho) * (alpha / omega);
+    // p = r + beta (p - omega v)
+    PYN_CHECK(vec_axpby(ctx, p, -beta * omega, v, beta, n));
+    PYN_CHECK(vec_axpby(ctx, p, 1.0, r, 1.0, n));
+    PYN_CHECK(op.apply(p, v));
+    PYN_CHECK(op.dot(rh, v, &rhv));
+    if (rhv == 0.0) {
+      why = -9;
+      break;
+    }
+    alpha = rho1 / rhv;
+    PYN_CHECK(vec_waxpy(ctx, s, -alpha, v, r, n));           // s = r - alpha v
+    PYN_CHECK(op.apply(s, t));
+    PYN_CHECK(op.dot(t, s, &ts[0]));
+    PYN_CHECK(op.dot(t, t, &ts[1]));
+    omega = ts[1] != 0.0 ? ts[0] / ts[1] : 0.0;
+    PYN_CHECK(vec_axpby(ctx, x, alpha, p, 1.0, n));
+    PYN_CHECK(vec_axpby(ctx, x, omega, s, 1.0, n));
+    PYN_CHECK(vec_waxpy(ctx, r, -omega, t, s, n));           // r = s - omega t
+    PYN_CHECK(op.dot(r, r, &rn2));
+    rn = sqrt(rn2);
+    rho = rho1;
+    ++it;
+    if (!(rn == rn)) why = -9;
+    else if (rn <= ttol) why = why_ok;
+    else if (rn >= dtol) why = -4;
+    else if (it >= k->maxit) why = -3;
+  }
+  if (its) *its = it;
+  if (reason) *reason = why;
+  if (rnorm) *rnorm = rn;
+  return PYN_OK;
+}
+
+template <int B>
+static int ksp_solve_gmres(pyn_ksp* k, const double* b, double* x, int* its, int* reason, double* rnorm) {
+  pyn_ctx* ctx = k->ctx;
+  KrylovOps<B> op;
+  op.k = k;
+  op.ctx = ctx;
+  op.dist = k->A->halo != nullptr && ctx->nranks > 1;
+  op.nn = k->A->halo ? k->A->halo->n_own : k->nnodes;
+  op.n = op.nn * B;
+  op.gridn = grid_for(ctx, op.nn > 0 ? op.nn : 1, 256);
+  const int64_t n = op.n;
+  const int m = k->restart > 0 ? k->restart : 30;
+  if (!k->pc_ready) PYN_CHECK(ksp_setup_pc<B>(k));
+  if ((int)k->gv.size() != m + 1) {
+    k->gv.clear();
+    for (int i = 0; i <= m; ++i) {
+      k->gv.emplace_back(new DevBuf<double>());
+      PYN_CHECK(k->gv.back()->alloc(ctx, k->n));
+    }
+    PYN_CHECK(k->gcoef.alloc(ctx, kFischerMax));
+  }
+  const int gridv = grid_for(ctx, n > 0 ? n : 1, 256);
+  double bn2 = 0;
+  PYN_CHECK(op.pc(b, k->z.p));
+  PYN_CHECK(op.dot(k->z.p, k->z.p, &bn2));
+  double ttol = k->rtol * sqrt(bn2);
+  int why_ok = 2;
+  if (k->atol > ttol) {
+    ttol = k->atol;
+    why_ok = 3;
+  }
+  const double dtol = k->dtol * (bn2 > 0 ? sqrt(bn2) : 1.0);
+  std::vector<double> H((size_t)(m + 1) * m, 0.0), cs(m, 0.0), sn(m, 0.0), g(m + 1, 0.0), y(m, 0.0), hcol(m + 2, 0.0);
+  int it = 0, why = 0;
+  double rn = 0;
+  while (!why) {
+    // r = M^-1 (b - A x); v0 = r / ||r||
+    PYN_CHECK(spmv(k->A, -1.0, x, 1.0, b, k->w.p));
+    PYN_CHECK(op.pc(k->w.p, k->gv[0]->p));
+    double rn2 = 0;
+    PYN_CHECK(op.dot(k->gv[0]->p, k->gv[0]->p, &rn2));
+    rn = sqrt(rn2);
+    if (!(rn == rn)) { why = -9; break; }
+    if (rn <= ttol) { why = why_ok; break; }
+    if (rn >= dtol) { why = -4; break; }
+    if (it >= k->maxit) { why = -3; break; }
+    PYN_CHECK(vec_scale(ctx, k->gv[0]->p, n, 1.0 / rn));
+    std::fill(g.begin(), g.end(), 0.0);
+    g[0] = rn;
+    int j = 0;
+    for (; j < m && !why; ++j) {
+      double* w = k->gv[j + 1]->p;
+      PYN_CHECK(op.apply(k->gv[j]->p, w));
+      // classical Gram-Schmidt, two passes (h = V^T w; w -= V h), coefficients summed
+      for (int i = 0; i <= j; ++i) hcol[i] = 0.0;
+      for (int pass = 0; pass < 2; ++pass) {
+        for (int i0 = 0; i0 <= j; i0 += kFischerMax) {
+          BasisPtrs bp;
+          bp.k = (j + 1 - i0) < kFischerMax ? (j + 1 - i0) : kFischerMax;
+          for (int i = 0; i < bp.k; ++i) bp.v[i] = k->gv[i0 + i]->p;
+          multi_dot_kernel<<<gridv, 256, 0, ctx->stream>>>(bp, w, n, ctx->red_partials, ctx->red_ticket, k->gcoef.p);
+          PYN_LAUNCHED(ctx);
+          if (op.dist) PYN_CHECK(comm_allreduce_sum(ctx, k->gcoef.p, kFischerMax));
+          lincomb_kernel<<<gridv, 256, 0, ctx->stream>>>(w, bp, k->gcoef.p, -1.0, 1, n);
+          PYN_LAUNCHED(ctx);
+          double hc[kFischerMax];
+          PYN_CHECK(k->gcoef.download(hc, kFischerMax));
+          for (int i = 0; i < bp.k; ++i) hcol[i0 + i] += hc[i];
+        }
+      }
+      double wn2 = 0;
+      PYN_CHECK(op.dot(w, w, &wn2));
+      const double hn = sqrt(wn2);
+      hcol[j + 1] = hn;
+      if (hn > 0) PYN_CHECK(vec_scale(ctx, w, n, 1.0 / hn));
+      // Givens rotations on the new column
+      for (int i = 0; i < j; ++i) {
+        const double t0 = cs[i] * hcol[i] + sn[i] * hcol[i + 1];
+        hcol[i + 1] = -sn[i] * hcol[i] + cs[i] * hcol[i + 1];
+        hcol[i] = t0;
+      }
+      const double den = sqrt(hcol[j] * hcol[j] + hcol[j + 1] * hcol[j + 1]);
+      cs[j] = den > 0 ? hcol[j] / den : 1.0;
+      sn[j] = den > 0 ? hcol[j + 1] / den : 0.0;
+      hcol[j] = den;
+      g[j + 1] = -sn[j] * g[j];
+      g[j] = cs[j] * g[j];
+      for (int i = 0; i <= j; ++i) H[(size_t)i * m + j] = hcol[i];
+      rn = fabs(g[j + 1]);
+      ++it;
+      if (!(rn == rn)) why = -9;
+      else if (rn <= ttol) why = why_ok;
+      else if (rn >= dtol) why = -4;
+      else if (it >= k->maxit) why = -3;
+      else if (hn == 0.0) { ++j; break; }                      // happy breakdown
+    }
+    // x += V y, H y = g (upper triangular, j columns)
+    for (int i = j - 1; i >= 0; --i) {
+      double sum = g[i];
+      for (int l = i + 1; l < j; ++l) sum -= H[(size_t)i * m + l] * y[l];
+      y[i] = H[(size_t)i * m + i] != 0.0 ? sum / H[(size_t)i * m + i] : 0.0;
+    }
+    for (int i0 = 0; i0 < j; i0 += kFischerMax) {
+      BasisPtrs bp;
+      bp.k = (j - i0) < kFischerMax ? (j - i0) : kFischerMax;
+      double yc[kFischerMax] = {0, 0, 0, 0, 0, 0, 0, 0};
+      for (int i = 0; i < bp.k; ++i) {
+        bp.v[i] = k->gv[i0 + i]->p;
+        yc[i] = y[i0 + i];
+      }
+      PYN_CHECK(k->gcoef.upload(yc, kFischerMax));
+      lincomb_kernel<<<gridv, 256, 0, ctx->stream>>>(x, bp, k->gcoef.p, 1.0, 1, n);
+      PYN_LAUNCHED(ctx);
+    }
+    PYN_CUDA(cudaStreamSynchronize(ctx->stream));
+  }
+  if (its) *its = it;
+  if (reason) *reason = why;
+  if (rnorm) *rnorm = rn;
+  return PYN_OK;
+}
+
 extern "C" {
 
 int pyn_ksp_create(pyn_ctx* ctx, pyn_mat* a, int type, int pc, pyn_ksp** out) {
   PYN_REQUIRE(ctx && a && out, "pyn_ksp_create: null argument");
   PYN_REQUIRE(a->br == a->bc && a->nbrows == a->nbcols, "KSP operator must be square");
   PYN_REQUIRE(pc >= PYN_PC_NONE && pc <= PYN_PC_BJACOBI, "unknown pc type %d", pc);
-  if (type != PYN_KSP_CG) {
-    set_error("KSP type %d is not implemented yet (available: cg)", type);
+  if (type != PYN_KSP_CG && type != PYN_KSP_GMRES && type != PYN_KSP_BCGS) {
+    set_error("KSP type %d is not available (cg, gmres, bcgs)", type);
     return PYN_E_UNSUPPORTED;
   }
   pyn_ksp* k = new pyn_ksp();
@@ -626,11 +871,20 @@ int pyn_ksp_solve(pyn_ksp* k, pyn_vec* b, pyn_vec* x, int* its, int* reason, dou
   PYN_REQUIRE(b->n == k->n && x->n == k->n, "pyn_ksp_solve: vector size %lld/%lld, operator %lld",
               (long long)b->n, (long long)x->n, (long long)k->n);
   PYN_REQUIRE(b != x, "pyn_ksp_solve: b and x must differ");
-  switch (k->B) {
-    case 1: return ksp_solve_cg<1>(k, b->d.p, x->d.p, its, reason, rnorm);
-    case 2: return ksp_solve_cg<2>(k, b->d.p, x->d.p, its, reason, rnorm);
-    case 3: return ksp_solve_cg<3>(k, b->d.p, x->d.p, its, reason, rnorm);
+#define SOLVE(FN)                                                         \
+  switch (k->B) {                                                         \
+    case 1: return FN<1>(k, b->d.p, x->d.p, its, reason, rnorm);          \
+    case 2: return FN<2>(k, b->d.p, x->d.p, its, reason, rnorm);          \
+    case 3: return FN<3>(k, b->d.p, x->d.p, its, reason, rnorm);          \
   }
+  if (k->type == PYN_KSP_GMRES) {
+    SOLVE(ksp_solve_gmres)
+  } else if (k->type == PYN_KSP_BCGS) {
+    SOLVE(ksp_solve_bcgs)
+  } else {
+    SOLVE(ksp_solve_cg)
+  }
+#undef SOLVE
   set_error("unsupported block size %d", k->B);
   return PYN_E_UNSUPPORTED;
 }

@@ -773,11 +773,11 @@ class PC:
 class KSP:
     """PETSc.KSP surface used by KspSolver (solver/kle_solver.py:49-64).
 
-    Types: cg (and, being SPD-only for now, every other requested type is
-    refused loudly rather than silently replaced).  ``-pc_type lu`` -- the
-    reference default, a direct solve -- is mapped to CG + node-block Jacobi at
-    rtol 1e-12 and logged, because a sparse direct factorisation is not part of
-    the B200 path.
+    Types: cg (production path: the KLE operator is SPD), gmres (restart
+    ``-ksp_gmres_restart``, default 30) and bcgs, all left-preconditioned with
+    none / jacobi / bjacobi.  ``-pc_type lu`` -- the reference default, a direct
+    solve -- is mapped to CG + node-block Jacobi at rtol 1e-12 and logged, because
+    a sparse direct factorisation is not part of the B200 path.
     """
     _TYPES = {"cg": 0, "gmres": 1, "bcgs": 2, "preonly": 3}
     _PCS = {"none": 0, "jacobi": 1, "bjacobi": 2, "pbjacobi": 2}
@@ -871,11 +871,6 @@ class KSP:
             self._log.warning("direct solve (-ksp_type %s -pc_type %s) requested: using cg + node-block "
                               "Jacobi at rtol 1e-12 on the GPU instead", ktype, pctype)
             ktype, pctype, rtol = "cg", "bjacobi", min(self.rtol, 1e-12)
-        if ktype == "gmres" and pctype in self._PCS:
-            # K is SPD after the Dirichlet elimination, so CG applies; GMRES is the
-            # reference's *default type* only because its LU preconditioner is exact.
-            self._log.info("ksp_type gmres on the SPD KLE operator: solving with cg")
-            ktype = "cg"
         if ktype not in self._TYPES:
             raise PynamaError(f"unknown KSP type '{ktype}'")
         if pctype not in self._PCS:

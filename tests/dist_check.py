@@ -27,7 +27,7 @@ def main():
     import bench
     from pynama_b200.cases.base_problem import BaseProblem
     o = Options()
-    for k, v in (("ksp_type", "cg"), ("pc_type", "bjacobi"), ("ksp_rtol", 1e-13), ("ksp_max_it", 20000),
+    for k, v in (("ksp_type", os.environ.get("DIST_KSP", "cg")), ("pc_type", "bjacobi"), ("ksp_rtol", 1e-13), ("ksp_max_it", 20000),
                  ("ts_adapt_type", "none"), ("ts_dt", 1e-3)):
         o.setValue(k, v)
     if os.environ.get("DIST_FISCHER", "0") != "0":

@@ -26,9 +26,9 @@ def _run(nproc, port, env_extra=None):
     assert "OK" in r.stdout
 
 
-@pytest.mark.parametrize("fischer", ["0", "4"])
-def test_single_rank_script(fischer):
-    env = dict(os.environ, DIST_FISCHER=fischer)
+@pytest.mark.parametrize("fischer,ksp", [("0", "cg"), ("4", "cg"), ("0", "gmres"), ("0", "bcgs")])
+def test_single_rank_script(fischer, ksp):
+    env = dict(os.environ, DIST_FISCHER=fischer, DIST_KSP=ksp)
     r = subprocess.run([sys.executable, SCRIPT], capture_output=True, text=True, timeout=600, env=env)
     assert r.returncode == 0, r.stdout[-3000:] + "\n" + r.stderr[-3000:]
 
@@ -38,6 +38,13 @@ def test_partitioned_run_nccl_and_fischer():
     if _ngpus() < 2:
         pytest.skip("needs 2 GPUs")
     _run(2, 29549, {"PYN_P2P": "0", "DIST_FISCHER": "4"})
+
+
+@pytest.mark.parametrize("ksp", ["gmres", "bcgs"])
+def test_partitioned_run_other_ksp_types(ksp):
+    if _ngpus() < 2:
+        pytest.skip("needs 2 GPUs")
+    _run(2, 29551, {"DIST_KSP": ksp})
 
 
 @pytest.mark.parametrize("nproc", [2, 4, 8])

@@ -230,3 +230,42 @@ def test_fischer_guess_on_a_family_of_right_hand_sides():
             assert np.linalg.norm(x.getArray() - ref) <= 1e-8 * np.linalg.norm(ref), (fischer, a)
             its[fischer].append(ksp.getIterationNumber())
     assert sum(its[4][2:]) < 0.3 * sum(its[0][2:]), its
+
+
+@pytest.mark.parametrize("ktype", ["gmres", "bcgs"])
+@pytest.mark.parametrize("pc", ["jacobi", "bjacobi"])
+def test_gmres_and_bcgs_vs_direct(ktype, pc):
+    """-ksp_type gmres / bcgs (the reference's KspSolver default type is gmres, kle_solver.py:58)"""
+    from pynama_b200.petsc import KSP, PC, Vec
+    mesh, dm, tab = _setup([3, 3, 3], 3, 0.1)
+    cls = fs_classes(mesh)
+    dm.set_dof_class(cls)
+    mats = dm.assemble_kle("FS")
+    want = assembly.assemble_kle(tab, mesh.corner_xyz, mesh.elem_nodes, mesh.nnodes, cls, "FS")
+    rng = np.random.default_rng(11)
+    b = rng.uniform(-1, 1, mesh.nnodes * 3)
+    ref = spl.spsolve(want["K"].tocsc(), b)
+    ksp = KSP().create()
+    ksp.setType(ktype)
+    p = PC().create()
+    p.setType(pc)
+    ksp.setPC(p)
+    ksp.setOperators(mats["K"])
+    ksp.setTolerances(rtol=1e-12, max_it=4000)
+    x = Vec(mesh.nnodes * 3)
+    ksp.solve(Vec().createWithArray(b), x)
+    assert ksp.getConvergedReason() > 0, (ksp.getConvergedReason(), ksp.getIterationNumber())
+    assert np.linalg.norm(x.getArray() - ref) <= 1e-8 * np.linalg.norm(ref)
+    # 2-D (2x2 blocks) too
+    mesh2, dm2, tab2 = _setup([4, 4], 4)
+    cls2 = fs_classes(mesh2)
+    dm2.set_dof_class(cls2)
+    m2 = dm2.assemble_kle("FS")
+    w2 = assembly.assemble_kle(tab2, mesh2.corner_xyz, mesh2.elem_nodes, mesh2.nnodes, cls2, "FS")
+    b2 = rng.uniform(-1, 1, mesh2.nnodes * 2)
+    ksp.setOperators(m2["K"])
+    x2 = Vec(mesh2.nnodes * 2)
+    ksp.solve(Vec().createWithArray(b2), x2)
+    assert ksp.getConvergedReason() > 0
+    ref2 = spl.spsolve(w2["K"].tocsc(), b2)
+    assert np.linalg.norm(x2.getArray() - ref2) <= 1e-8 * np.linalg.norm(ref2)
