@@ -195,3 +195,100 @@ class OracleProblem:
                 unew += h * RK5BS_B[j] * k[j]
         self.vort = unew
         return t + h, k[s - 1]
+
+
+# ---- no-slip (NS) path --------------------------------------------------------------------------
+SIDE_AXIS = {"left": 0, "right": 0, "down": 1, "up": 1, "back": 2, "front": 2}   # boundary.py:151-162
+
+
+def ns_dof_classes(sides, side_nodes, nnodes, dim):
+    """velocity dof classes of an all-no-slip box (0 free, 2 normal, 3 tangential).
+
+    sides: side names in the order of the case file; side_nodes[name]: node ids.
+    Tangential dofs: boundary_conditions.py:214-225; normal dofs with the left/right
+    corner rule of :227-243 (single rank, collect=True); a dof that is both is normal
+    (mat_ns.py:59-62)."""
+    tang, normal, remove = set(), set(), set()
+    for s in sides:
+        ax = SIDE_AXIS[s]
+        nodes = np.asarray(side_nodes[s], dtype=np.int64)
+        for d in range(dim):
+            if d != ax:
+                tang |= set((nodes * dim + d).tolist())
+        loc = set((nodes * dim + ax).tolist())
+        if s in ("left", "right"):
+            for ind in loc:
+                if (ind + 1) in normal:
+                    remove.add(ind)
+        normal |= loc
+    normal -= remove
+    cls = np.zeros(nnodes * dim, np.uint8)
+    cls[np.fromiter(tang, dtype=np.int64, count=len(tang))] = 3
+    cls[np.fromiter(normal, dtype=np.int64, count=len(normal))] = 2
+    return cls
+
+
+class OracleProblemNS:
+    """Lid-driven cavity style problem: every side no-slip with a constant wall velocity.
+    Restates MatNS (through oracle.assembly), KleSolver.solveFS/solve (kle_solver.py:33-41)
+    and the NS branch of evalRHS (base_problem.py:119-123)."""
+
+    def __init__(self, dim, ngl, corner_xyz, elem_nodes, coords, sides, side_nodes, wall_vel, rho, mu):
+        self.dim, self.dim_w = dim, (1 if dim == 2 else 3)
+        self.rho, self.mu, self.nu = rho, mu, mu / rho
+        self.coords = np.asarray(coords, dtype=np.float64)
+        n = len(self.coords)
+        self.sides = list(sides)
+        self.side_nodes = {s: np.asarray(side_nodes[s], dtype=np.int64) for s in self.sides}
+        self.wall_vel = {s: np.asarray(wall_vel[s], dtype=np.float64) for s in self.sides}
+        self.cls = ns_dof_classes(self.sides, self.side_nodes, n, dim)
+        tab = sem.SpectralTables(ngl, dim)
+        self.mats = assembly.assemble_kle(tab, corner_xyz, elem_nodes, n, self.cls, "NS")
+        self.ops = assembly.assemble_ops(tab, corner_xyz, elem_nodes, n)
+        self._lu = spl.splu(self.mats["K"].tocsc())
+        self._lufs = spl.splu((self.mats["K"] + self.mats["Kfs"]).tocsc())      # kle_solver.py:25
+        self.vel = np.zeros(n * dim)
+        self.velfs = np.zeros(n * dim)
+        self.vort = np.zeros(n * self.dim_w)
+
+    def _set_sides(self, vec, ncomp, values):
+        """setValuesToVec (boundary_conditions.py:252-260): sides in order, later sides overwrite"""
+        v = vec.reshape(-1, ncomp)
+        for s in self.sides:
+            v[self.side_nodes[s]] = values[s]
+
+    def eval_rhs(self, t):
+        dim = self.dim
+        self._set_sides(self.vort, self.dim_w, {s: np.zeros(self.dim_w) for s in self.sides})   # :115
+        self._set_sides(self.vel, dim, self.wall_vel)                                            # :116-117
+        m = self.mats
+        b = m["Rw"] @ self.vort + m["Rwfs"] @ self.vort + m["Krhsfs"] @ self.vel                 # kle_solver.py:39-41
+        self.velfs = self._lufs.solve(b)
+        v = self.velfs.reshape(-1, dim)                                                          # :121-122
+        for s in self.sides:                    # setTangentialValuesToVec, boundary_conditions.py:262-277
+            for d in range(dim):
+                if d != SIDE_AXIS[s]:
+                    v[self.side_nodes[s], d] = self.wall_vel[s][d]
+        self.vort = self.ops["Curl"] @ self.velfs                                                # :123
+        self.vel = self._lu.solve(m["Rw"] @ self.vort + m["Krhs"] @ self.vel)                    # :125
+        aux = self.ops["SrT"] @ self.vel
+        aux *= 2.0 * self.mu
+        aux += -1.0 * self.rho * vtensv(self.vel, dim)
+        rhs = self.ops["DivSrT"] @ aux
+        rhs *= 1.0 / self.rho
+        return self.ops["Curl"] @ rhs
+
+    def step(self, t, h, k0=None):
+        s = len(RK5BS_B)
+        k = [None] * s
+        for i in range(s):
+            if i == 0 and k0 is not None:
+                k[0] = k0
+                continue
+            k[i] = self.eval_rhs(t + RK5BS_C[i] * h)
+        unew = self.vort.copy()
+        for j in range(s):
+            if RK5BS_B[j] != 0.0:
+                unew += h * RK5BS_B[j] * k[j]
+        self.vort = unew
+        return t + h, k[s - 1]

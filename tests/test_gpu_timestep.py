@@ -1,0 +1,81 @@
+"""GPU parity of the whole time loop through the reference-shaped API (BaseProblem / TsSolver /
+KleSolver): velocity and vorticity after N fixed RK5BS steps against the CPU oracle
+(oracle/timestep.py, direct solves).  Tolerance 1e-8 relative to the field's max (KSP rtol 1e-13)."""
+import numpy as np
+import pytest
+
+from oracle import timestep
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-8
+
+
+def _options(ksp="cg"):
+    from pynama_b200.petsc import Options
+    o = Options()
+    for k, v in (("ksp_type", ksp), ("pc_type", "bjacobi"), ("ksp_rtol", 1e-13), ("ksp_max_it", 50000),
+                 ("ts_adapt_type", "none"), ("ts_dt", 2e-3)):
+        o.setValue(k, v)
+    o.delValue("ksp_fischer_guess")
+    return o
+
+
+def _rel(a, b):
+    return np.abs(np.asarray(a) - b).max() / max(np.abs(b).max(), 1e-300)
+
+
+@pytest.mark.parametrize("case,nelem,ngl", [("taylor-green", [5, 4], 4), ("taylor-green3d", [3, 3, 3], 3)])
+def test_free_slip_fields_after_n_steps(case, nelem, ngl):
+    from pynama_b200.cases.base_problem import BaseProblem
+    from pynama_b200.run_case import loadCase
+    _options()
+    cfg = loadCase(case)
+    fem = BaseProblem(cfg, case=case, nelem=nelem, ngl=ngl)
+    fem.setUp()
+    fem.setUpSolver()
+    fem.ts._post = None
+    fem.ts.setSolution(fem.vort)
+    mesh = fem.dom.getMesh()
+    dim = len(nelem)
+    orc = timestep.OracleProblem(dim, ngl, mesh.corner_xyz, mesh.elem_nodes, mesh.coords, mesh.getBordersNodes(),
+                                 rho=fem.rho, mu=fem.mu, solver="direct")
+    assert _rel(fem.vort.getArray(), orc.vort) < 1e-13
+    t, k0 = 0.0, None
+    for _ in range(3):
+        fem.ts.step()
+        t, k0 = orc.step(t, 2e-3, k0)
+    assert abs(fem.ts.getTime() - t) < 1e-15
+    assert _rel(fem.vort.getArray(), orc.vort) < TOL
+    assert _rel(fem.solverKLE.getSolution().getArray(), orc.vel) < TOL
+    # and the discrete solution stays close to the analytic Taylor-Green field
+    a = timestep.tg_alpha(fem.nu, t, dim)
+    assert _rel(fem.solverKLE.getSolution().getArray(), timestep.tg_velocity(mesh.coords, a)) < 0.15   # coarse meshes
+
+
+@pytest.mark.parametrize("case,nelem,ngl", [("cavity-2d", [5, 5], 3), ("cavity", [3, 3, 3], 3)])
+def test_no_slip_cavity_fields_after_n_steps(case, nelem, ngl):
+    """MatNS + the two-solve NS branch of evalRHS (base_problem.py:119-123, kle_solver.py:22-41)"""
+    from pynama_b200.cases.base_problem import BaseProblem
+    from pynama_b200.run_case import loadCase
+    _options("gmres")            # K + Kfs is symmetric but need not be definite
+    cfg = loadCase(case)
+    fem = BaseProblem(cfg, case=case, nelem=nelem, ngl=ngl)
+    fem.setUp()
+    fem.setUpSolver()
+    fem.ts._post = None
+    fem.ts.setSolution(fem.vort)
+    mesh = fem.dom.getMesh()
+    dim = len(nelem)
+    walls = cfg["boundary-conditions"]["no-slip"]
+    sides = list(walls.keys())
+    orc = timestep.OracleProblemNS(dim, ngl, mesh.corner_xyz, mesh.elem_nodes, mesh.coords, sides,
+                                   {s: mesh.getBorderNodes(s) for s in sides}, walls, rho=fem.rho, mu=fem.mu)
+    assert np.array_equal(fem.dom.getDofClasses(), orc.cls)
+    t, k0 = 0.0, None
+    for _ in range(2):
+        fem.ts.step()
+        t, k0 = orc.step(t, 2e-3, k0)
+    assert np.abs(orc.vel).max() > 0.5
+    assert _rel(fem.solverKLE.getSolution().getArray(), orc.vel) < TOL
+    assert _rel(fem.solverKLE.getFreeSlipSolution().getArray(), orc.velfs) < TOL
+    assert _rel(fem.vort.getArray(), orc.vort) < TOL

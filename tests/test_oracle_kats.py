@@ -154,3 +154,49 @@ def test_taylor_green3d_field_is_consistent():
                       np.asarray(tg.velocity(Xm, a)).reshape(-1, 3)) / (2 * eps)
     curl = np.stack([J[:, 2, 1] - J[:, 1, 2], J[:, 0, 2] - J[:, 2, 0], J[:, 1, 0] - J[:, 0, 1]], 1)
     assert np.abs(curl - w).max() < 1e-6 * max(np.abs(w).max(), 1)
+
+
+# ---- oracle time loop ---------------------------------------------------------------------------
+def test_oracle_timestep_tracks_taylor_green_decay():
+    """RK5BS steps of the restated evalRHS keep following the analytic Taylor-Green decay"""
+    from oracle import timestep
+    mesh = BoxMesh([6, 6], [0, 0], [1, 1], 5)
+    p = timestep.OracleProblem(2, 5, mesh.corner_xyz, mesh.elem_nodes, mesh.coords, mesh.getBordersNodes(),
+                               rho=0.5, mu=0.01, solver="direct")
+    t, k0 = 0.0, None
+    for _ in range(3):
+        t, k0 = p.step(t, 5e-3, k0)
+    a = timestep.tg_alpha(p.nu, t, 2)
+    assert a < 0.99
+    assert np.abs(p.vel - timestep.tg_velocity(mesh.coords, a)).max() < 2e-2      # 6x6, ngl 5 mesh
+    assert np.abs(p.vort - timestep.tg_vorticity(mesh.coords, a)).max() < 0.2     # |w| ~ 12.6
+
+
+def test_oracle_fischer_guess_same_solution_fewer_iterations():
+    from oracle import timestep
+    mesh = BoxMesh([3, 3, 3], [0, 0, 0], [1, 1, 1], 3)
+    out = {}
+    for f in (0, 6):
+        p = timestep.OracleProblem(3, 3, mesh.corner_xyz, mesh.elem_nodes, mesh.coords, mesh.getBordersNodes(),
+                                   rho=0.5, mu=0.01, solver="cg", rtol=1e-11, pc="bjacobi", fischer=f)
+        t, k0 = 0.0, None
+        for _ in range(3):
+            t, k0 = p.step(t, 1e-3, k0)
+        out[f] = (p.vel.copy(), p.iterations)
+    assert np.abs(out[0][0] - out[6][0]).max() < 1e-8
+    assert out[6][1] < 0.6 * out[0][1]
+
+
+def test_ns_dof_classes_corner_rule():
+    """boundary_conditions.py:227-243: up/down listed first -> the x dof of a left/right corner node
+    is tangential, not normal"""
+    from oracle import timestep
+    mesh = BoxMesh([3, 3], [0, 0], [1, 1], 3)
+    sides = ["up", "down", "left", "right"]
+    cls = timestep.ns_dof_classes(sides, {s: mesh.getBorderNodes(s) for s in sides}, mesh.nnodes, 2)
+    corner = 0                                  # node (0, 0): on 'down' and 'left'
+    assert cls[corner * 2 + 1] == 2 and cls[corner * 2 + 0] == 3
+    assert np.array_equal(ns_classes(mesh) == 0, cls == 0)
+    sides = ["left", "right", "up", "down"]     # sides in the other order: normal wins everywhere
+    cls2 = timestep.ns_dof_classes(sides, {s: mesh.getBorderNodes(s) for s in sides}, mesh.nnodes, 2)
+    assert np.array_equal(cls2, ns_classes(mesh))
