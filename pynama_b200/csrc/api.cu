@@ -130,6 +130,18 @@ int pyn_init(int device, pyn_ctx** out) {
   ctx->num_sms = prop.multiProcessorCount;
   ctx->smem_optin = prop.sharedMemPerBlockOptin;
   PYN_CUDA(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+  {
+    cudaMemPool_t pool;
+    unsigned long long keep = ~0ull;   // never trim: assembly scratch is reused by the next phase
+    PYN_CUDA(cudaDeviceGetDefaultMemPool(&pool, device));
+    PYN_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
+    // first use creates the pool (tens of ms): pay it here, with the CUDA context, and keep
+    // 256 MB mapped for the vectors and sort scratch of the set-up phase
+    void* warm = nullptr;
+    PYN_CUDA(cudaMallocAsync(&warm, (size_t)256 << 20, ctx->stream));
+    PYN_CUDA(cudaFreeAsync(warm, ctx->stream));
+    PYN_CUDA(cudaStreamSynchronize(ctx->stream));
+  }
   PYN_CUDA(cudaEventCreate(&ctx->ev0));
   PYN_CUDA(cudaEventCreate(&ctx->ev1));
   PYN_CUDA(cudaMalloc((void**)&ctx->red_partials, sizeof(double) * kRedMaxBlocks * kRedMaxVals));
@@ -392,6 +404,7 @@ static MatSpec kle_spec(pyn_mesh* mesh, int br, int bc, const double* ebs, doubl
   s.graph = &mesh->dense;
   s.ebs = ebs;
   s.ebs_pairs = (int64_t)mesh->nn * mesh->nn;
+  s.ebs_ppa = 0;
   s.pair_map = nullptr;
   s.sign = sign;
   s.use_rowcls = true;

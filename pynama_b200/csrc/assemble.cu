@@ -70,7 +70,7 @@ __global__ void __launch_bounds__(256)
 numeric_kernel(int64_t nrows, const int64_t* __restrict__ m_rowptr,
                const int32_t* __restrict__ m_colidx, const int64_t* __restrict__ m_base,
                const int64_t* __restrict__ cptr, const int2* __restrict__ csrc,
-               const double* __restrict__ ebs, int64_t ebs_pairs, int64_t e_base,
+               const double* __restrict__ ebs, int64_t ebs_pairs, int ebs_ppa, int64_t e_base,
                const int32_t* __restrict__ pair_map, double sign,
                const uint8_t* __restrict__ cls, bool use_rowcls, bool use_colcls,
                uint32_t pairmask, uint32_t diagmask, DiagAdd dadd,
@@ -97,9 +97,16 @@ numeric_kernel(int64_t nrows, const int64_t* __restrict__ m_rowptr,
         const int2 eq = csrc[k];
         const int32_t qq = pair_map ? pair_map[eq.y] : eq.y;
         if (qq >= 0) {
-          const double* src = ebs + (((int64_t)eq.x - e_base) * ebs_pairs + qq) * BB;
+          if (ebs_ppa > 0) {       // plane-major store
+            const int a = qq / ebs_ppa, m = qq - a * ebs_ppa;
+            const double* src = ebs + (((int64_t)eq.x - e_base) * ebs_pairs + (int64_t)a * ebs_ppa) * BB + m;
 #pragma unroll
-          for (int q = 0; q < BB; ++q) acc[q] += src[q];
+            for (int q = 0; q < BB; ++q) acc[q] += __ldcs(src + (int64_t)q * ebs_ppa);
+          } else {
+            const double* src = ebs + (((int64_t)eq.x - e_base) * ebs_pairs + qq) * BB;
+#pragma unroll
+            for (int q = 0; q < BB; ++q) acc[q] += src[q];
+          }
         }
       }
 #pragma unroll
@@ -194,7 +201,7 @@ int assemble_matrix(pyn_mesh* mesh, const MatSpec& sp, pyn_mat** out) {
 #define CALL(BR, BC)                                                                              \
   numeric_kernel<BR, BC><<<grid, 256, 0, ctx->stream>>>(                                          \
       m->nbrows, m->rowptr.p, m->colidx.p, m->base_slot.p, sp.graph->cptr.p, sp.graph->csrc.p,    \
-      sp.ebs, sp.ebs_pairs, 0, sp.pair_map, sp.sign, mesh->dofcls.p, sp.use_rowcls, sp.use_colcls, \
+      sp.ebs, sp.ebs_pairs, sp.ebs_ppa, 0, sp.pair_map, sp.sign, mesh->dofcls.p, sp.use_rowcls, sp.use_colcls, \
       sp.pairmask, sp.diagmask, da, sp.row_scale, m->val.p)
     prof_begin(ctx, PROF_NUMERIC);
     PYN_DISPATCH_BLOCK(sp.br, sp.bc, CALL);

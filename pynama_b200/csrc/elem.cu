@@ -2,10 +2,10 @@
 //
 // k1+k2: K_e, Rw_e, Rd_e of Spectral.getElemKLEMatrices (spectral.py:92-160).
 //   One CTA per (element, tile of row nodes).  Per chunk of quadrature points
-//   the CTA stages J^-1, w|J| and the physical gradients G[g][k][b] of all
-//   element nodes in shared memory (rebuilt from the 1-D tables), then every
-//   thread accumulates its node pairs (a,b) in registers: 21 fp64
-//   accumulators per pair in 3-D (K 3x3, Rw 3x3, Rd 3).
+//   the CTA stages J^-1, w|J| and the physical gradients of all element nodes
+//   in shared memory (rebuilt from the 1-D tables), then every thread
+//   accumulates the 16 moments (3-D) of its AT x 1 node pairs in registers
+//   and expands them into K (3x3), Rw (3x3), Rd (3) once, at the end.
 // k3: SrT_e, DivSrT_e, Curl_e, W_e of Spectral.getElemKLEOperators
 //   (spectral.py:162-228).  The nodal rule is collocated (H[g][a] = delta_ga,
 //   exact in the reference's tables), so row node a only sees point g = a and
@@ -20,92 +20,336 @@
 
 namespace pyn {
 
-template <int DIM, int P>
-__global__ void __launch_bounds__(256)
+// 1-D tables of the full and the reduced rule, copied to shared memory once per CTA; tensor
+// indices of nodes / points / corners packed into one word (t0 | t1<<8 | t2<<16).
+struct KleSmemTab {
+  double h[2][kMaxPts1d][kMaxNgl];
+  double dh[2][kMaxPts1d][kMaxNgl];
+  double hc[2][kMaxPts1d][2];
+  double dhc[2][kMaxPts1d][2];
+  double w[2][kMaxPts1d];
+};
+__device__ __forceinline__ uint32_t pack_t(const uint8_t* t) {
+  return (uint32_t)t[0] | ((uint32_t)t[1] << 8) | ((uint32_t)t[2] << 16);
+}
+// value (which < 0) or derivative along `which` of a tensor-product basis function; factors
+// multiplied in direction order as tensor_val does
+template <int DIM>
+__device__ __forceinline__ double tensor3(const double* v, const double* dv, int which) {
+  double r = which == 0 ? dv[0] : v[0];
+#pragma unroll
+  for (int d = 1; d < DIM; ++d) r = r * (which == d ? dv[d] : v[d]);
+  return r;
+}
+// J^-1 and det J at a point with packed tensor index gt (same arithmetic as point_geometry)
+template <int DIM>
+__device__ __forceinline__ void point_geometry_s(const KleSmemTab& T, int q, uint32_t gt,
+                                                 const uint32_t* cornT, const double* X,
+                                                 double* jinv, double* det) {
+  constexpr int NC = 1 << DIM;
+  double J[DIM][DIM];
+#pragma unroll
+  for (int d = 0; d < DIM; ++d)
+#pragma unroll
+    for (int e = 0; e < DIM; ++e) J[d][e] = 0.0;
+#pragma unroll
+  for (int c = 0; c < NC; ++c) {
+    const uint32_t ct = cornT[c];
+    double v[DIM], dv[DIM];
+#pragma unroll
+    for (int d = 0; d < DIM; ++d) {
+      const int gi = (gt >> (8 * d)) & 255, ci = (ct >> (8 * d)) & 255;
+      v[d] = T.hc[q][gi][ci];
+      dv[d] = T.dhc[q][gi][ci];
+    }
+#pragma unroll
+    for (int d = 0; d < DIM; ++d) {
+      const double hv = tensor3<DIM>(v, dv, d);
+#pragma unroll
+      for (int e = 0; e < DIM; ++e) J[d][e] += hv * X[c * DIM + e];
+    }
+  }
+  if (DIM == 2) {
+    double dt = J[0][0] * J[1][1] - J[0][1] * J[1][0];
+    double inv = 1.0 / dt;
+    jinv[0] = J[1][1] * inv;
+    jinv[1] = -J[0][1] * inv;
+    jinv[2] = -J[1][0] * inv;
+    jinv[3] = J[0][0] * inv;
+    *det = dt;
+  } else {
+    double c00 = J[1][1] * J[2][2] - J[1][2] * J[2][1];
+    double c01 = J[1][2] * J[2][0] - J[1][0] * J[2][2];
+    double c02 = J[1][0] * J[2][1] - J[1][1] * J[2][0];
+    double dt = J[0][0] * c00 + J[0][1] * c01 + J[0][2] * c02;
+    double inv = 1.0 / dt;
+    jinv[0] = c00 * inv;
+    jinv[1] = (J[0][2] * J[2][1] - J[0][1] * J[2][2]) * inv;
+    jinv[2] = (J[0][1] * J[1][2] - J[0][2] * J[1][1]) * inv;
+    jinv[3] = c01 * inv;
+    jinv[4] = (J[0][0] * J[2][2] - J[0][2] * J[2][0]) * inv;
+    jinv[5] = (J[0][2] * J[1][0] - J[0][0] * J[1][2]) * inv;
+    jinv[6] = c02 * inv;
+    jinv[7] = (J[0][1] * J[2][0] - J[0][0] * J[2][1]) * inv;
+    jinv[8] = (J[0][0] * J[1][1] - J[0][1] * J[1][0]) * inv;
+    *det = dt;
+  }
+}
+
+// Moments of one node pair (a,b) over the quadrature points; every entry of K_e, Rw_e and
+// Rd_e of the pair is a fixed linear combination of them (C(g) = the curl matrix of g):
+//   L   = sum_full wd (ga . gb)            M[k][l] = sum_red wd ga[k] gb[l]
+//   N[k] = sum_full wd ha gb[k]            Q[k]    = sum_red wd hb ga[k]
+//   K[c][e]  = delta_ce (L + aw tr M) + ad M[c][e] - aw M[e][c]     (C(ga)^T C(gb) = (ga.gb) I - gb ga^T)
+//   Rw[r][c] = curl_w(r,c,N) + aw curl_v(c,r,Q)        Rd[c] = -N[c] + ad Q[c]
+// 16 accumulators and 7 / 15 FMA-pipe instructions per full / reduced point in 3-D, against 21
+// accumulators and ~25 / ~50 for the entry-by-entry form (PairAcc, kept for the host check).
+template <int DIM>
+struct PairMoments {
+  double L, M[DIM][DIM], N[DIM], Q[DIM];
+  __device__ __forceinline__ void clear() {
+    L = 0.0;
+#pragma unroll
+    for (int k = 0; k < DIM; ++k) {
+      N[k] = 0.0;
+      Q[k] = 0.0;
+#pragma unroll
+      for (int l = 0; l < DIM; ++l) M[k][l] = 0.0;
+    }
+  }
+};
+
+// scr holds one BB-double block per lane (lane-major); write them to dst[blk*BB ..) so that
+// consecutive lanes of a store instruction touch consecutive doubles.  All 32 lanes call.
+template <int BB>
+__device__ __forceinline__ void warp_store_blocks(const double* scr, double* __restrict__ dst,
+                                                  long long blk, bool valid, int lane) {
+  __syncwarp();
+#pragma unroll
+  for (int j = 0; j < BB; ++j) {
+    const int idx = j * 32 + lane;
+    const int src = idx / BB, q = idx - src * BB;
+    const long long bl = __shfl_sync(0xffffffffu, blk, src);
+    const int ok = __shfl_sync(0xffffffffu, (int)valid, src);
+    if (ok) __stcs(dst + bl * BB + q, scr[idx]);
+  }
+  __syncwarp();
+}
+
+// One CTA per (element, tile of row nodes).  Thread = AT row nodes x 1 column node b, so the
+// column-side gradient is loaded once per point and reused AT times from registers; the
+// row-side data is stored interleaved ([node][g0,g1,g2,h]) and read with two broadcast
+// 16-byte loads, the column side planar ([k][node]) and read conflict-free.
+template <int DIM, int AT, int NTH>
+__global__ void __launch_bounds__(NTH, 1)
 elem_kle_kernel(const ElemTables* __restrict__ tab, const double* __restrict__ corners,
-                int64_t e0, int natiles, int TA, int GC, double* __restrict__ ebsK,
+                int64_t e0, int natiles, int ntile, int GC, double* __restrict__ ebsK,
                 double* __restrict__ ebsRw, double* __restrict__ ebsRd) {
   constexpr int NC = 1 << DIM;
   constexpr int DW = DIM == 2 ? 1 : 3;
-  extern __shared__ double smem[];
+  extern __shared__ __align__(16) double smem[];
   const int nn = tab->nn;
   const int64_t el = blockIdx.x / natiles;          // local element in this batch
   const int atile = blockIdx.x % natiles;
-  const int a0 = atile * TA;
-  const int ta = min(TA, nn - a0);
-  const int tid = threadIdx.x, nth = blockDim.x;
+  const int tid = threadIdx.x;
 
-  double* sX = smem;                                 // [NC*DIM]
-  double* sJinv = sX + NC * DIM;                     // [GC*DIM*DIM]
+  double* sA = smem;                                 // [GC][nn][4]  interleaved g0,g1,g2,h
+  double* sB = sA + (size_t)GC * nn * 4;             // [GC][4][nn]  planar
+  double* sJinv = sB + (size_t)GC * nn * 4;          // [GC*DIM*DIM]
   double* sWd = sJinv + GC * DIM * DIM;              // [GC]
-  double* sG = sWd + GC;                             // [GC*DIM*nn]
-  double* sH = sG + (size_t)GC * DIM * nn;           // [GC*nn]
+  double* sX = sWd + GC;                             // [NC*DIM]
+  KleSmemTab& T = *reinterpret_cast<KleSmemTab*>(sX + NC * DIM);
+  uint32_t* sNodeT = reinterpret_cast<uint32_t*>(&T + 1);   // [nn]
+  uint32_t* sCornT = sNodeT + nn;                            // [8]
+  uint32_t* sGpT = sCornT + 8;                               // [npts(full)] then [npts(red)]
+  const int npts_full = tab->rule[RULE_FULL].npts;
 
   if (tid < NC * DIM) sX[tid] = corners[(e0 + el) * NC * DIM + tid];
+  for (int i = tid; i < 2 * kMaxPts1d * kMaxNgl; i += NTH) {
+    const int q = i / (kMaxPts1d * kMaxNgl), r = i % (kMaxPts1d * kMaxNgl);
+    const Rule1D& rl = tab->rule[q == 0 ? RULE_FULL : RULE_RED];
+    (&T.h[q][0][0])[r] = (&rl.h[0][0])[r];
+    (&T.dh[q][0][0])[r] = (&rl.dh[0][0])[r];
+    if (r < kMaxPts1d * 2) {
+      (&T.hc[q][0][0])[r] = (&rl.hc[0][0])[r];
+      (&T.dhc[q][0][0])[r] = (&rl.dhc[0][0])[r];
+    }
+    if (r < kMaxPts1d) T.w[q][r] = rl.w[r];
+  }
+  for (int i = tid; i < nn; i += NTH) sNodeT[i] = pack_t(tab->node_t[i]);
+  if (tid < NC) sCornT[tid] = pack_t(tab->corn_t[tid]);
+  for (int i = tid; i < npts_full; i += NTH) sGpT[i] = pack_t(tab->rule[RULE_FULL].gp_t[i]);
+  for (int i = tid; i < tab->rule[RULE_RED].npts; i += NTH)
+    sGpT[npts_full + i] = pack_t(tab->rule[RULE_RED].gp_t[i]);
 
-  PairAcc<DIM> acc[P];
+  // this thread's pairs: rows a_first .. a_first+AT-1 (clipped), column b
+  const int it = tid / nn;
+  const int b = tid - it * nn;
+  const int a_first = (atile * ntile + it) * AT;
+  const bool active = it < ntile && a_first < nn;
+  int arow[AT];
 #pragma unroll
-  for (int m = 0; m < P; ++m) acc[m].clear();
+  for (int t = 0; t < AT; ++t) arow[t] = min(a_first + t, nn - 1);
 
-  const int npairs = ta * nn;
+  const unsigned nn_rcp = (unsigned)((0x100000000ull + (unsigned)nn - 1) / (unsigned)nn);  // i / nn = umulhi(i, nn_rcp), i < 2^32/nn
+
+  PairMoments<DIM> acc[AT];
+#pragma unroll
+  for (int t = 0; t < AT; ++t) acc[t].clear();
+
   for (int q = 0; q < 2; ++q) {                      // 0: full rule, 1: reduced rule
-    const Rule1D& rule = tab->rule[q == 0 ? RULE_FULL : RULE_RED];
-    const int npts = rule.npts;
+    const int npts = q == 0 ? npts_full : tab->rule[RULE_RED].npts;
+    const uint32_t* gpT = sGpT + (q == 0 ? 0 : npts_full);
     for (int g0 = 0; g0 < npts; g0 += GC) {
       const int gc_n = min(GC, npts - g0);
-      __syncthreads();                               // previous chunk fully consumed (and sX visible)
-      for (int gc = tid; gc < gc_n; gc += nth) {
+      __syncthreads();                               // previous chunk fully consumed (and tables visible)
+      for (int gc = tid; gc < gc_n; gc += NTH) {
+        const uint32_t gt = gpT[g0 + gc];
         double det;
-        point_geometry<DIM>(rule, tab->corn_t, g0 + gc, sX, sJinv + gc * DIM * DIM, &det);
-        sWd[gc] = point_weight<DIM>(rule, g0 + gc) * det;
+        point_geometry_s<DIM>(T, q, gt, sCornT, sX, sJinv + gc * DIM * DIM, &det);
+        double w = T.w[q][gt & 255];
+#pragma unroll
+        for (int d = 1; d < DIM; ++d) w = w * T.w[q][(gt >> (8 * d)) & 255];
+        sWd[gc] = w * det;
       }
       __syncthreads();
-      for (int i = tid; i < gc_n * nn; i += nth) {
-        const int gc = i / nn, b = i - gc * nn;
-        double G[DIM], H;
-        node_gradient<DIM>(rule, tab->node_t[b], g0 + gc, sJinv + gc * DIM * DIM, G, &H);
+      {
+        // unit i -> (point gc, node nb) = (i / nn, i % nn); SU independent units per trip so the
+        // table / J^-1 loads of one overlap the arithmetic of another (2 warps per scheduler only)
+        constexpr int SU = 4;
+        const int units = gc_n * nn;
+        for (int i0 = tid; i0 < units; i0 += SU * NTH) {
+          double G[SU][4];
+          int gcs[SU], nbs[SU];
 #pragma unroll
-        for (int k = 0; k < DIM; ++k) sG[((size_t)gc * DIM + k) * nn + b] = G[k];
-        sH[gc * nn + b] = H;
-      }
-      __syncthreads();
+          for (int u = 0; u < SU; ++u) {
+            const int i = min(i0 + u * NTH, units - 1);
+            const int gc = (int)__umulhi((unsigned)i, nn_rcp), nb = i - gc * nn;
+            gcs[u] = gc;
+            nbs[u] = nb;
+            const uint32_t gt = gpT[g0 + gc], nt = sNodeT[nb];
+            double v[DIM], dv[DIM];
 #pragma unroll
-      for (int m = 0; m < P; ++m) {
-        const int p = tid + m * nth;
-        if (p < npairs) {
-          const int a = a0 + p / nn, b = p % nn;
-          for (int gc = 0; gc < gc_n; ++gc) {
-            double ga[DIM], gb[DIM];
+            for (int d = 0; d < DIM; ++d) {
+              const int gi = (gt >> (8 * d)) & 255, ni = (nt >> (8 * d)) & 255;
+              v[d] = T.h[q][gi][ni];
+              dv[d] = T.dh[q][gi][ni];
+            }
+            double hr[DIM];
+#pragma unroll
+            for (int d = 0; d < DIM; ++d) hr[d] = tensor3<DIM>(v, dv, d);
+            const double* ji = sJinv + gc * DIM * DIM;
 #pragma unroll
             for (int k = 0; k < DIM; ++k) {
-              ga[k] = sG[((size_t)gc * DIM + k) * nn + a];
-              gb[k] = sG[((size_t)gc * DIM + k) * nn + b];
+              double sum = ji[k * DIM] * hr[0];
+#pragma unroll
+              for (int d = 1; d < DIM; ++d) sum += ji[k * DIM + d] * hr[d];
+              G[u][k] = sum;
             }
+            if (DIM == 2) G[u][2] = 0.0;
+            G[u][3] = tensor3<DIM>(v, dv, -1);
+          }
+#pragma unroll
+          for (int u = 0; u < SU; ++u) {
+            if (i0 + u * NTH < units) {
+              double2* dst = reinterpret_cast<double2*>(sA + ((size_t)gcs[u] * nn + nbs[u]) * 4);
+              dst[0] = make_double2(G[u][0], G[u][1]);
+              dst[1] = make_double2(G[u][2], G[u][3]);
+#pragma unroll
+              for (int k = 0; k < 4; ++k)
+                if (k < DIM || k == 3) sB[((size_t)gcs[u] * 4 + k) * nn + nbs[u]] = G[u][k];
+            }
+          }
+        }
+      }
+      __syncthreads();
+      if (active) {
+        if (q == 0) {
+#pragma unroll 2
+          for (int gc = 0; gc < gc_n; ++gc) {
             const double wd = sWd[gc];
-            if (q == 0)
-              acc[m].add_full(wd, ga, sH[gc * nn + a], gb);
-            else
-              acc[m].add_red(wd, ga, gb, sH[gc * nn + b]);
+            double gb[DIM];
+#pragma unroll
+            for (int k = 0; k < DIM; ++k) gb[k] = sB[((size_t)gc * 4 + k) * nn + b];
+#pragma unroll
+            for (int t = 0; t < AT; ++t) {
+              const double2* pa = reinterpret_cast<const double2*>(sA + ((size_t)gc * nn + arow[t]) * 4);
+              const double2 g01 = pa[0], g2h = pa[1];
+              double lap = g01.x * gb[0];
+              lap = fma(g01.y, gb[1], lap);
+              if (DIM == 3) lap = fma(g2h.x, gb[2], lap);
+              acc[t].L = fma(wd, lap, acc[t].L);
+              const double wha = wd * g2h.y;
+#pragma unroll
+              for (int k = 0; k < DIM; ++k) acc[t].N[k] = fma(wha, gb[k], acc[t].N[k]);
+            }
+          }
+        } else {
+#pragma unroll 2
+          for (int gc = 0; gc < gc_n; ++gc) {
+            const double wd = sWd[gc];
+            double gb[DIM];
+#pragma unroll
+            for (int k = 0; k < DIM; ++k) gb[k] = sB[((size_t)gc * 4 + k) * nn + b];
+            const double whb = wd * sB[((size_t)gc * 4 + 3) * nn + b];
+#pragma unroll
+            for (int t = 0; t < AT; ++t) {
+              const double2* pa = reinterpret_cast<const double2*>(sA + ((size_t)gc * nn + arow[t]) * 4);
+              const double2 g01 = pa[0];
+              double ga[3];
+              ga[0] = g01.x;
+              ga[1] = g01.y;
+              if (DIM == 3) ga[2] = pa[1].x;
+#pragma unroll
+              for (int k = 0; k < DIM; ++k) {
+                const double wga = wd * ga[k];
+#pragma unroll
+                for (int l = 0; l < DIM; ++l) acc[t].M[k][l] = fma(wga, gb[l], acc[t].M[k][l]);
+                acc[t].Q[k] = fma(whb, ga[k], acc[t].Q[k]);
+              }
+            }
           }
         }
       }
     }
   }
+  // Epilogue: expand the moments and store block-major ([pair][i][j]).  A lane's block is BB
+  // consecutive doubles, so the warp transposes through a private shared-memory tile and writes
+  // runs of 32 consecutive doubles (the lanes' blocks are adjacent when their b are).
+  __syncthreads();                                   // staging buffers are free now
+  const int lane = tid & 31;
+  double* scr = smem + (size_t)(tid >> 5) * 32 * (DIM * DIM);
 #pragma unroll
-  for (int m = 0; m < P; ++m) {
-    const int p = tid + m * nth;
-    if (p < npairs) {
-      const int a = a0 + p / nn, b = p % nn;
-      const size_t blk = ((size_t)el * nn + a) * nn + b;
+  for (int t = 0; t < AT; ++t) {
+    const int a = a_first + t;
+    const bool valid = active && a < nn;
+    const long long blk = ((long long)el * nn + a) * nn + b;
+    const PairMoments<DIM>& m = acc[t];
+    double tr = m.M[0][0];
 #pragma unroll
-      for (int c = 0; c < DIM; ++c) {
+    for (int k = 1; k < DIM; ++k) tr += m.M[k][k];
+    const double dg = m.L + kAlphaW * tr;
 #pragma unroll
-        for (int e = 0; e < DIM; ++e) ebsK[blk * DIM * DIM + c * DIM + e] = acc[m].K[c][e];
+    for (int c = 0; c < DIM; ++c)
 #pragma unroll
-        for (int e = 0; e < DW; ++e) ebsRw[blk * DIM * DW + c * DW + e] = acc[m].Rw[c][e];
-        ebsRd[blk * DIM + c] = acc[m].Rd[c];
+      for (int e = 0; e < DIM; ++e) {
+        double v = kAlphaD * m.M[c][e] - kAlphaW * m.M[e][c];
+        if (c == e) v += dg;
+        scr[lane * (DIM * DIM) + c * DIM + e] = v;
       }
-    }
+    warp_store_blocks<DIM * DIM>(scr, ebsK, blk, valid, lane);
+#pragma unroll
+    for (int c = 0; c < DIM; ++c)
+#pragma unroll
+      for (int e = 0; e < DW; ++e) {
+        double v = 0.0;
+        if (DIM == 2 || c != e) v = curl_w<DIM>(c, e, m.N) + kAlphaW * curl_v<DIM>(e, c, m.Q);
+        scr[lane * (DIM * DW) + c * DW + e] = v;
+      }
+    warp_store_blocks<DIM * DW>(scr, ebsRw, blk, valid, lane);
+#pragma unroll
+    for (int c = 0; c < DIM; ++c) scr[lane * DIM + c] = kAlphaD * m.Q[c] - m.N[c];
+    warp_store_blocks<DIM>(scr, ebsRd, blk, valid, lane);
   }
 }
 
@@ -165,42 +409,53 @@ elem_ops_kernel(const ElemTables* __restrict__ tab, const double* __restrict__ c
 }
 
 // ---- launchers ----------------------------------------------------------------
-static void kle_launch_shape(const pyn_mesh* mesh, int* TA, int* GC, int* natiles, size_t* smem) {
+struct KleShape {
+  int nth, at, ntile, natiles, gc;
+  size_t smem;
+};
+static KleShape kle_launch_shape(const pyn_mesh* mesh) {
   const int nn = mesh->nn, dim = mesh->dim;
-  const int P = 2, nth = 256;
-  int ta = (P * nth) / nn;
-  if (ta < 1) ta = 1;
-  if (ta > nn) ta = nn;
+  KleShape s;
+  s.nth = nn <= 256 ? 256 : 512;           // nn <= 512 (kMaxNN)
+  s.at = nn <= 256 ? 4 : 2;
+  s.ntile = s.nth / nn;
+  s.natiles = (nn + s.ntile * s.at - 1) / (s.ntile * s.at);
   const int npts_max = mesh->htab.rule[RULE_FULL].npts;
-  const size_t per_pt = (size_t)(dim + 1) * nn * 8 + (dim * dim + 1) * 8;
-  int gc = (int)((size_t)(64 * 1024) / per_pt);
+  const size_t per_pt = (size_t)nn * 64 + (dim * dim + 1) * 8;
+  int gc = (int)((size_t)(144 * 1024) / per_pt);
   if (gc < 1) gc = 1;
   if (gc > npts_max) gc = npts_max;
-  *TA = ta;
-  *GC = gc;
-  *natiles = (nn + ta - 1) / ta;
-  *smem = (size_t)(1 << dim) * dim * 8 + gc * per_pt;
+  const int nchunks = (npts_max + gc - 1) / gc;    // equal chunks: no short last chunk
+  gc = (npts_max + nchunks - 1) / nchunks;
+  s.gc = gc;
+  s.smem = (size_t)(1 << dim) * dim * 8 + gc * per_pt + sizeof(KleSmemTab) +
+           4 * ((size_t)nn + 8 + npts_max + mesh->htab.rule[RULE_RED].npts);
+  const size_t scratch = (size_t)s.nth * dim * dim * 8;      // epilogue transpose tiles
+  if (s.smem < scratch) s.smem = scratch;
+  return s;
 }
 
 int launch_elem_kle(pyn_mesh* mesh, int64_t e0, int64_t ne, double* ebsK, double* ebsRw,
                     double* ebsRd) {
   pyn_ctx* ctx = mesh->ctx;
   if (ne <= 0) return PYN_OK;
-  int TA, GC, natiles;
-  size_t smem;
-  kle_launch_shape(mesh, &TA, &GC, &natiles, &smem);
-  PYN_REQUIRE(ne * natiles < (int64_t)2147483647, "element batch too large for one launch");
-  dim3 grid((unsigned)(ne * natiles)), block(256);
+  const KleShape s = kle_launch_shape(mesh);
+  PYN_REQUIRE(ne * s.natiles < (int64_t)2147483647, "element batch too large for one launch");
+  dim3 grid((unsigned)(ne * s.natiles));
   prof_begin(ctx, PROF_ELEM_KLE);
+#define KLE_CALL(DIM, AT, NTH)                                                                       \
+  do {                                                                                               \
+    PYN_CUDA(cudaFuncSetAttribute(elem_kle_kernel<DIM, AT, NTH>,                                     \
+                                  cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s.smem));        \
+    elem_kle_kernel<DIM, AT, NTH><<<grid, NTH, s.smem, ctx->stream>>>(                               \
+        mesh->dtab.p, mesh->corners.p, e0, s.natiles, s.ntile, s.gc, ebsK, ebsRw, ebsRd);            \
+  } while (0)
   if (mesh->dim == 2) {
-    PYN_CUDA(cudaFuncSetAttribute(elem_kle_kernel<2, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    elem_kle_kernel<2, 2><<<grid, block, smem, ctx->stream>>>(mesh->dtab.p, mesh->corners.p, e0, natiles,
-                                                              TA, GC, ebsK, ebsRw, ebsRd);
+    if (s.nth == 256) KLE_CALL(2, 4, 256); else KLE_CALL(2, 2, 512);
   } else {
-    PYN_CUDA(cudaFuncSetAttribute(elem_kle_kernel<3, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    elem_kle_kernel<3, 2><<<grid, block, smem, ctx->stream>>>(mesh->dtab.p, mesh->corners.p, e0, natiles,
-                                                              TA, GC, ebsK, ebsRw, ebsRd);
+    if (s.nth == 256) KLE_CALL(3, 4, 256); else KLE_CALL(3, 2, 512);
   }
+#undef KLE_CALL
   prof_end(ctx);
   PYN_LAUNCHED(ctx);
   return PYN_OK;

@@ -20,6 +20,7 @@ struct MatSpec {
   const NodeGraph* graph;          // storage graph
   const double* ebs;               // [nel][npairs_src][br*bc]
   int64_t ebs_pairs;               // pairs per element in the store
+  int ebs_ppa = 0;                 // > 0: plane-major store [e][a][plane][m], pair = a*ebs_ppa + m; 0: block-major
   const int32_t* pair_map;         // graph pair id -> store pair id (or -1), NULL = identity
   double sign;
   bool use_rowcls, use_colcls;     // velocity dof classes on rows / columns
