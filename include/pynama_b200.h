@@ -112,6 +112,12 @@ int pyn_halo_exchange(pyn_halo* h, pyn_vec* v, int bs);
 /* Mat of a partitioned mesh: products refresh the ghosts of x first and compute the owned
  * rows only; a KSP on it sums its inner products over ranks. */
 int pyn_mat_set_halo(pyn_mat* m, pyn_halo* h);
+/* Matrix-free products for the KLE matrix K.  on != 0: every product with m
+ * (MatMult in KleSolver.solve / the KSP, kle_solver.py:33-41) is evaluated element by element
+ * with sum-factorised quadrature instead of reading the stored blocks; the stored blocks stay
+ * (export, diagonal blocks for the preconditioner).  m must be the K of pyn_assemble_kle on a
+ * 3-D mesh, ngl 2..6.  Same result up to summation order. */
+int pyn_mat_set_matfree(pyn_mat* m, int on);
 /* Vec of a partitioned mesh: entries [0, owned) are this rank's; dot/norm/sum run over them and
  * are summed over ranks.  owned < 0 (default): plain local Vec. */
 int pyn_vec_set_owned(pyn_vec* v, int64_t owned);

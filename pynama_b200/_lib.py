@@ -64,6 +64,7 @@ _PROTOS = {
     "pyn_halo_destroy": [vp],
     "pyn_halo_exchange": [vp, vp, c_int],
     "pyn_mat_set_halo": [vp, vp],
+    "pyn_mat_set_matfree": [vp, c_int],
     "pyn_vec_set_owned": [vp, c_i64],
     "pyn_mesh_create": [vp, c_int, c_int, c_i64, c_i64, vp, vp, P(vp)],
     "pyn_mesh_destroy": [vp],

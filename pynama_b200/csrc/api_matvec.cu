@@ -3,6 +3,7 @@
 
 #include "elem.cuh"
 #include "spmv.cuh"
+#include "matfree.cuh"
 #include "vec.cuh"
 #include "comm.cuh"
 
@@ -210,6 +211,20 @@ int pyn_mat_set_halo(pyn_mat* m, pyn_halo* h) {
               "pyn_mat_set_halo: layout has %lld local nodes, matrix is %lld x %lld", h ? (long long)h->n_loc : 0LL,
               (long long)m->nbrows, (long long)m->nbcols);
   m->halo = h;
+  return PYN_OK;
+}
+int pyn_mat_set_matfree(pyn_mat* m, int on) {
+  PYN_REQUIRE(m, "null mat");
+  if (!on) {
+    m->mf = nullptr;
+    return PYN_OK;
+  }
+  pyn_mesh* mesh = m->mesh;
+  PYN_REQUIRE(mesh && m->ref_dense && m->br == mesh->dim && m->bc == mesh->dim && m->use_rowcls &&
+                  m->use_colcls && m->pairmask == 1u && m->diagmask == 0xEu,
+              "pyn_mat_set_matfree: not the KLE matrix K of pyn_assemble_kle");
+  if (!mesh->mf) PYN_CHECK(pyn::matfree_create(mesh, &mesh->mf));
+  m->mf = mesh->mf;
   return PYN_OK;
 }
 int pyn_vec_size(pyn_vec* v, int64_t* n) {

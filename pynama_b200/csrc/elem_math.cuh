@@ -26,10 +26,10 @@ PYN_HD double tensor_val(const double (*h)[LD], const double (*dh)[LD], const ui
   return v;
 }
 
-// J = Hrsc . X at one point, its inverse (row-major jinv[k*DIM+d]) and det.
+// J = Hrsc . X at the point with tensor index gt, its inverse (row-major jinv[k*DIM+d]) and det.
 template <int DIM>
-PYN_HD void point_geometry(const Rule1D& r, const uint8_t (*corn_t)[3], int g, const double* X,
-                           double* jinv, double* det) {
+PYN_HD void point_geometry_t(const Rule1D& r, const uint8_t (*corn_t)[3], const uint8_t* gt,
+                             const double* X, double* jinv, double* det) {
   constexpr int NC = 1 << DIM;
   double J[DIM][DIM];
 #pragma unroll
@@ -39,7 +39,7 @@ PYN_HD void point_geometry(const Rule1D& r, const uint8_t (*corn_t)[3], int g, c
   for (int c = 0; c < NC; ++c) {
 #pragma unroll
     for (int d = 0; d < DIM; ++d) {
-      double hv = tensor_val<DIM, 2>(r.hc, r.dhc, r.gp_t[g], corn_t[c], d);
+      double hv = tensor_val<DIM, 2>(r.hc, r.dhc, gt, corn_t[c], d);
 #pragma unroll
       for (int e = 0; e < DIM; ++e) J[d][e] += hv * X[c * DIM + e];
     }
@@ -69,6 +69,12 @@ PYN_HD void point_geometry(const Rule1D& r, const uint8_t (*corn_t)[3], int g, c
     jinv[8] = (J[0][0] * J[1][1] - J[0][1] * J[1][0]) * inv;
     *det = dt;
   }
+}
+// ... at local point g of the rule
+template <int DIM>
+PYN_HD void point_geometry(const Rule1D& r, const uint8_t (*corn_t)[3], int g, const double* X,
+                           double* jinv, double* det) {
+  point_geometry_t<DIM>(r, corn_t, r.gp_t[g], X, jinv, det);
 }
 
 // quadrature weight of local point g: w[c1]*w[c2](*w[c3]) left to right (utilities.py:15-41)

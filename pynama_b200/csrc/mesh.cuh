@@ -2,6 +2,7 @@
 #pragma once
 #include "tables.cuh"
 struct pyn_halo;
+struct pyn_matfree;
 
 namespace pyn {
 
@@ -44,6 +45,8 @@ struct pyn_mesh {
   bool has_stencil = false;
   pyn::DevBuf<int32_t> stencil_of_dense;   // [nn*nn] stencil pair id of dense pair or -1
   double phase_ms[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  pyn_matfree* mf = nullptr;               // matrix-free K data, built on first use
+  ~pyn_mesh();                             // matfree.cu
 };
 
 // Node-block sparse matrix, "row-plane" BSR: the blocks of block-row r are
@@ -69,6 +72,9 @@ struct pyn_mat {
   // row-partitioned run: rows [0, halo->n_own) are this rank's; x gets its ghost entries
   // refreshed before every product (comm.cu)
   pyn_halo* halo = nullptr;
+  // products through the matrix-free element kernels instead of the stored blocks (matfree.cuh);
+  // owned by the mesh
+  pyn_matfree* mf = nullptr;
 };
 
 #define PYN_DISPATCH_BLOCK(br, bc, CALL)                        \

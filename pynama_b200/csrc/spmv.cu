@@ -11,20 +11,10 @@
 #include "spmv.cuh"
 #include "vec.cuh"
 #include "comm.cuh"
+#include "matfree.cuh"
 #include <stdlib.h>
 
 namespace pyn {
-
-// Optional fusions for the Krylov loop: `skip` (device flag, non-zero = solver
-// already converged -> return at once) and DOT (also reduce sum_i y_i*x_i, the
-// p.Ap of CG, into dot_out with the deterministic grid reduction).
-struct SpmvFuse {
-  const double* skip;
-  double* partials;
-  unsigned int* ticket;
-  double* dot_out;
-  P2PRed red;          // nranks > 1: push the dot partial to every rank's window instead
-};
 
 // Column ids of the next pass (and the extent + first column ids of the group's next row)
 // are fetched before the current pass is consumed, which takes the colidx -> x dependent
@@ -113,6 +103,7 @@ static int spmv_launch(pyn_mat* m, double alpha, const double* x, double beta, c
     nrows = m->halo->n_own;
     if (nrows == 0) return PYN_OK;
   }
+  if (m->mf) return matfree_apply(m, nrows, alpha, x, beta, z, y, dot, fuse);
   const double avg = m->nbrows ? (double)m->nblocks / (double)m->nbrows : 0.0;
   const int G = avg > 24.0 ? 32 : (avg > 10.0 ? 16 : 8);
   // one wave: 4 resident CTAs per SM (__launch_bounds__(256, 4))

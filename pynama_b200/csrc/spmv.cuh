@@ -4,6 +4,17 @@
 #include "comm.cuh"
 
 namespace pyn {
+// Optional fusions for the Krylov loop: `skip` (device flag, non-zero = solver
+// already converged -> return at once) and DOT (also reduce sum_i y_i*x_i, the
+// p.Ap of CG, into dot_out with the deterministic grid reduction).
+struct SpmvFuse {
+  const double* skip;
+  double* partials;
+  unsigned int* ticket;
+  double* dot_out;
+  P2PRed red;          // nranks > 1: push the dot partial to every rank's window instead
+};
+
 // y = alpha*A*x + beta*z (z may be NULL when beta == 0; z may alias y)
 int spmv(pyn_mat* m, double alpha, const double* x, double beta, const double* z, double* y);
 // red != NULL with nranks > 1: the dot partial is pushed to every rank's window (kind 0) instead of dot_out

@@ -603,11 +603,19 @@ class Mat:
         self._name = name
         self._shape = None
         self._layout = None
+        self._matfree = False
 
     def _setLayout(self, layout):
         """matrix of a row-partitioned mesh: owned rows only, ghost refresh before each product"""
         self._layout = layout
         call("pyn_mat_set_halo", self._h, layout._h if layout is not None else None)
+        return self
+
+    def setMatFree(self, on=True):
+        """products of the KLE matrix K evaluated element by element (sum-factorised quadrature)
+        instead of from the stored blocks; same result up to summation order"""
+        call("pyn_mat_set_matfree", self._h, 1 if on else 0)
+        self._matfree = bool(on)
         return self
 
     def _info(self):

@@ -10,7 +10,7 @@ kle_solver.py:54-64); how those are honoured on the GPU is described in
 """
 import logging
 
-from ..petsc import COMM_WORLD, KSP, PC
+from ..petsc import COMM_WORLD, KSP, PC, Options
 
 
 class KleSolver:
@@ -23,6 +23,10 @@ class KleSolver:
     def setUp(self):
         solveType = self.mat.bcType
         K = self.mat.K
+        # -kle_matfree 1: the products with K inside the Krylov loop are evaluated element by
+        # element (sum-factorised quadrature) instead of from the stored blocks
+        if Options().getBool("kle_matfree", False):
+            K.setMatFree(True)
         self.solver = KspSolver()
         self.solver.createSolver(K)
         self.__vel = K.createVecRight()
