@@ -53,6 +53,8 @@ def parse_args():
     ap.add_argument("--no-matfree", action="store_true", help="skip the extra matrix-free (-kle_matfree 1) pass")
     ap.add_argument("--fischer", type=int, default=8,
                     help="-ksp_fischer_guess 1,<n>: initial guess from the last n solutions (0: off, PETSc default)")
+    ap.add_argument("--opt", action="append", default=[], metavar="NAME=VALUE",
+                    help="extra options-database entry, e.g. --opt ksp_cg_single_reduction=1 (repeatable)")
     ap.add_argument("--check-every", type=int, default=0, help="KSP status poll interval (0: library default)")
     return ap.parse_args()
 
@@ -139,6 +141,9 @@ def build_problem(args):
         o.setValue("ksp_fischer_guess", f"1,{args.fischer}")
     o.setValue("ts_adapt_type", "none")
     o.setValue("ts_dt", args.dt)
+    for kv in args.opt:
+        name, _, val = kv.partition("=")
+        o.setValue(name, val or "1")
     fem = BaseProblem(case_config(args.nelem, args.ngl), case="taylor-green3d")
     fem.setUp()
     t0 = time.perf_counter()
@@ -279,7 +284,8 @@ def run_b200(args, rank, world):
                                "(BASELINE.json configs[1]); one RK5BS time step = 7 evalRHS",
                    "dofs": int(ndof), "nodes": int(ndof // 3), "ksp": f"cg+{args.pc}", "ksp_rtol": args.rtol,
                    "ksp_options": f"-ksp_type cg -pc_type {args.pc} -ksp_rtol {args.rtol:g}" +
-                                  (f" -ksp_fischer_guess 1,{args.fischer}" if args.fischer > 0 else ""),
+                                  (f" -ksp_fischer_guess 1,{args.fischer}" if args.fischer > 0 else "") +
+                                  "".join(" -" + kv.replace("=", " ") for kv in args.opt),
                    "dt": args.dt, "rhs_evals_per_step": evals / args.steps,
                    "ksp_iterations_per_step": its / args.steps, "ksp_solves_per_step": solves / args.steps,
                    "parallelism": "1 GPU" if world == 1 else

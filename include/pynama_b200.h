@@ -242,6 +242,10 @@ int pyn_ksp_set_tolerances(pyn_ksp* k, double rtol, double atol, int maxit, int 
 /* KSPSetUseFischerGuess / -ksp_fischer_guess <model>,<size>: model 1 (A-conjugate projection
  * of the new right-hand side on the last <size> <= 8 solution increments) forms the initial
  * guess; size 0 switches it off (default, as in PETSc). */
+/* KSPCGUseSingleReduction / -ksp_cg_single_reduction: CG with the inner products of an
+ * iteration merged into one reduction (fused into the product kernel) and the rest of the
+ * recurrence in one vector kernel: 2 launches and 1 reduction per iteration instead of 3 and 2. */
+int pyn_ksp_set_cg_single_reduction(pyn_ksp* k, int on);
 int pyn_ksp_set_fischer_guess(pyn_ksp* k, int model, int size);
 /* x: initial guess in, solution out (KSP.__call__(b, x), kle_solver.py:35).
  * reason > 0 converged (2 rtol, 3 atol), < 0 diverged (-3 max iterations). */

@@ -20,7 +20,7 @@ constexpr long long kSpinMax = 40000000LL;   // bounded spin (~ seconds): a lost
 // bits.  Slots are double-buffered by sequence parity.  No NCCL call, no extra launch: the
 // collective rides inside the compute kernels.
 struct RedWindow {                      // device layout of one rank's reduction window
-  double val[2][2][kMaxRanks][2];       // [kind][parity][source rank][value]
+  double val[2][2][kMaxRanks][4];       // [kind][parity][source rank][value]
   unsigned long long flag[2][2][kMaxRanks];
 };
 struct P2PRed {                         // by-value kernel argument

@@ -34,6 +34,7 @@ enum {
   S_DTOL = 9,
   S_LRZ = 10,  // this rank's r.z / z.z partials (row-partitioned runs), summed in place by
   S_LZZ = 11,  // an allreduce before the bookkeeping kernel
+  S_SR = 12,   // single-reduction CG: {w.u, r.u, u.u} of the current iterate (3 slots)
   S_COUNT = 16
 };
 
@@ -215,6 +216,150 @@ cg_update_kernel(int pc, const double* __restrict__ pcd, const double* __restric
   }
 }
 
+// ---- single-synchronisation CG (PETSc -ksp_cg_single_reduction; Chronopoulos & Gear) ---------
+// u = M^-1 r, w = A u.  delta = w.u is fused into the product kernel as before; gamma = r.u and
+// u.u of the NEXT iterate are reduced by the vector kernel that produces r and u, so they travel
+// while the next product runs and an iteration has ONE point where it waits for reductions:
+//   beta = gamma/gamma_old, alpha = gamma/(delta - beta*gamma/alpha_old),
+//   p = u + beta p, s = w + beta s, x += alpha p, r -= alpha s, u = M^-1 r.
+// Two launches per iteration instead of three.  Scalars of iteration i live in slots [i & 1]
+// (S_RZ0/1: gamma, S_LRZ/S_LZZ: alpha) so that the CTA doing the bookkeeping never overwrites
+// what the others still read; S_SR+1/+2 are rewritten by the last CTA only after every CTA has
+// read them (they deposit their partials after reading).
+template <int B>
+__global__ void __launch_bounds__(256)
+cg_sr_update_kernel(int pc, const double* __restrict__ pcd, double* __restrict__ u,
+                    const double* __restrict__ w, double* __restrict__ p, double* __restrict__ s,
+                    double* __restrict__ x, double* __restrict__ r, int64_t nnodes, double* S, int it,
+                    int maxit, double* partials, unsigned int* ticket, P2PRed red) {
+  __shared__ double sm[64];
+  __shared__ double s_sum[3];
+  __shared__ int s_ok;
+  __shared__ bool is_last;
+  if (S[S_DONE] != 0.0) return;
+  double delta, gamma, uu;
+  if (red.nranks > 1) {                    // the ranks' partials arrive in this rank's window
+    if (threadIdx.x < 32) {
+      double o[1], g[2] = {0.0, 0.0};
+      bool ok = p2p_wait_sum<1>(red, 0, o);
+      if (it > 0) {                        // pushed by the previous iteration's vector kernel
+        P2PRed prev = red;
+        prev.seq = red.seq - 1;
+        ok = p2p_wait_sum<2>(prev, 1, g) && ok;
+      }
+      if (threadIdx.x == 0) {
+        s_sum[0] = o[0];
+        s_sum[1] = g[0];
+        s_sum[2] = g[1];
+        s_ok = ok ? 1 : 0;
+      }
+    }
+    __syncthreads();
+    if (!s_ok) {
+      if (threadIdx.x == 0 && blockIdx.x == 0) {
+        S[S_REASON] = -100.0;              // a peer never answered
+        S[S_DONE] = 1.0;
+      }
+      return;
+    }
+    delta = s_sum[0];
+    gamma = it > 0 ? s_sum[1] : S[S_SR + 1];
+    uu = it > 0 ? s_sum[2] : S[S_SR + 2];
+  } else {
+    delta = S[S_SR];
+    gamma = S[S_SR + 1];
+    uu = S[S_SR + 2];
+  }
+  const int cur = it & 1;
+  const double gamma_old = S[cur ? S_RZ0 : S_RZ1];
+  const double alpha_old = S[cur ? S_LRZ : S_LZZ];
+  const double beta = it == 0 ? 0.0 : gamma / gamma_old;
+  const double denom = it == 0 ? delta : delta - beta * gamma / alpha_old;
+  const double alpha = gamma / denom;
+  const double rn = sqrt(uu);
+  // every CTA evaluates the same test on the same numbers; CTA 0 records the outcome
+  int stop = 0;
+  double reason = 0.0;
+  if (!(rn == rn) || !(delta == delta)) {
+    stop = 1; reason = -9.0;
+  } else if (rn <= S[S_TTOL]) {
+    stop = 1; reason = S[S_REASON] == 3.0 ? 3.0 : 2.0;
+  } else if (rn >= S[S_DTOL]) {
+    stop = 1; reason = -4.0;
+  } else if (it >= maxit) {
+    stop = 1; reason = -3.0;
+  } else if (!(denom == denom) || denom == 0.0) {
+    stop = 1; reason = -9.0;
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    S[S_ZZ] = uu;
+    S[S_RNORM] = rn;
+    S[S_PW] = delta;
+    if (stop) {
+      S[S_REASON] = reason;
+      S[S_DONE] = 1.0;
+    } else {
+      S[cur ? S_RZ1 : S_RZ0] = gamma;
+      S[cur ? S_LZZ : S_LRZ] = alpha;
+      S[S_ITS] = (double)(it + 1);
+    }
+  }
+  if (stop) return;
+  double v[2] = {0.0, 0.0};
+  for (int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; n < nnodes;
+       n += (int64_t)gridDim.x * blockDim.x) {
+    double rr[B], zz[B];
+#pragma unroll
+    for (int i = 0; i < B; ++i) {
+      const int64_t j = n * B + i;
+      const double pj = it == 0 ? u[j] : u[j] + beta * p[j];
+      const double sj = it == 0 ? w[j] : w[j] + beta * s[j];
+      p[j] = pj;
+      s[j] = sj;
+      x[j] += alpha * pj;
+      rr[i] = r[j] - alpha * sj;
+      r[j] = rr[i];
+    }
+    apply_pc_node<B>(pc, pcd, n, rr, zz);
+#pragma unroll
+    for (int i = 0; i < B; ++i) {
+      u[n * B + i] = zz[i];
+      v[0] += rr[i] * zz[i];
+      v[1] += zz[i] * zz[i];
+    }
+  }
+  // gamma and u.u of the next iterate: grid reduction, then to S (or to every rank's window)
+  block_reduce<2>(v, sm);
+  if (threadIdx.x == 0) {
+    partials[(size_t)blockIdx.x * 2 + 0] = v[0];
+    partials[(size_t)blockIdx.x * 2 + 1] = v[1];
+    __threadfence();
+    is_last = (atomicAdd(ticket, 1u) == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  if (wid < 2) {
+    double t = 0.0;
+    for (unsigned int b = lane; b < gridDim.x; b += 32) t += partials[(size_t)b * 2 + wid];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+    if (lane == 0) sm[wid] = t;
+  }
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    if (red.nranks > 1) {
+      double t[2] = {sm[0], sm[1]};
+      p2p_push<2>(red, 1, t);
+    } else if (threadIdx.x == 0) {
+      S[S_SR + 1] = sm[0];
+      S[S_SR + 2] = sm[1];
+    }
+    if (threadIdx.x == 0) *ticket = 0u;
+  }
+}
+
 // step (3): p = z + (rz_new/rz_old) p
 __global__ void __launch_bounds__(256)
 cg_direction_kernel(const double* __restrict__ z, double* __restrict__ p, int64_t n, const double* S,
@@ -238,6 +383,8 @@ __global__ void cg_init_scalars_kernel(double* S, const double* rz_zz, const dou
     reason_if = 3.0;
   }
   S[S_RZ0] = rz_zz[0];
+  S[S_SR + 1] = rz_zz[0];      // single-reduction CG reads gamma_0 = r.u and u.u of the start here
+  S[S_SR + 2] = rz_zz[1];
   S[S_RZ1] = 0.0;
   S[S_PW] = 0.0;
   S[S_ZZ] = rz_zz[1];
@@ -389,6 +536,8 @@ struct pyn_ksp {
   int B = 0;
   int64_t n = 0, nnodes = 0;
   DevBuf<double> pcd, r, z, p, w, S, tmp2;
+  bool single_reduction = false;        // -ksp_cg_single_reduction
+  DevBuf<double> sr_s;                  // s = A p of the single-reduction recurrence
   double* status_host = nullptr;  // pinned [2][S_COUNT]
   cudaEvent_t ev[2] = {nullptr, nullptr};
   bool pc_ready = false;
@@ -435,6 +584,7 @@ static int ksp_solve_cg(pyn_ksp* k, const double* b, double* x, int* its, int* r
   double* S = k->S.p;
   const int gridn = grid_for(ctx, nn > 0 ? nn : 1, 256);
   if (!k->pc_ready) PYN_CHECK(ksp_setup_pc<B>(k));
+  if (k->single_reduction && k->sr_s.n < k->n) PYN_CHECK(k->sr_s.alloc(ctx, k->n));
   const bool fischer = k->fischer_m > 0;
   const int gridv = grid_for(ctx, n > 0 ? n : 1, 256);
   if (fischer && k->fischer_n > 0) {        // x <- sum_i (x~_i . b) x~_i
@@ -477,6 +627,20 @@ static int ksp_solve_cg(pyn_ksp* k, const double* b, double* x, int* its, int* r
     for (int j = 0; j < todo; ++j, ++it) {
       const int parity = it & 1;
       P2PRed red = p2p ? p2p_next(ctx) : red_off;
+      if (k->single_reduction) {
+        // w = A u with w.u fused; then the whole recurrence (and r.u, u.u of the next iterate)
+        // in one vector kernel
+        PYN_CHECK(spmv_dot(k->A, k->z.p, k->w.p, S + S_SR, S + S_DONE, &red));
+        if (dist && !p2p) PYN_CHECK(comm_allreduce_sum(ctx, S + S_SR, 1));
+        prof_begin(ctx, PROF_CG_UPDATE);
+        cg_sr_update_kernel<B><<<gridn, 256, 0, ctx->stream>>>(k->pc, k->pcd.p, k->z.p, k->w.p, k->p.p,
+                                                               k->sr_s.p, x, k->r.p, nn, S, it, k->maxit,
+                                                               ctx->red_partials, ctx->red_ticket, red);
+        prof_end(ctx);
+        PYN_LAUNCHED(ctx);
+        if (dist && !p2p) PYN_CHECK(comm_allreduce_sum(ctx, S + S_SR + 1, 2));
+        continue;
+      }
       PYN_CHECK(spmv_dot(k->A, k->p.p, k->w.p, S + S_PW, S + S_DONE, &red));
       if (dist && !p2p) PYN_CHECK(comm_allreduce_sum(ctx, S + S_PW, 1));
       prof_begin(ctx, PROF_CG_UPDATE);
@@ -842,6 +1006,12 @@ int pyn_ksp_set_tolerances(pyn_ksp* k, double rtol, double atol, int maxit, int 
   if (atol >= 0) k->atol = atol;
   if (maxit > 0) k->maxit = maxit;
   if (restart > 0) k->restart = restart;
+  return PYN_OK;
+}
+
+int pyn_ksp_set_cg_single_reduction(pyn_ksp* k, int on) {
+  PYN_REQUIRE(k, "null ksp");
+  k->single_reduction = on != 0;
   return PYN_OK;
 }
 

@@ -423,15 +423,18 @@ mf_apply_kernel(int64_t nel, const int32_t* __restrict__ nodes_t, const int32_t*
 }
 
 // ---- node kernel: y[r] = alpha * (free ? sum of the element results : x[r]) + beta z[r] --------
-template <bool DOT>
+template <int NDOT>
 __global__ void __launch_bounds__(256)
 mf_gather_kernel(int64_t nrows, const int64_t* __restrict__ n2e_ptr, const int2* __restrict__ n2e,
                  const double* __restrict__ ye, int nn, const uint8_t* __restrict__ cls,
                  const double* __restrict__ x, double alpha, double beta, const double* __restrict__ z,
                  double* __restrict__ y, SpmvFuse fuse) {
-  __shared__ double red_sm[32];
+  constexpr int NV = NDOT > 0 ? NDOT : 1;
+  __shared__ double red_sm[NV * 32];
   if (fuse.skip && *fuse.skip != 0.0) return;
-  double dotacc[1] = {0.0};
+  double dotacc[NV];
+#pragma unroll
+  for (int k = 0; k < NV; ++k) dotacc[k] = 0.0;
   for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < nrows;
        r += (int64_t)gridDim.x * blockDim.x) {
     double acc[3] = {0.0, 0.0, 0.0};
@@ -450,15 +453,21 @@ mf_gather_kernel(int64_t nrows, const int64_t* __restrict__ n2e_ptr, const int2*
       double out = alpha * (cls[dof] == 0 ? acc[c] : xv);
       if (beta != 0.0) out += beta * z[dof];
       y[dof] = out;
-      if (DOT) dotacc[0] += out * xv;
+      if (NDOT > 0) {
+        dotacc[0] += out * xv;
+        if (NDOT == 3) {
+          dotacc[NV > 1 ? 1 : 0] += fuse.dot_r[dof] * xv;
+          dotacc[NV > 2 ? 2 : 0] += xv * xv;
+        }
+      }
     }
   }
-  if (DOT) {
-    block_reduce<1>(dotacc, red_sm);
+  if (NDOT > 0) {
+    block_reduce<NV>(dotacc, red_sm);
     if (fuse.red.nranks > 1)
-      grid_reduce_push<1>(dotacc, fuse.partials, fuse.ticket, fuse.red, 0);
+      grid_reduce_push<NV>(dotacc, fuse.partials, fuse.ticket, fuse.red, 0);
     else
-      grid_reduce_finish<1>(dotacc, fuse.partials, fuse.ticket, fuse.dot_out);
+      grid_reduce_finish<NV>(dotacc, fuse.partials, fuse.ticket, fuse.dot_out);
   }
 }
 
@@ -494,12 +503,13 @@ int matfree_apply(pyn_mat* m, int64_t nrows, double alpha, const double* x, doub
   }
   int grid = grid_for(ctx, nrows, 256, 8);
   if (grid > kRedMaxBlocks) grid = kRedMaxBlocks;
-  if (dot)
-    mf_gather_kernel<true><<<grid, 256, 0, ctx->stream>>>(nrows, mesh->n2e_ptr.p, mesh->n2e.p, mf->ye.p,
-                                                          mesh->nn, mesh->dofcls.p, x, alpha, beta, z, y, fuse);
-  else
-    mf_gather_kernel<false><<<grid, 256, 0, ctx->stream>>>(nrows, mesh->n2e_ptr.p, mesh->n2e.p, mf->ye.p,
-                                                           mesh->nn, mesh->dofcls.p, x, alpha, beta, z, y, fuse);
+#define MF_GATHER(NDOT)                                                                                   \
+  mf_gather_kernel<NDOT><<<grid, 256, 0, ctx->stream>>>(nrows, mesh->n2e_ptr.p, mesh->n2e.p, mf->ye.p,   \
+                                                        mesh->nn, mesh->dofcls.p, x, alpha, beta, z, y, fuse)
+  if (dot && fuse.dot_r) MF_GATHER(3);
+  else if (dot) MF_GATHER(1);
+  else MF_GATHER(0);
+#undef MF_GATHER
   prof_end(ctx);
   PYN_LAUNCHED(ctx);
   return PYN_OK;

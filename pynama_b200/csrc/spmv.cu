@@ -26,15 +26,18 @@ namespace pyn {
 // producer warp (cp.async.bulk + mbarrier, 128 KB ring) was correct but 6x slower -- 16
 // consumer warps each holding a whole row (<= 24.7 KB) span more than the ring, so the
 // warps serialise (profiles/README.md, round 1).
-template <int BR, int BC, int G, bool DOT>
+template <int BR, int BC, int G, int NDOT>
 __global__ void __launch_bounds__(256, 4)
 spmv_kernel(int64_t nbrows, const int64_t* __restrict__ rowptr, const int32_t* __restrict__ colidx,
              const double* __restrict__ val, const double* __restrict__ x, double alpha, double beta,
              const double* __restrict__ z, double* __restrict__ y, SpmvFuse fuse) {
   constexpr int BB = BR * BC;
-  __shared__ double red_sm[32];
+  constexpr int NV = NDOT > 0 ? NDOT : 1;
+  __shared__ double red_sm[NV * 32];
   if (fuse.skip && *fuse.skip != 0.0) return;
-  double dotacc[1] = {0.0};
+  double dotacc[NV];
+#pragma unroll
+  for (int k = 0; k < NV; ++k) dotacc[k] = 0.0;
   const int lane = threadIdx.x & (G - 1);
   const int64_t grp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / G;
   const int64_t ngrp = ((int64_t)gridDim.x * blockDim.x) / G;
@@ -76,7 +79,14 @@ spmv_kernel(int64_t nbrows, const int64_t* __restrict__ rowptr, const int32_t* _
         double out = alpha * acc[i];
         if (beta != 0.0) out += beta * z[r * BR + i];
         y[r * BR + i] = out;
-        if (DOT) dotacc[0] += out * x[r * BC + i];
+        if (NDOT > 0) {
+          const double xr = x[r * BC + i];
+          dotacc[0] += out * xr;
+          if (NDOT == 3) {
+            dotacc[NV > 1 ? 1 : 0] += fuse.dot_r[r * BR + i] * xr;
+            dotacc[NV > 2 ? 2 : 0] += xr * xr;
+          }
+        }
       }
     }
     r = rn;
@@ -84,12 +94,12 @@ spmv_kernel(int64_t nbrows, const int64_t* __restrict__ rowptr, const int32_t* _
     p0 = p0n;
     nb = nbn;
   }
-  if (DOT) {
-    block_reduce<1>(dotacc, red_sm);
+  if (NDOT > 0) {
+    block_reduce<NV>(dotacc, red_sm);
     if (fuse.red.nranks > 1)
-      grid_reduce_push<1>(dotacc, fuse.partials, fuse.ticket, fuse.red, 0);
+      grid_reduce_push<NV>(dotacc, fuse.partials, fuse.ticket, fuse.red, 0);
     else
-      grid_reduce_finish<1>(dotacc, fuse.partials, fuse.ticket, fuse.dot_out);
+      grid_reduce_finish<NV>(dotacc, fuse.partials, fuse.ticket, fuse.dot_out);
   }
 }
 
@@ -118,13 +128,19 @@ static int spmv_launch(pyn_mat* m, double alpha, const double* x, double beta, c
         set_error("spmv+dot needs square blocks");       \
         return PYN_E_INVALID;                            \
       }                                                  \
-      if (G == 32) LAUNCH(BR, BC, 32, true);             \
-      else if (G == 16) LAUNCH(BR, BC, 16, true);        \
-      else LAUNCH(BR, BC, 8, true);                      \
+      if (fuse.dot_r) {                                  \
+        if (G == 32) LAUNCH(BR, BC, 32, 3);              \
+        else if (G == 16) LAUNCH(BR, BC, 16, 3);         \
+        else LAUNCH(BR, BC, 8, 3);                       \
+      } else {                                           \
+        if (G == 32) LAUNCH(BR, BC, 32, 1);              \
+        else if (G == 16) LAUNCH(BR, BC, 16, 1);         \
+        else LAUNCH(BR, BC, 8, 1);                       \
+      }                                                  \
     } else {                                             \
-      if (G == 32) LAUNCH(BR, BC, 32, false);            \
-      else if (G == 16) LAUNCH(BR, BC, 16, false);       \
-      else LAUNCH(BR, BC, 8, false);                     \
+      if (G == 32) LAUNCH(BR, BC, 32, 0);                \
+      else if (G == 16) LAUNCH(BR, BC, 16, 0);           \
+      else LAUNCH(BR, BC, 8, 0);                         \
     }                                                    \
   } while (0)
   prof_begin(ctx, dot ? PROF_SPMV_KSP : PROF_SPMV);
@@ -151,6 +167,20 @@ int spmv_dot(pyn_mat* m, const double* x, double* y, double* dot_out, const doub
   f.partials = ctx->red_partials;
   f.ticket = ctx->red_ticket;
   f.dot_out = dot_out;
+  if (red) f.red = *red;
+  return spmv_launch(m, 1.0, x, 0.0, nullptr, y, true, f);
+}
+
+int spmv_dot3(pyn_mat* m, const double* x, double* y, const double* r, double* out3, const double* skip,
+              const P2PRed* red) {
+  pyn_ctx* ctx = m->ctx;
+  SpmvFuse f;
+  memset(&f, 0, sizeof(f));
+  f.skip = skip;
+  f.partials = ctx->red_partials;
+  f.ticket = ctx->red_ticket;
+  f.dot_out = out3;
+  f.dot_r = r;
   if (red) f.red = *red;
   return spmv_launch(m, 1.0, x, 0.0, nullptr, y, true, f);
 }

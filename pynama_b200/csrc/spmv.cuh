@@ -13,6 +13,8 @@ struct SpmvFuse {
   unsigned int* ticket;
   double* dot_out;
   P2PRed red;          // nranks > 1: push the dot partial to every rank's window instead
+  // single-reduction CG: with dot_r the reduction has three values, {y.x, dot_r.x, x.x}
+  const double* dot_r;
 };
 
 // y = alpha*A*x + beta*z (z may be NULL when beta == 0; z may alias y)
@@ -20,6 +22,9 @@ int spmv(pyn_mat* m, double alpha, const double* x, double beta, const double* z
 // red != NULL with nranks > 1: the dot partial is pushed to every rank's window (kind 0) instead of dot_out
 int spmv_dot(pyn_mat* m, const double* x, double* y, double* dot_out, const double* skip,
              const P2PRed* red = nullptr);
+// y = A x and out3 = {x.y, r.x, x.x} in one pass (single-reduction CG)
+int spmv_dot3(pyn_mat* m, const double* x, double* y, const double* r, double* out3, const double* skip,
+              const P2PRed* red = nullptr);
 int diag_blocks(pyn_mat* m, double* dblk);   // [nbrows][b][b]
 int scale_rows(pyn_mat* m, const double* l);
 int mat_add_new(pyn_mat* a, pyn_mat* b, pyn_mat** out);

@@ -802,6 +802,7 @@ class KSP:
         self._its, self._reason, self._rnorm = 0, 0, 0.0
         self._guess_nonzero = True
         self._fischer = (0, 0)              # (model, size); KSPSetUseFischerGuess, off by default
+        self._cg_single_reduction = False   # KSPCGUseSingleReduction
         self._log = logging.getLogger("KSP")
 
     def create(self, comm=None):
@@ -847,9 +848,17 @@ class KSP:
         self._fischer = (int(model), int(size))
         self._drop()
 
+    def setCGSingleReduction(self, flag=True):
+        """KSPCGUseSingleReduction: one fused reduction and two launches per CG iteration"""
+        self._cg_single_reduction = bool(flag)
+        self._drop()
+
     def setFromOptions(self):
         o = Options()
         self._type = o.getString("ksp_type", self._type)
+        sr = o.getBool("ksp_cg_single_reduction", None)
+        if sr is not None:
+            self._cg_single_reduction = sr
         self._pc.setFromOptions()
         self.rtol = o.getReal("ksp_rtol", self.rtol)
         self.atol = o.getReal("ksp_atol", self.atol)
@@ -891,6 +900,8 @@ class KSP:
              int(self.restart))
         if self._fischer[1] > 0:
             call("pyn_ksp_set_fischer_guess", h, self._fischer[0], min(self._fischer[1], 8))
+        if self._cg_single_reduction and ktype == "cg":
+            call("pyn_ksp_set_cg_single_reduction", h, 1)
 
     def solve(self, b, x):
         self.setUp()

@@ -32,6 +32,11 @@ def main():
         o.setValue(k, v)
     if os.environ.get("DIST_FISCHER", "0") != "0":
         o.setValue("ksp_fischer_guess", "1," + os.environ["DIST_FISCHER"])
+    for name in ("ksp_cg_single_reduction", "kle_matfree"):          # DIST_OPTS="name=value,name=value"
+        o.delValue(name)
+    for kv in filter(None, os.environ.get("DIST_OPTS", "").split(",")):
+        name, val = kv.split("=")
+        o.setValue(name, val)
     cfg = bench.case_config(nelem[0], ngl)
     cfg["domain"]["box-mesh"]["nelem"] = nelem
     fem = BaseProblem(cfg, case="taylor-green3d")

@@ -47,6 +47,20 @@ def test_partitioned_run_other_ksp_types(ksp):
     _run(2, 29551, {"DIST_KSP": ksp})
 
 
+@pytest.mark.parametrize("opts", ["ksp_cg_single_reduction=1", "kle_matfree=1",
+                                  "ksp_cg_single_reduction=1,kle_matfree=1"])
+@pytest.mark.parametrize("p2p", ["1", "0"])
+def test_partitioned_run_single_reduction_and_matfree(opts, p2p):
+    """2 ranks: single-reduction CG and the matrix-free K, over peer-memory windows and over NCCL"""
+    env = {"DIST_OPTS": opts, "PYN_P2P": p2p, "DIST_NGL": "4"}
+    if _ngpus() < 2:
+        r = subprocess.run([sys.executable, SCRIPT], capture_output=True, text=True, timeout=600,
+                           env=dict(os.environ, **env))
+        assert r.returncode == 0, r.stdout[-3000:] + "\n" + r.stderr[-3000:]
+        return
+    _run(2, 29553, env)
+
+
 @pytest.mark.parametrize("nproc", [2, 4, 8])
 def test_partitioned_run_matches_oracle(nproc):
     if _ngpus() < nproc:

@@ -269,3 +269,40 @@ def test_gmres_and_bcgs_vs_direct(ktype, pc):
     assert ksp.getConvergedReason() > 0
     ref2 = spl.spsolve(w2["K"].tocsc(), b2)
     assert np.linalg.norm(x2.getArray() - ref2) <= 1e-8 * np.linalg.norm(ref2)
+
+
+@pytest.mark.parametrize("pc", ["jacobi", "bjacobi", "none"])
+def test_cg_single_reduction_matches_cg(pc):
+    """-ksp_cg_single_reduction (KSPCGUseSingleReduction): same solution and iteration count (+-2)
+    as the two-reduction recurrence, 3-D and 2-D"""
+    from pynama_b200.petsc import KSP, PC, Vec
+    for nelem, ngl in (([4, 4, 3], 4), ([6, 5], 5)):
+        mesh, dm, tab = _setup(nelem, ngl, 0.1)
+        dim = len(nelem)
+        cls = fs_classes(mesh)
+        dm.set_dof_class(cls)
+        K = dm.assemble_kle("FS")["K"]
+        rng = np.random.default_rng(5)
+        xs = np.where(cls == 0, rng.uniform(-1, 1, mesh.nnodes * dim), -0.25)
+        b = K * Vec().createWithArray(xs)
+        res = {}
+        for sr in (False, True):
+            ksp = KSP().create()
+            ksp.setType("cg")
+            p = PC().create()
+            p.setType(pc)
+            ksp.setPC(p)
+            ksp.setCGSingleReduction(sr)
+            ksp.setOperators(K)
+            ksp.setTolerances(rtol=1e-11, max_it=20000)
+            x = Vec(mesh.nnodes * dim)
+            ksp.solve(b, x)
+            assert ksp.getConvergedReason() == 2, (sr, ksp.getConvergedReason())
+            res[sr] = (x.getArray(), ksp.getIterationNumber(), ksp.getResidualNorm())
+        assert np.abs(res[True][0] - xs).max() <= 1e-7
+        assert np.abs(res[True][0] - res[False][0]).max() <= 1e-8
+        assert abs(res[True][1] - res[False][1]) <= 2, (res[True][1], res[False][1])
+    # converged on entry: zero iterations
+    x = Vec().createWithArray(xs)
+    ksp.solve(b, x)
+    assert ksp.getIterationNumber() <= 1

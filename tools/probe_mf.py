@@ -47,4 +47,19 @@ for mf in (False, True):
         ctx.sync(); ctx.timer_start()
         ksp.solve(rhs, sol)
         ms = ctx.timer_stop()
+    ctx.prof_enable(True); sol = Vec(n); ksp.solve(rhs, sol); ctx.sync()
+    print("   per-launch us:", {k: round(ctx.prof_get(k)[1] / max(ctx.prof_get(k)[0], 1) * 1e3, 2) for k in ("spmv_ksp", "cg_update", "cg_direction")}); ctx.prof_enable(False)
     print(f"CG matfree={mf}: its {ksp.its} {ms:.2f} ms ({ms/max(ksp.its,1)*1e3:.1f} us/it) err {np.abs(sol.getArray()-xs).max():.2e}", flush=True)
+for mf in (False, True):
+    K.setMatFree(mf)
+    ksp = KSP().create(); ksp.setType("cg"); pc = PC().create(); pc.setType("bjacobi"); ksp.setPC(pc)
+    ksp.setCGSingleReduction(True)
+    ksp.setOperators(K); ksp.setTolerances(rtol=1e-10, max_it=20000); ksp.setUp()
+    for rep in range(2):
+        sol = Vec(n)
+        ctx.sync(); ctx.timer_start()
+        ksp.solve(rhs, sol)
+        ms = ctx.timer_stop()
+    ctx.prof_enable(True); sol = Vec(n); ksp.solve(rhs, sol); ctx.sync()
+    print("   per-launch us (single reduction):", {k: round(ctx.prof_get(k)[1] / max(ctx.prof_get(k)[0], 1) * 1e3, 2) for k in ("spmv_ksp", "cg_update", "cg_direction")}); ctx.prof_enable(False)
+    print(f"CG single-reduction matfree={mf}: its {ksp.its} {ms:.2f} ms ({ms/max(ksp.its,1)*1e3:.1f} us/it) err {np.abs(sol.getArray()-xs).max():.2e}", flush=True)
