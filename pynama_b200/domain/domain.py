@@ -17,6 +17,7 @@ import numpy as np
 from ..boundaries.boundary_conditions import BoundaryConditions
 from ..petsc import COMM_WORLD, Vec
 from .box_mesh import BoxMesh
+from .gmsh_mesh import GmshMesh
 
 
 class Domain:
@@ -65,7 +66,13 @@ class Domain:
             self._mesh = BoxMesh(cfg["nelem"], cfg["lower"], cfg["upper"], self._ngl,
                                  perturb=self._perturb)
         elif "gmsh-file" in self.domData:
-            raise NotImplementedError("gmsh meshes are outside the B200 hot path for now (box-mesh only)")
+            # unstructured quad/hex mesh (GmshDom, dmplex.py:389-395); single GPU for now
+            self._meshType = "gmsh"
+            cfg = self.domData["gmsh-file"]
+            self._ngl = self.domData["ngl"]
+            if self.comm.size > 1:
+                raise NotImplementedError("gmsh meshes are not partitioned yet: run on one GPU")
+            self._mesh = GmshMesh(cfg if isinstance(cfg, str) else cfg["fileName"], self._ngl)
         else:
             raise Exception("Mesh Type not defined")
         del self.domData
