@@ -66,12 +66,10 @@ class Domain:
             self._mesh = BoxMesh(cfg["nelem"], cfg["lower"], cfg["upper"], self._ngl,
                                  perturb=self._perturb)
         elif "gmsh-file" in self.domData:
-            # unstructured quad/hex mesh (GmshDom, dmplex.py:389-395); single GPU for now
+            # unstructured quad/hex mesh (GmshDom, dmplex.py:389-395)
             self._meshType = "gmsh"
             cfg = self.domData["gmsh-file"]
             self._ngl = self.domData["ngl"]
-            if self.comm.size > 1:
-                raise NotImplementedError("gmsh meshes are not partitioned yet: run on one GPU")
             self._mesh = GmshMesh(cfg if isinstance(cfg, str) else cfg["fileName"], self._ngl)
         else:
             raise Exception("Mesh Type not defined")

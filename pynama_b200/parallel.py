@@ -1,4 +1,4 @@
-"""Row partition of a structured spectral-element mesh over the GPUs of one box.
+"""Row partition of a spectral-element mesh over the GPUs of one box.
 
 Replaces what PETSc does for the reference when it runs under ``mpiexec``
 (``DMPlex.distribute()``, src/domain/dmplex.py:21; AIJ local-row ownership,
@@ -6,6 +6,7 @@ src/matrices/mat_fs.py:102-106; VecScatter ghost updates inside ``MatMult``):
 
 * the box of elements is cut into ``px * py * pz`` contiguous blocks (z-slabs for
   2 ranks, 2x2x1 for 4, 2x2x2 for 8: smallest halo surface), rank = bx + px*(by + py*bz);
+  an unstructured (Gmsh) mesh is cut by recursive coordinate bisection of the element centroids;
 * a node is owned by the lowest rank whose block touches it;
 * every rank holds **all elements that touch one of its owned nodes** (its block plus one
   layer of elements on the upper sides): owned rows are then assembled completely and
@@ -52,28 +53,52 @@ def _cuts(n, parts):
     return np.concatenate([[0], np.cumsum(sizes)]).astype(np.int64)
 
 
+def rcb(centroids, size):
+    """recursive coordinate bisection of element centroids into `size` parts (unstructured meshes,
+    SURVEY.md 8e-E1): cut the longest extent at the weighted median, recurse.  Returns the part of
+    every element; parts are numbered left to right along the cuts."""
+    c = np.asarray(centroids, dtype=np.float64)
+    part = np.zeros(len(c), dtype=np.int64)
+
+    def split(idx, first, nparts):
+        if nparts == 1:
+            part[idx] = first
+            return
+        nl = nparts // 2
+        ext = np.ptp(c[idx], axis=0)
+        axis = int(np.argmax(ext))
+        order = idx[np.lexsort((idx, c[idx, axis]))]          # ties broken by element id: deterministic
+        k = (len(order) * nl) // nparts
+        split(order[:k], first, nl)
+        split(order[k:], first + nl, nparts - nl)
+
+    split(np.arange(len(c)), 0, int(size))
+    return part
+
+
 class Partition:
-    """Local tables of one rank.  `mesh` is the global BoxMesh (replicated)."""
+    """Local tables of one rank.  `mesh` is the global mesh (BoxMesh or GmshMesh, replicated)."""
 
     def __init__(self, mesh, rank, size, grid=None):
         self.rank, self.size = int(rank), int(size)
         self.dim = dim = mesh.dim
-        self.pgrid = tuple(grid) if grid is not None else block_grid(size, mesh.nelem)
-        assert int(np.prod(self.pgrid)) == size
-        p = mesh.ngl - 1
-        self.cuts = [_cuts(mesh.nelem[d], self.pgrid[d]) for d in range(dim)]
-        # owner block per axis of every GLL grid index: lowest block touching it
-        owner_axis = []
-        for d in range(dim):
-            upper = self.cuts[d][1:] * p                     # last grid index of each block
-            owner_axis.append(np.searchsorted(upper, np.arange(mesh.grid[d]), side="left"))
-        self._owner_axis = owner_axis
-        nijk = mesh.node_ijk
-        owner = np.zeros(mesh.nnodes, dtype=np.int64)
-        stride = 1
-        for d in range(dim):
-            owner += owner_axis[d][nijk[:, d]] * stride
-            stride *= self.pgrid[d]
+        if hasattr(mesh, "nelem"):                       # structured box: contiguous element blocks
+            self.pgrid = tuple(grid) if grid is not None else block_grid(size, mesh.nelem)
+            assert int(np.prod(self.pgrid)) == size
+            self.cuts = [_cuts(mesh.nelem[d], self.pgrid[d]) for d in range(dim)]
+            elem_rank = np.zeros(mesh.nel, dtype=np.int64)
+            stride = 1
+            for d in range(dim):
+                blk = np.searchsorted(self.cuts[d][1:], mesh.cell_ijk[:, d], side="right")
+                elem_rank += blk * stride
+                stride *= self.pgrid[d]
+        else:                                            # unstructured: recursive coordinate bisection
+            self.pgrid = (size,)
+            elem_rank = rcb(mesh.corner_xyz.mean(axis=1), size)
+        self.elem_rank = elem_rank
+        # a node belongs to the lowest rank whose elements touch it
+        owner = np.full(mesh.nnodes, size, dtype=np.int64)
+        np.minimum.at(owner, mesh.elem_nodes.ravel(), np.repeat(elem_rank, mesh.elem_nodes.shape[1]))
         self.node_owner = owner
         self.owned = np.nonzero(owner == self.rank)[0]                      # ascending global id
         # elements touching an owned node

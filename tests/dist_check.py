@@ -39,6 +39,15 @@ def main():
         o.setValue(name, val)
     cfg = bench.case_config(nelem[0], ngl)
     cfg["domain"]["box-mesh"]["nelem"] = nelem
+    if os.environ.get("DIST_GMSH", "0") != "0":
+        # the same box as an unstructured .msh file (scrambled numbering, rotated and mirrored
+        # cells): recursive-coordinate-bisection partition; every rank writes its own identical copy
+        import tempfile
+        from tests.test_gmsh_mesh import box_as_msh
+        path = os.path.join(tempfile.mkdtemp(prefix=f"pyn_gmsh_{rank}_"), "mesh.msh")
+        box_as_msh(path, nelem, perturb=0.1)
+        del cfg["domain"]["box-mesh"]
+        cfg["domain"]["gmsh-file"] = path
     fem = BaseProblem(cfg, case="taylor-green3d")
     fem.setUp()
     fem.setUpSolver()

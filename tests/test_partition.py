@@ -21,10 +21,49 @@ def test_block_grid():
         block_grid(8, [1, 1, 2])
 
 
+def _gmsh_twin(tmp_path, nelem, ngl):
+    from pynama_b200.domain.gmsh_mesh import GmshMesh
+    from tests.test_gmsh_mesh import box_as_msh
+    path = str(tmp_path / "m.msh")
+    box_as_msh(path, nelem)
+    return GmshMesh(path, ngl)
+
+
+def test_block_owner_rule_is_the_lowest_block_touching_the_node():
+    """structured meshes: ownership from element ranks == the per-axis rule of the first version"""
+    mesh = BoxMesh([5, 4, 3], [0] * 3, [1] * 3, 3)
+    p = Partition(mesh, 0, 8)
+    q = mesh.ngl - 1
+    want = np.zeros(mesh.nnodes, dtype=np.int64)
+    stride = 1
+    for d in range(3):
+        upper = p.cuts[d][1:] * q
+        want += np.searchsorted(upper, mesh.node_ijk[:, d], side="left") * stride
+        stride *= p.pgrid[d]
+    assert np.array_equal(p.node_owner, want)
+
+
+def test_rcb_balances_and_is_deterministic():
+    from pynama_b200.parallel import rcb
+    rng = np.random.default_rng(0)
+    c = rng.uniform(0, 1, (1001, 3)) * [4.0, 1.0, 2.0]
+    for size in (2, 3, 4, 8):
+        part = rcb(c, size)
+        counts = np.bincount(part, minlength=size)
+        assert counts.max() - counts.min() <= 2, counts
+        assert np.array_equal(part, rcb(c, size))
+    assert np.all(c[rcb(c, 2) == 0][:, 0].max() <= c[rcb(c, 2) == 1][:, 0].min())      # first cut: longest axis
+
+
 @pytest.mark.parametrize("nelem,ngl,size", [([4, 4], 3, 2), ([4, 3], 4, 4), ([3, 3, 4], 3, 2),
-                                            ([4, 4, 4], 3, 8), ([3, 4, 5], 2, 3)])
-def test_ownership_and_halo_tables(nelem, ngl, size):
-    mesh = BoxMesh(nelem, [0] * len(nelem), [1] * len(nelem), ngl)
+                                            ([4, 4, 4], 3, 8), ([3, 4, 5], 2, 3),
+                                            ("gmsh", [5, 4], 3, 2), ("gmsh", [3, 3, 4], 3, 4)][:5] +
+                         [(("gmsh", [5, 4]), 3, 2), (("gmsh", [3, 3, 4]), 3, 4), (("gmsh", [4, 3, 3]), 4, 8)])
+def test_ownership_and_halo_tables(tmp_path, nelem, ngl, size):
+    if isinstance(nelem, tuple):
+        mesh = _gmsh_twin(tmp_path, nelem[1], ngl)
+    else:
+        mesh = BoxMesh(nelem, [0] * len(nelem), [1] * len(nelem), ngl)
     parts = [Partition(mesh, r, size) for r in range(size)]
     # every node owned exactly once; owned sets partition the nodes
     allown = np.concatenate([p.owned for p in parts])
