@@ -455,7 +455,8 @@ __global__ void pc_setup_kernel(int pc, const double* __restrict__ dblk, double*
 // the A-norm-optimal element of their span.  Successive KLE systems differ only through
 // time-dependent boundary values and the slowly changing vorticity, so most of the solution is
 // recovered before the first Krylov iteration.
-constexpr int kFischerMax = 8;
+constexpr int kFischerMax = 8;        // basis vectors handled by one multi_dot / lincomb launch
+constexpr int kFischerCap = 32;       // capacity of the Fischer basis (chunks of kFischerMax)
 struct BasisPtrs {
   const double* v[kFischerMax];
   int k;
@@ -543,8 +544,8 @@ struct pyn_ksp {
   bool pc_ready = false;
   // Fischer guess: basis of <= fischer_m A-orthonormal increments and their images
   int fischer_m = 0, fischer_n = 0;
-  DevBuf<double> fx[kFischerMax], fax[kFischerMax];
-  DevBuf<double> x0, r0, fd, fad, fcoef;     // fcoef: [kFischerMax + 4]
+  DevBuf<double> fx[kFischerCap], fax[kFischerCap];
+  DevBuf<double> x0, r0, fd, fad, fcoef;     // fcoef: [kFischerCap + 4]
   int64_t fischer_used = 0, fischer_restarts = 0;
   // work vectors of BiCGStab / GMRES(m)
   DevBuf<double> kv[4];
@@ -588,14 +589,17 @@ static int ksp_solve_cg(pyn_ksp* k, const double* b, double* x, int* its, int* r
   const bool fischer = k->fischer_m > 0;
   const int gridv = grid_for(ctx, n > 0 ? n : 1, 256);
   if (fischer && k->fischer_n > 0) {        // x <- sum_i (x~_i . b) x~_i
-    BasisPtrs bp;
-    bp.k = k->fischer_n;
-    for (int i = 0; i < bp.k; ++i) bp.v[i] = k->fx[i].p;
-    multi_dot_kernel<<<gridv, 256, 0, ctx->stream>>>(bp, b, n, ctx->red_partials, ctx->red_ticket, k->fcoef.p);
-    PYN_LAUNCHED(ctx);
-    if (dist) PYN_CHECK(comm_allreduce_sum(ctx, k->fcoef.p, kFischerMax));
-    lincomb_kernel<<<gridv, 256, 0, ctx->stream>>>(x, bp, k->fcoef.p, 1.0, 0, n);
-    PYN_LAUNCHED(ctx);
+    for (int i0 = 0; i0 < k->fischer_n; i0 += kFischerMax) {
+      BasisPtrs bp;
+      bp.k = k->fischer_n - i0 < kFischerMax ? k->fischer_n - i0 : kFischerMax;
+      for (int i = 0; i < bp.k; ++i) bp.v[i] = k->fx[i0 + i].p;
+      multi_dot_kernel<<<gridv, 256, 0, ctx->stream>>>(bp, b, n, ctx->red_partials, ctx->red_ticket,
+                                                       k->fcoef.p + i0);
+      PYN_LAUNCHED(ctx);
+      if (dist) PYN_CHECK(comm_allreduce_sum(ctx, k->fcoef.p + i0, kFischerMax));
+      lincomb_kernel<<<gridv, 256, 0, ctx->stream>>>(x, bp, k->fcoef.p + i0, 1.0, i0 > 0 ? 1 : 0, n);
+      PYN_LAUNCHED(ctx);
+    }
     k->fischer_used++;
   } else if (fischer) {
     // empty basis: start from zero so that the increments span the solutions themselves
@@ -679,22 +683,29 @@ static int ksp_solve_cg(pyn_ksp* k, const double* b, double* x, int* its, int* r
       PYN_CUDA(cudaMemcpyAsync(k->fd.p, x, sizeof(double) * n, cudaMemcpyDeviceToDevice, ctx->stream));
       PYN_CHECK(vec_waxpy(ctx, k->fad.p, -1.0, k->r.p, b, n));
     }
-    double* nrm2 = k->fcoef.p + kFischerMax;
+    double* nrm2 = k->fcoef.p + kFischerCap;
     PYN_CHECK(vec_dot_dev(ctx, k->fd.p, k->fad.p, n, nrm2 + 1));
-    if (k->fischer_n > 0) {
-      BasisPtrs bp, bap;
-      bp.k = bap.k = k->fischer_n;
-      for (int i = 0; i < bp.k; ++i) {
-        bp.v[i] = k->fx[i].p;
-        bap.v[i] = k->fax[i].p;
-      }
+    // classical Gram-Schmidt in the A inner product: all coefficients from the same A d, so the
+    // chunks are independent
+    for (int i0 = 0; i0 < k->fischer_n; i0 += kFischerMax) {
+      BasisPtrs bp;
+      bp.k = k->fischer_n - i0 < kFischerMax ? k->fischer_n - i0 : kFischerMax;
+      for (int i = 0; i < bp.k; ++i) bp.v[i] = k->fx[i0 + i].p;
       multi_dot_kernel<<<gridv, 256, 0, ctx->stream>>>(bp, k->fad.p, n, ctx->red_partials, ctx->red_ticket,
-                                                       k->fcoef.p);
+                                                       k->fcoef.p + i0);
       PYN_LAUNCHED(ctx);
-      if (dist) PYN_CHECK(comm_allreduce_sum(ctx, k->fcoef.p, kFischerMax));
-      lincomb_kernel<<<gridv, 256, 0, ctx->stream>>>(k->fd.p, bp, k->fcoef.p, -1.0, 1, n);
+      if (dist) PYN_CHECK(comm_allreduce_sum(ctx, k->fcoef.p + i0, kFischerMax));
+    }
+    for (int i0 = 0; i0 < k->fischer_n; i0 += kFischerMax) {
+      BasisPtrs bp, bap;
+      bp.k = bap.k = k->fischer_n - i0 < kFischerMax ? k->fischer_n - i0 : kFischerMax;
+      for (int i = 0; i < bp.k; ++i) {
+        bp.v[i] = k->fx[i0 + i].p;
+        bap.v[i] = k->fax[i0 + i].p;
+      }
+      lincomb_kernel<<<gridv, 256, 0, ctx->stream>>>(k->fd.p, bp, k->fcoef.p + i0, -1.0, 1, n);
       PYN_LAUNCHED(ctx);
-      lincomb_kernel<<<gridv, 256, 0, ctx->stream>>>(k->fad.p, bap, k->fcoef.p, -1.0, 1, n);
+      lincomb_kernel<<<gridv, 256, 0, ctx->stream>>>(k->fad.p, bap, k->fcoef.p + i0, -1.0, 1, n);
       PYN_LAUNCHED(ctx);
     }
     PYN_CHECK(vec_dot_dev(ctx, k->fd.p, k->fad.p, n, nrm2));
@@ -709,7 +720,7 @@ static int ksp_solve_cg(pyn_ksp* k, const double* b, double* x, int* its, int* r
   PYN_CUDA(cudaStreamSynchronize(ctx->stream));
   PYN_CUDA(cudaMemcpyAsync(k->status_host, S, sizeof(double) * S_COUNT, cudaMemcpyDeviceToHost, ctx->stream));
   if (fischer)
-    PYN_CUDA(cudaMemcpyAsync(k->status_host + S_COUNT, k->fcoef.p + kFischerMax + 3, sizeof(double),
+    PYN_CUDA(cudaMemcpyAsync(k->status_host + S_COUNT, k->fcoef.p + kFischerCap + 3, sizeof(double),
                              cudaMemcpyDeviceToHost, ctx->stream));
   PYN_CUDA(cudaStreamSynchronize(ctx->stream));
   if (fischer && k->status_host[S_COUNT] != 0.0) k->fischer_n++;
@@ -1018,7 +1029,7 @@ int pyn_ksp_set_cg_single_reduction(pyn_ksp* k, int on) {
 int pyn_ksp_set_fischer_guess(pyn_ksp* k, int model, int size) {
   PYN_REQUIRE(k, "null ksp");
   PYN_REQUIRE(size == 0 || model == 1, "KSP Fischer guess: only model 1 (A-conjugate projection) is implemented");
-  PYN_REQUIRE(size >= 0 && size <= kFischerMax, "KSP Fischer guess: size %d (max %d)", size, kFischerMax);
+  PYN_REQUIRE(size >= 0 && size <= kFischerCap, "KSP Fischer guess: size %d (max %d)", size, kFischerCap);
   pyn_ctx* ctx = k->ctx;
   k->fischer_m = size;
   k->fischer_n = 0;
@@ -1031,7 +1042,7 @@ int pyn_ksp_set_fischer_guess(pyn_ksp* k, int model, int size) {
   PYN_CHECK(k->r0.alloc(ctx, k->n));
   PYN_CHECK(k->fd.alloc(ctx, k->n));
   PYN_CHECK(k->fad.alloc(ctx, k->n));
-  PYN_CHECK(k->fcoef.alloc(ctx, kFischerMax + 4));
+  PYN_CHECK(k->fcoef.alloc(ctx, kFischerCap + 4 + kFischerMax));
   PYN_CHECK(k->fcoef.zero());
   return PYN_OK;
 }

@@ -899,7 +899,7 @@ class KSP:
         call("pyn_ksp_set_tolerances", h, float(rtol), float(self.atol), int(self.max_it),
              int(self.restart))
         if self._fischer[1] > 0:
-            call("pyn_ksp_set_fischer_guess", h, self._fischer[0], min(self._fischer[1], 8))
+            call("pyn_ksp_set_fischer_guess", h, self._fischer[0], min(self._fischer[1], 32))
         if self._cg_single_reduction and ktype == "cg":
             call("pyn_ksp_set_cg_single_reduction", h, 1)
 
