@@ -141,6 +141,10 @@ def build_problem(args):
         o.setValue("ksp_fischer_guess", f"1,{args.fischer}")
     o.setValue("ts_adapt_type", "none")
     o.setValue("ts_dt", args.dt)
+    if int(os.environ.get("WORLD_SIZE", "1")) > 1 and not any(kv.startswith("ksp_cg_single_reduction") for kv in args.opt):
+        # row-partitioned runs: CG with one synchronisation point per iteration (PETSc's
+        # -ksp_cg_single_reduction); with the peer-memory back end the halo exchange is fused too
+        args.opt.append("ksp_cg_single_reduction=1")
     for kv in args.opt:
         name, _, val = kv.partition("=")
         o.setValue(name, val or "1")
@@ -451,6 +455,9 @@ def init_dist():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    # rank 0 prints ONE JSON line on stdout: keep NCCL's version banner (NCCL_DEBUG=VERSION) out of it
+    if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+        os.environ["NCCL_DEBUG"] = "WARN"
     return rank, world
 
 

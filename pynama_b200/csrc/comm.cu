@@ -88,13 +88,6 @@ __global__ void halo_pack_kernel(const double* __restrict__ v, const int32_t* __
 }
 
 // ---- peer-memory halo: senders store straight into the receiver's window -------------------
-constexpr int kHaloHdr = 256;   // bytes: flag[2][kMaxRanks] u64, padded
-__device__ __forceinline__ unsigned long long* halo_flag(unsigned char* win, int par, int src) {
-  return reinterpret_cast<unsigned long long*>(win) + par * kMaxRanks + src;
-}
-__device__ __forceinline__ double* halo_buf(unsigned char* win, int par, int64_t nghost, int max_bs) {
-  return reinterpret_cast<double*>(win + kHaloHdr) + (int64_t)par * nghost * max_bs;
-}
 
 __global__ void halo_push_kernel(const double* __restrict__ v, const int32_t* __restrict__ send_nodes,
                                  const int64_t* __restrict__ send_ptr, int nneigh,
@@ -169,6 +162,32 @@ static int halo_exchange_p2p(pyn_halo* h, double* v, int bs) {
   PYN_LAUNCHED(ctx);
   ctx->collectives++;
   return PYN_OK;
+}
+
+void halo_fused_next(pyn_halo* h, int bs, HaloPush* push, HaloWait* wait) {
+  pyn_ctx* ctx = h->ctx;
+  const unsigned long long seq = ++h->seq;
+  push->nslot_ptr = h->d_nslot_ptr.p;
+  push->nslot = h->d_nslot.p;
+  push->send_ptr = h->d_send_ptr.p;
+  push->peer_win = h->d_peer_win.p;
+  push->peer_off = h->d_peer_off.p;
+  push->peer_nghost = h->d_peer_nghost.p;
+  push->nneigh = h->nneigh;
+  push->bs = bs;
+  push->max_bs = h->max_bs;
+  push->my_rank = ctx->rank;
+  push->seq = seq;
+  wait->win = h->win;
+  wait->ranks = h->d_ranks.p;
+  wait->nneigh = h->nneigh;
+  wait->bs = bs;
+  wait->max_bs = h->max_bs;
+  wait->n_own = h->n_own;
+  wait->nghost = h->n_loc - h->n_own;
+  wait->seq = seq;
+  wait->timeout_flag = ctx->p2p_timeout;
+  ctx->collectives++;
 }
 
 P2PRed p2p_next(pyn_ctx* ctx) {
@@ -340,6 +359,19 @@ int pyn_halo_create(pyn_ctx* ctx, int64_t n_own, int64_t n_loc, int nneigh, cons
     }
   int rc = h->send_nodes.alloc(ctx, nsend > 0 ? nsend : 1);
   if (rc == PYN_OK && nsend > 0) rc = h->send_nodes.upload(send_nodes, nsend);
+  // inverse of the send list (fused halo push: the thread that produces node n stores it remotely)
+  std::vector<int64_t> nptr((size_t)n_own + 1, 0);
+  for (int64_t i = 0; i < nsend; ++i) nptr[send_nodes[i] + 1]++;
+  for (int64_t n = 0; n < n_own; ++n) nptr[n + 1] += nptr[n];
+  std::vector<int32_t> nslot((size_t)(nsend > 0 ? nsend : 1), 0);
+  {
+    std::vector<int64_t> fill(nptr.begin(), nptr.end() - 1);
+    for (int64_t i = 0; i < nsend; ++i) nslot[fill[send_nodes[i]]++] = (int32_t)i;
+  }
+  if (rc == PYN_OK) rc = h->d_nslot_ptr.alloc(ctx, n_own + 1);
+  if (rc == PYN_OK) rc = h->d_nslot_ptr.upload(nptr.data(), n_own + 1);
+  if (rc == PYN_OK) rc = h->d_nslot.alloc(ctx, (int64_t)nslot.size());
+  if (rc == PYN_OK) rc = h->d_nslot.upload(nslot.data(), (int64_t)nslot.size());
   if (rc == PYN_OK && cudaStreamSynchronize(ctx->stream) != cudaSuccess) rc = PYN_E_CUDA;
   if (rc != PYN_OK) {
     delete h;

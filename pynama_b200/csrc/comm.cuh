@@ -112,6 +112,78 @@ __device__ __forceinline__ void grid_reduce_push(double (&v)[NV], double* partia
   if (threadIdx.x == 0) *ticket = 0u;
 }
 #endif
+
+// ---- halo exchange fused into the Krylov kernels (peer-memory path) ------------------------
+// Producer side: the vector kernel that computes the next product's input stores the values
+// of the nodes its neighbours hold as ghosts straight into their windows; its last CTA
+// releases the flags.  Consumer side: the product kernel waits for the flags at CTA start
+// and reads ghost columns from its own window.  No pack / wait / unpack launches.
+constexpr int kHaloHdr = 256;   // bytes: flag[2][kMaxRanks] u64, padded
+struct HaloPush {
+  const int64_t* nslot_ptr;          // [n_own+1] send slots of every owned node (most have none)
+  const int32_t* nslot;              // slot ids k (position in the send list, grouped by neighbour)
+  const int64_t* send_ptr;           // [nneigh+1]
+  const unsigned long long* peer_win;  // [nneigh] neighbours' window addresses
+  const int64_t* peer_off;           // [nneigh] offset of my run in the neighbour's ghost section
+  const int64_t* peer_nghost;        // [nneigh] the neighbour's ghost count
+  int nneigh;                        // 0: disabled
+  int bs, max_bs, my_rank;
+  unsigned long long seq;
+};
+struct HaloWait {
+  unsigned char* win;                // own window
+  const int32_t* ranks;              // [nneigh]
+  int nneigh;                        // 0: disabled
+  int bs, max_bs;
+  int64_t n_own, nghost;
+  unsigned long long seq;
+  int* timeout_flag;
+};
+#ifdef __CUDACC__
+__device__ __forceinline__ unsigned long long* halo_flag(unsigned char* win, int par, int src) {
+  return reinterpret_cast<unsigned long long*>(win) + par * kMaxRanks + src;
+}
+__device__ __forceinline__ double* halo_buf(unsigned char* win, int par, int64_t nghost, int max_bs) {
+  return reinterpret_cast<double*>(win + kHaloHdr) + (int64_t)par * nghost * max_bs;
+}
+// values vals[0..bs) of owned node n -> every neighbour that holds n as a ghost
+__device__ __forceinline__ void halo_push_node(const HaloPush& h, int64_t n, const double* vals) {
+  const int par = (int)(h.seq & 1ull);
+  for (int64_t q = h.nslot_ptr[n]; q < h.nslot_ptr[n + 1]; ++q) {
+    const int64_t k = h.nslot[q];
+    int nb = 0;
+    while (k >= h.send_ptr[nb + 1]) ++nb;
+    double* dst = halo_buf(reinterpret_cast<unsigned char*>(h.peer_win[nb]), par, h.peer_nghost[nb], h.max_bs) +
+                  (h.peer_off[nb] + (k - h.send_ptr[nb])) * h.bs;
+    for (int c = 0; c < h.bs; ++c) dst[c] = vals[c];
+  }
+}
+// by the last CTA of the producer, after every CTA fenced its stores (threadfence_system
+// before the ticket): one thread per neighbour
+__device__ __forceinline__ void halo_release_flags(const HaloPush& h) {
+  __threadfence_system();
+  if ((int)threadIdx.x < h.nneigh)
+    st_release_sys(halo_flag(reinterpret_cast<unsigned char*>(h.peer_win[threadIdx.x]), (int)(h.seq & 1ull), h.my_rank),
+                   h.seq);
+}
+// all threads of the CTA call; false on spin timeout
+__device__ __forceinline__ bool halo_wait_cta(const HaloWait& h) {
+  __shared__ int halo_ok_sm;
+  if (threadIdx.x == 0) halo_ok_sm = 1;
+  __syncthreads();
+  if ((int)threadIdx.x < h.nneigh) {
+    long long spins = 0;
+    while (ld_acquire_sys(halo_flag(h.win, (int)(h.seq & 1ull), h.ranks[threadIdx.x])) < h.seq)
+      if (++spins > kSpinMax) {
+        halo_ok_sm = 0;
+        *h.timeout_flag = 1;
+        break;
+      }
+  }
+  __syncthreads();
+  return halo_ok_sm != 0;
+}
+#endif
 }  // namespace pyn
 
 struct pyn_halo {
@@ -135,6 +207,8 @@ struct pyn_halo {
   pyn::DevBuf<int64_t> d_send_ptr, d_peer_off, d_peer_nghost, d_recv_off, d_recv_cnt;
   pyn::DevBuf<int32_t> d_ranks;
   pyn::DevBuf<unsigned long long> d_peer_win;   // device array of the neighbours' window addresses
+  pyn::DevBuf<int64_t> d_nslot_ptr;             // [n_own+1] inverse of the send list: owned node -> its send slots
+  pyn::DevBuf<int32_t> d_nslot;
   unsigned long long seq = 0;
   ~pyn_halo();
 };
@@ -148,4 +222,6 @@ int halo_exchange(pyn_halo* h, double* v, int bs);
 // (nranks = 1) unless the peer windows are attached
 P2PRed p2p_next(pyn_ctx* ctx);
 bool p2p_enabled(const pyn_ctx* ctx);
+// descriptors of the NEXT fused halo exchange of h (advances its sequence); bs = dofs per node
+void halo_fused_next(pyn_halo* h, int bs, HaloPush* push, HaloWait* wait);
 }  // namespace pyn

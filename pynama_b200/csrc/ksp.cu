@@ -12,6 +12,7 @@
 // CTA of (2).  The host only polls a pinned status word every few iterations;
 // iterations launched after convergence return immediately.
 #include "ksp.cuh"
+#include <stdlib.h>
 #include "vec.cuh"
 #include "comm.cuh"
 #include <memory>
@@ -231,7 +232,7 @@ __global__ void __launch_bounds__(256)
 cg_sr_update_kernel(int pc, const double* __restrict__ pcd, double* __restrict__ u,
                     const double* __restrict__ w, double* __restrict__ p, double* __restrict__ s,
                     double* __restrict__ x, double* __restrict__ r, int64_t nnodes, double* S, int it,
-                    int maxit, double* partials, unsigned int* ticket, P2PRed red) {
+                    int maxit, double* partials, unsigned int* ticket, P2PRed red, HaloPush hp) {
   __shared__ double sm[64];
   __shared__ double s_sum[3];
   __shared__ int s_ok;
@@ -327,7 +328,10 @@ cg_sr_update_kernel(int pc, const double* __restrict__ pcd, double* __restrict__
       v[0] += rr[i] * zz[i];
       v[1] += zz[i] * zz[i];
     }
+    // fused halo push: u is the input of the next product; neighbours read it from their windows
+    if (hp.nneigh > 0) halo_push_node(hp, n, zz);
   }
+  if (hp.nneigh > 0) __threadfence_system();       // this thread's remote stores, before the ticket
   // gamma and u.u of the next iterate: grid reduction, then to S (or to every rank's window)
   block_reduce<2>(v, sm);
   if (threadIdx.x == 0) {
@@ -348,6 +352,7 @@ cg_sr_update_kernel(int pc, const double* __restrict__ pcd, double* __restrict__
     if (lane == 0) sm[wid] = t;
   }
   __syncthreads();
+  if (hp.nneigh > 0) halo_release_flags(hp);       // every CTA's pushes are visible: raise the flags
   if (threadIdx.x < 32) {
     if (red.nranks > 1) {
       double t[2] = {sm[0], sm[1]};
@@ -623,6 +628,12 @@ static int ksp_solve_cg(pyn_ksp* k, const double* b, double* x, int* its, int* r
   PYN_LAUNCHED(ctx);
   PYN_CUDA(cudaMemcpyAsync(k->p.p, k->z.p, sizeof(double) * n, cudaMemcpyDeviceToDevice, ctx->stream));
 
+  // single-reduction CG over peer memory: halo exchange fused into the two kernels of an iteration
+  const bool fuse_halo = k->single_reduction && p2p && k->A->halo->p2p && k->A->halo->nneigh > 0 &&
+                         getenv("PYN_FUSED_HALO_OFF") == nullptr;
+  bool halo_ready = false;
+  HaloWait hw;
+  memset(&hw, 0, sizeof(hw));
   // Chunks of `check_every` iterations; the status of chunk c-1 is read while
   // chunk c runs, so the GPU never idles on the host.
   int it = 0;
@@ -633,13 +644,20 @@ static int ksp_solve_cg(pyn_ksp* k, const double* b, double* x, int* its, int* r
       P2PRed red = p2p ? p2p_next(ctx) : red_off;
       if (k->single_reduction) {
         // w = A u with w.u fused; then the whole recurrence (and r.u, u.u of the next iterate)
-        // in one vector kernel
-        PYN_CHECK(spmv_dot(k->A, k->z.p, k->w.p, S + S_SR, S + S_DONE, &red));
+        // in one vector kernel.  Over peer memory the halo exchange of u rides in the same two
+        // kernels: pushed by the vector kernel, awaited by the next product.
+        PYN_CHECK(spmv_dot(k->A, k->z.p, k->w.p, S + S_SR, S + S_DONE, &red, halo_ready ? &hw : nullptr));
         if (dist && !p2p) PYN_CHECK(comm_allreduce_sum(ctx, S + S_SR, 1));
+        HaloPush hp;
+        memset(&hp, 0, sizeof(hp));
+        if (fuse_halo) {
+          halo_fused_next(k->A->halo, B, &hp, &hw);
+          halo_ready = true;
+        }
         prof_begin(ctx, PROF_CG_UPDATE);
         cg_sr_update_kernel<B><<<gridn, 256, 0, ctx->stream>>>(k->pc, k->pcd.p, k->z.p, k->w.p, k->p.p,
                                                                k->sr_s.p, x, k->r.p, nn, S, it, k->maxit,
-                                                               ctx->red_partials, ctx->red_ticket, red);
+                                                               ctx->red_partials, ctx->red_ticket, red, hp);
         prof_end(ctx);
         PYN_LAUNCHED(ctx);
         if (dist && !p2p) PYN_CHECK(comm_allreduce_sum(ctx, S + S_SR + 1, 2));

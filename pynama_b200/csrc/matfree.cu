@@ -381,10 +381,16 @@ template <int N, int WPC>
 __global__ void __launch_bounds__(WPC * 32)
 mf_apply_kernel(int64_t nel, const int32_t* __restrict__ nodes_t, const int32_t* __restrict__ loc_of_t,
                 const uint8_t* __restrict__ cls, const double* __restrict__ geo, int64_t npts,
-                const double* __restrict__ x, double* __restrict__ ye, const double* __restrict__ skip) {
+                const double* __restrict__ x, double* __restrict__ ye, const double* __restrict__ skip,
+                HaloWait hw) {
   using S = MfShape<N>;
   extern __shared__ double mf_smem[];
   if (skip && *skip != 0.0) return;
+  const double* xg = nullptr;          // ghost section of x in the halo window (fused exchange)
+  if (hw.win) {
+    if (!halo_wait_cta(hw)) return;
+    xg = halo_buf(hw.win, (int)(hw.seq & 1ull), hw.nghost, hw.max_bs);
+  }
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const int64_t e = (int64_t)blockIdx.x * WPC + wid;
   if (e >= nel) return;
@@ -397,7 +403,10 @@ mf_apply_kernel(int64_t nel, const int32_t* __restrict__ nodes_t, const int32_t*
     const int i = t % N, j = (t / N) % N, k = t / (N * N);
     const int off = i + S::S1 * j + S::S2 * k;
 #pragma unroll
-    for (int c = 0; c < 3; ++c) su[c * S::SC + off] = cls[node * 3 + c] == 0 ? x[node * 3 + c] : 0.0;
+    for (int c = 0; c < 3; ++c) {
+      const double xv = (xg && node >= hw.n_own) ? __ldcg(xg + (node - hw.n_own) * 3 + c) : x[node * 3 + c];
+      su[c * S::SC + off] = cls[node * 3 + c] == 0 ? xv : 0.0;
+    }
   }
   __syncwarp();
   double yacc[S::SLOTS][N];
@@ -472,14 +481,14 @@ mf_gather_kernel(int64_t nrows, const int64_t* __restrict__ n2e_ptr, const int2*
 }
 
 template <int N, int WPC>
-static int mf_launch_apply(pyn_matfree* mf, const double* x, const double* skip) {
+static int mf_launch_apply(pyn_matfree* mf, const double* x, const double* skip, const HaloWait& hw) {
   pyn_mesh* mesh = mf->mesh;
   pyn_ctx* ctx = mesh->ctx;
   const size_t smem = (size_t)WPC * MfShape<N>::WARP_DOUBLES * sizeof(double);
   PYN_CUDA(cudaFuncSetAttribute(mf_apply_kernel<N, WPC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const unsigned grid = (unsigned)((mesh->nel + WPC - 1) / WPC);
   mf_apply_kernel<N, WPC><<<grid, WPC * 32, smem, ctx->stream>>>(
-      mesh->nel, mf->nodes_t.p, mf->loc_of_t.p, mesh->dofcls.p, mf->geo.p, mf->npts, x, mf->ye.p, skip);
+      mesh->nel, mf->nodes_t.p, mf->loc_of_t.p, mesh->dofcls.p, mf->geo.p, mf->npts, x, mf->ye.p, skip, hw);
   PYN_LAUNCHED(ctx);
   return PYN_OK;
 }
@@ -492,11 +501,11 @@ int matfree_apply(pyn_mat* m, int64_t nrows, double alpha, const double* x, doub
   PYN_CHECK(mf_upload_tables(mesh));
   prof_begin(ctx, dot ? PROF_SPMV_KSP : PROF_SPMV);
   switch (mesh->ngl) {
-    case 2: PYN_CHECK((mf_launch_apply<2, 4>(mf, x, fuse.skip))); break;
-    case 3: PYN_CHECK((mf_launch_apply<3, 4>(mf, x, fuse.skip))); break;
-    case 4: PYN_CHECK((mf_launch_apply<4, 4>(mf, x, fuse.skip))); break;
-    case 5: PYN_CHECK((mf_launch_apply<5, 4>(mf, x, fuse.skip))); break;
-    case 6: PYN_CHECK((mf_launch_apply<6, 2>(mf, x, fuse.skip))); break;
+    case 2: PYN_CHECK((mf_launch_apply<2, 4>(mf, x, fuse.skip, fuse.hw))); break;
+    case 3: PYN_CHECK((mf_launch_apply<3, 4>(mf, x, fuse.skip, fuse.hw))); break;
+    case 4: PYN_CHECK((mf_launch_apply<4, 4>(mf, x, fuse.skip, fuse.hw))); break;
+    case 5: PYN_CHECK((mf_launch_apply<5, 4>(mf, x, fuse.skip, fuse.hw))); break;
+    case 6: PYN_CHECK((mf_launch_apply<6, 2>(mf, x, fuse.skip, fuse.hw))); break;
     default:
       set_error("matrix-free K: ngl %d not supported", mesh->ngl);
       return PYN_E_UNSUPPORTED;

@@ -35,6 +35,13 @@ spmv_kernel(int64_t nbrows, const int64_t* __restrict__ rowptr, const int32_t* _
   constexpr int NV = NDOT > 0 ? NDOT : 1;
   __shared__ double red_sm[NV * 32];
   if (fuse.skip && *fuse.skip != 0.0) return;
+  const double* xg = nullptr;          // ghost section of x in the halo window (fused exchange)
+  int64_t n_own = 0;
+  if (fuse.hw.win) {
+    if (!halo_wait_cta(fuse.hw)) return;
+    xg = halo_buf(fuse.hw.win, (int)(fuse.hw.seq & 1ull), fuse.hw.nghost, fuse.hw.max_bs);
+    n_own = fuse.hw.n_own;
+  }
   double dotacc[NV];
 #pragma unroll
   for (int k = 0; k < NV; ++k) dotacc[k] = 0.0;
@@ -61,8 +68,13 @@ spmv_kernel(int64_t nbrows, const int64_t* __restrict__ rowptr, const int32_t* _
       const int64_t c = cnext;
       if (u + G < nb) cnext = colidx[p0 + u + G];
       double xv[BC];
+      if (xg && c >= n_own) {            // written by a peer GPU: read through L2, not L1
 #pragma unroll
-      for (int j = 0; j < BC; ++j) xv[j] = x[c * BC + j];
+        for (int j = 0; j < BC; ++j) xv[j] = __ldcg(xg + (c - n_own) * BC + j);
+      } else {
+#pragma unroll
+        for (int j = 0; j < BC; ++j) xv[j] = x[c * BC + j];
+      }
 #pragma unroll
       for (int i = 0; i < BR; ++i)
 #pragma unroll
@@ -109,7 +121,7 @@ static int spmv_launch(pyn_mat* m, double alpha, const double* x, double beta, c
   if (m->nbrows == 0) return PYN_OK;
   int64_t nrows = m->nbrows;
   if (m->halo) {                       // distributed: refresh the ghosts of x, own rows only
-    PYN_CHECK(halo_exchange(m->halo, const_cast<double*>(x), m->bc));
+    if (!fuse.hw.win) PYN_CHECK(halo_exchange(m->halo, const_cast<double*>(x), m->bc));
     nrows = m->halo->n_own;
     if (nrows == 0) return PYN_OK;
   }
@@ -159,7 +171,8 @@ int spmv(pyn_mat* m, double alpha, const double* x, double beta, const double* z
 }
 
 // y = A x and dot_out = x . y in one pass; no-op when *skip != 0
-int spmv_dot(pyn_mat* m, const double* x, double* y, double* dot_out, const double* skip, const P2PRed* red) {
+int spmv_dot(pyn_mat* m, const double* x, double* y, double* dot_out, const double* skip, const P2PRed* red,
+             const HaloWait* hw) {
   pyn_ctx* ctx = m->ctx;
   SpmvFuse f;
   memset(&f, 0, sizeof(f));
@@ -168,6 +181,7 @@ int spmv_dot(pyn_mat* m, const double* x, double* y, double* dot_out, const doub
   f.ticket = ctx->red_ticket;
   f.dot_out = dot_out;
   if (red) f.red = *red;
+  if (hw) f.hw = *hw;
   return spmv_launch(m, 1.0, x, 0.0, nullptr, y, true, f);
 }
 

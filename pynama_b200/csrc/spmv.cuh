@@ -15,13 +15,16 @@ struct SpmvFuse {
   P2PRed red;          // nranks > 1: push the dot partial to every rank's window instead
   // single-reduction CG: with dot_r the reduction has three values, {y.x, dot_r.x, x.x}
   const double* dot_r;
+  // hw.win != NULL: the ghost entries of x were pushed into this rank's halo window by the
+  // kernel that produced x; wait for them at CTA start and read ghost columns from the window
+  HaloWait hw;
 };
 
 // y = alpha*A*x + beta*z (z may be NULL when beta == 0; z may alias y)
 int spmv(pyn_mat* m, double alpha, const double* x, double beta, const double* z, double* y);
 // red != NULL with nranks > 1: the dot partial is pushed to every rank's window (kind 0) instead of dot_out
 int spmv_dot(pyn_mat* m, const double* x, double* y, double* dot_out, const double* skip,
-             const P2PRed* red = nullptr);
+             const P2PRed* red = nullptr, const HaloWait* hw = nullptr);
 // y = A x and out3 = {x.y, r.x, x.x} in one pass (single-reduction CG)
 int spmv_dot3(pyn_mat* m, const double* x, double* y, const double* r, double* out3, const double* skip,
               const P2PRed* red = nullptr);
