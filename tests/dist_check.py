@@ -37,6 +37,9 @@ def main():
     for kv in filter(None, os.environ.get("DIST_OPTS", "").split(",")):
         name, val = kv.split("=")
         o.setValue(name, val)
+    case = os.environ.get("DIST_CASE", "taylor-green3d")
+    if case == "cavity":
+        return main_cavity(nelem, ngl, rank, size, ctx)
     cfg = bench.case_config(nelem[0], ngl)
     cfg["domain"]["box-mesh"]["nelem"] = nelem
     if os.environ.get("DIST_GMSH", "0") != "0":
@@ -103,6 +106,45 @@ def main():
     if rank == 0:
         print(f"[dist_check] ranks {size}, collectives issued on rank 0: {ctx.collectives()}, "
               f"{'OK' if nf == 0 else 'FAILED ' + str(fails)}", flush=True)
+    return 0 if nf == 0 else 1
+
+
+def main_cavity(nelem, ngl, rank, size, ctx):
+    """no-slip lid-driven cavity (MatNS, the two-solve branch of evalRHS) on the partitioned mesh
+    against OracleProblemNS on the global mesh"""
+    from pynama_b200.cases.base_problem import BaseProblem
+    from pynama_b200.run_case import loadCase
+    Options().setValue("ksp_type", os.environ.get("DIST_KSP", "gmres"))
+    cfg = loadCase("cavity")
+    fem = BaseProblem(cfg, case="cavity", nelem=nelem, ngl=ngl)
+    fem.setUp()
+    fem.setUpSolver()
+    fem.ts._post = None
+    fem.ts.setSolution(fem.vort)
+    mesh = fem.dom.getMesh()
+    walls = cfg["boundary-conditions"]["no-slip"]
+    sides = list(walls.keys())
+    orc = timestep.OracleProblemNS(3, ngl, mesh.corner_xyz, mesh.elem_nodes, mesh.coords, sides,
+                                   {s: mesh.getBorderNodes(s) for s in sides}, walls, rho=fem.rho, mu=fem.mu)
+    fails = []
+
+    def check(name, got, want, tol):
+        err = np.abs(got - want).max() / max(np.abs(want).max(), 1e-300)
+        if rank == 0:
+            print(f"[dist_check] {name:28s} rel.err {err:.2e} (tol {tol:g})", flush=True)
+        if not err <= tol:
+            fails.append(name)
+
+    t, k0 = 0.0, None
+    for _ in range(2):
+        fem.ts.step()
+        t, k0 = orc.step(t, 1e-3, k0)
+    check("cavity velocity", fem.solverKLE.getSolution().getGlobalArray(), orc.vel, 1e-8)
+    check("cavity free-slip velocity", fem.solverKLE.getFreeSlipSolution().getGlobalArray(), orc.velfs, 1e-8)
+    check("cavity vorticity", fem.vort.getGlobalArray(), orc.vort, 1e-8)
+    nf = ctx.allreduce([len(fails)], "max")[0]
+    if rank == 0:
+        print(f"[dist_check] cavity, ranks {size}: {'OK' if nf == 0 else 'FAILED ' + str(fails)}", flush=True)
     return 0 if nf == 0 else 1
 
 

@@ -62,6 +62,20 @@ def test_partitioned_run_single_reduction_and_matfree(opts, p2p):
 
 
 @pytest.mark.parametrize("nproc", [1, 2, 4])
+def test_no_slip_cavity_partitioned(nproc):
+    """MatNS (8 matrices), K + Kfs solved with GMRES, tangential wall values: row-partitioned"""
+    env = {"DIST_CASE": "cavity", "DIST_NELEM": "3,3,4", "DIST_NGL": "3"}
+    if nproc == 1:
+        r = subprocess.run([sys.executable, SCRIPT], capture_output=True, text=True, timeout=600,
+                           env=dict(os.environ, **env))
+        assert r.returncode == 0, r.stdout[-3000:] + "\n" + r.stderr[-3000:]
+        return
+    if _ngpus() < nproc:
+        pytest.skip(f"needs {nproc} GPUs")
+    _run(nproc, 29570 + nproc, env)
+
+
+@pytest.mark.parametrize("nproc", [1, 2, 4])
 def test_unstructured_mesh_partitioned_by_rcb(nproc):
     """Gmsh input, recursive coordinate bisection over the ranks, same oracle comparison"""
     env = {"DIST_GMSH": "1", "DIST_NELEM": "4,3,4"}
