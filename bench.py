@@ -51,6 +51,7 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-matfree", action="store_true", help="skip the extra matrix-free (-kle_matfree 1) pass")
+    ap.add_argument("--no-asm-warm", action="store_true", help="skip the warm re-assembly passes (uniform + perturbed mesh)")
     ap.add_argument("--fischer", type=int, default=16,
                     help="-ksp_fischer_guess 1,<n>: initial guess from the last n solutions (0: off, PETSc default)")
     ap.add_argument("--opt", action="append", default=[], metavar="NAME=VALUE",
@@ -317,6 +318,7 @@ def run_b200(args, rank, world):
         "kernel_time_ms_per_step": {"spmv_K_dot": ms_spmv / args.steps, "cg_update": ms_upd / args.steps,
                                     "cg_direction": ms_dir / args.steps, "spmv_other": ms_oth / args.steps},
         "assembly": assembly_report(asm, asm_kernels, fem, ndof, peak),
+        "assembly_kernels_warm": assembly_warm(args, ctx, fem, peak) if not args.no_asm_warm else None,
         "gpu_launches": int(launches),
         "clocks": clocks,
     }
@@ -325,6 +327,65 @@ def run_b200(args, rank, world):
     if matfree:
         out["matfree"] = matfree
     return out
+
+
+def assembly_kernels(ctx, dm, mode, reps=3):
+    """Re-assemble on an existing DeviceMesh `reps` times and return the kernel times of the LAST
+    pass (warm: the first launch of a kernel also pays its module load between the two events)."""
+    out = {}
+    for _ in range(reps):
+        ctx.sync()
+        ctx.prof_enable(True)
+        mats = dm.assemble_kle(mode)
+        ops = dm.assemble_ops(compact=True)
+        ctx.sync()
+        out = {k: ctx.prof_get(k) for k in ("elem_kle", "numeric")}
+        ctx.prof_enable(False)
+        values = sum(m.nblocks() * m.getBlockSizes()[0] * m.getBlockSizes()[1] * 8
+                     for m in list(mats.values()) + list(ops[:3]))
+        for m in list(mats.values()) + list(ops[:3]):
+            m.destroy()
+        del mats, ops
+    out["value_bytes"] = int(values)
+    out["classes"] = dm.congruence()[1]
+    return out
+
+
+def kernels_entry(k, peak, nel, ngl):
+    n_el, ms_el = k["elem_kle"]
+    n_nu, ms_nu = k["numeric"]
+    # element kernel: 16 pair moments, 7 / 15 fp64 instructions per full / reduced point and pair
+    # (DESIGN.md section 3), counted as 2 flop each, over the classes actually evaluated
+    nn = ngl ** 3
+    flop = 2.0 * nn * nn * (7 * ngl ** 3 + 15 * (ngl - 1) ** 3) * k["classes"]
+    return {"congruence_classes": int(k["classes"]), "elements": int(nel),
+            "elem_kle_ms": round(ms_el, 4), "elem_kle_TFLOPs": round(flop / (ms_el * 1e-3) / 1e12, 2) if ms_el else None,
+            "numeric_ms": round(ms_nu, 4), "numeric_launches": n_nu, "numeric_value_bytes": k["value_bytes"],
+            "numeric_GBs": round(k["value_bytes"] / (ms_nu * 1e-3) / 1e9, 1) if ms_nu else None,
+            "numeric_frac_of_peak": round(k["value_bytes"] / (ms_nu * 1e-3) / 1e9 / peak, 4) if ms_nu else None}
+
+
+def assembly_warm(args, ctx, fem, peak):
+    """Warm kernel times of the assembly, (a) on the bench mesh as the case builds it (uniform
+    box: ONE congruence class, the numeric pass is a pure HBM writer) and (b) on the perturbed
+    twin of the same mesh (every interior corner displaced by 0.15 h, no two
+    cells congruent: the graded input of the element kernel)."""
+    from pynama_b200.device_mesh import DeviceMesh
+    from pynama_b200.domain.box_mesh import BoxMesh
+    dm = fem.dom.getDeviceMesh()
+    mode = "NS" if getattr(fem.mat, "Kfs", None) is not None else "FS"
+    res = {"note": "third of three back-to-back assemblies on the same mesh tables; CUDA events around the "
+                   "element kernel and the numeric (COO -> node-block BSR) kernels; bytes = 8 B per stored "
+                   "value written once (SURVEY.md 8d-D4)",
+           "uniform": kernels_entry(assembly_kernels(ctx, dm, mode), peak, dm.nel, args.ngl)}
+    if int(os.environ.get("WORLD_SIZE", "1")) == 1:
+        m = fem.dom._mesh
+        pm = BoxMesh(m.nelem, m.lower, m.upper, m.ngl, perturb=0.15)
+        pdm = DeviceMesh(m.dim, m.ngl, pm.corner_xyz, pm.elem_nodes, pm.nnodes)
+        pdm.set_dof_class(fem.dom.getDofClasses())
+        res["perturbed"] = kernels_entry(assembly_kernels(ctx, pdm, mode), peak, pdm.nel, args.ngl)
+        pdm.destroy()
+    return res
 
 
 def assembly_report(asm, kern, fem, ndof, peak):

@@ -137,6 +137,14 @@ int pyn_mesh_graph_info(pyn_mesh* mesh, int64_t* npairs, int64_t* ncontrib, int*
  * (free-slip BC, mat_fs.py:158-172), 2 no-slip normal, 3 no-slip tangential
  * (mat_ns.py:59-75). */
 int pyn_mesh_set_dof_class(pyn_mesh* mesh, const uint8_t* cls);
+/* Congruence classes of element shapes.  getElemKLEMatrices / getElemKLEOperators
+ * (spectral.py:92-228) depend on an element only through its corner offsets, and the
+ * reference re-evaluates them for every cell of a uniform box (mat_fs.py:152-155,196-198);
+ * here elements whose corner offsets agree to tol * (largest offset in the mesh) share one
+ * set of element blocks.  pyn_mesh_create applies tol = 1e-13; tol <= 0 switches the
+ * merging off (one class per element).  *nclass (may be NULL) returns the class count. */
+int pyn_mesh_set_congruence(pyn_mesh* mesh, double tol, int64_t* nclass);
+int pyn_mesh_get_congruence(pyn_mesh* mesh, double* tol, int64_t* nclass);
 
 /* ---- element kernels (debug / parity export of raw element blocks) ---------
  * Spectral.getElemKLEMatrices (spectral.py:92-160): K_e [3nn x 3nn],
@@ -173,6 +181,27 @@ int pyn_assemble_ops(pyn_mesh* mesh, int compact, pyn_mat** curl, pyn_mat** srt,
  * 0 symbolic graph, 1 element KLE kernel, 2 KLE numeric, 3 element operator
  * kernel, 4 operator numeric */
 int pyn_mesh_phase_ms(pyn_mesh* mesh, int phase, double* ms);
+
+/* ---- immersed boundary, 2-D -------------------------------
+ * Replaces ImmersedBoundaryStatic.collectNodes / computeClose / computeDirac /
+ * buildIBMMatrix (src/cases/immersed_boundary.py:170-229,255-274; the dynamic
+ * computeClose :346-358) and ImmersedBody.getDiracs with the delta functions
+ * fourGrid / threeGrid / linear (src/domain/immersed_body.py:261-266,398-424).
+ * lag_xy: nlag*2 marker coordinates (HOST); cand_nodes / cand_xy: the Euler nodes
+ * of the affected cells, ascending node id, and their coordinates (HOST).
+ * D[l][n] = prod_axis phi(|x_n - X_l|/h)/h on the kept nodes of marker l;
+ * *H = scale_h*D (nlag*2 x n_euler_nodes*2), *S = scale_s*D^T, *A = H S, each
+ * with 2x2 blocks w*I (the reference sets the two dofs of a marker separately).
+ * kind: 0 fourGrid, 1 threeGrid, 2 linear; dynamic != 0 selects the dynamic
+ * body's node search.  *max_per_lag (may be NULL): longest row of D;
+ * affected (may be NULL): n_euler_nodes HOST bytes, 1 where a node has a positive
+ * weight.  A marker without Euler node is PYN_E_INVALID ("Lag Node without Euler",
+ * immersed_boundary.py:222-223). */
+int pyn_ibm_build(pyn_ctx* ctx, int64_t n_euler_nodes, int64_t nlag, const double* lag_xy,
+                  int64_t ncand, const int32_t* cand_nodes, const double* cand_xy, double h,
+                  double dl, double scale_h, double scale_s, int kind, int dynamic,
+                  pyn_mat** H, pyn_mat** S, pyn_mat** A, int64_t* max_per_lag,
+                  uint8_t* affected);
 
 /* ---- Mat (PETSc.Mat AIJ surface used by the hot path) --------------------------*/
 int pyn_mat_shape(pyn_mat* m, int64_t* nrows, int64_t* ncols, int* br, int* bc);

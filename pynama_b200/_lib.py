@@ -70,7 +70,11 @@ _PROTOS = {
     "pyn_mesh_destroy": [vp],
     "pyn_mesh_graph_info": [vp, P(c_i64), P(c_i64), P(c_int)],
     "pyn_mesh_set_dof_class": [vp, vp],
+    "pyn_mesh_set_congruence": [vp, c_dbl, P(c_i64)],
+    "pyn_mesh_get_congruence": [vp, P(c_dbl), P(c_i64)],
     "pyn_mesh_phase_ms": [vp, c_int, P(c_dbl)],
+    "pyn_ibm_build": [vp, c_i64, c_i64, vp, c_i64, vp, vp, c_dbl, c_dbl, c_dbl, c_dbl, c_int, c_int,
+                      P(vp), P(vp), P(vp), P(c_i64), vp],
     "pyn_elem_kle": [vp, c_i64, c_i64, vp, vp, vp],
     "pyn_elem_ops": [vp, c_i64, c_i64, vp, vp, vp, vp],
     "pyn_assemble_kle": [vp, c_int, P(vp)],

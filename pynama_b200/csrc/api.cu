@@ -30,6 +30,10 @@ struct PhaseTimer {
   }
 };
 
+// default matching tolerance of the congruence classes, relative to the largest element
+// extent: far above the rounding of generated coordinates (1e-16), far below the 1e-12
+// value parity of the assembled matrices
+constexpr double kDefaultCongruenceTol = 1e-13;
 constexpr int kProfPairs = 4096;
 void prof_drain(pyn_ctx* ctx) {
   if (ctx->prof_pending == 0) return;
@@ -211,6 +215,79 @@ int pyn_mem_used(pyn_ctx* ctx, int64_t* bytes) {
 }
 
 // ---- mesh ------------------------------------------------------------------------
+// Congruence classes of element shapes.  Two elements are congruent when the offsets of
+// their corners from corner 0, rounded to multiples of tol * (largest offset in the mesh),
+// are equal; the class representative is its lowest element.  tol <= 0: no merging.
+static int compute_classes(pyn_mesh* m, const double* corners, double tol) {
+  const int64_t nel = m->nel;
+  const int nv = (1 << m->dim) * m->dim;
+  m->congruence_tol = tol;
+  m->class_version++;
+  m->elem_class.release();
+  m->class_rep.release();
+  m->nclass = nel;
+  if (!(tol > 0.0) || nel < 2) return PYN_OK;
+  double scale = 0.0;
+  for (int64_t e = 0; e < nel; ++e) {
+    const double* X = corners + e * nv;
+    for (int k = m->dim; k < nv; ++k) scale = std::max(scale, std::fabs(X[k] - X[k % m->dim]));
+  }
+  if (!(scale > 0.0) || !std::isfinite(scale)) return PYN_OK;
+  const double inv_q = 1.0 / (tol * scale);
+  std::vector<int64_t> keys;                       // [nclass][nv] quantised offsets of the representatives
+  std::vector<int32_t> cls((size_t)nel), rep;
+  std::unordered_multimap<uint64_t, int32_t> table;
+  table.reserve(1024);
+  std::vector<int64_t> key((size_t)nv);
+  for (int64_t e = 0; e < nel; ++e) {
+    const double* X = corners + e * nv;
+    uint64_t h = 0x9E3779B97F4A7C15ull;
+    for (int k = 0; k < nv; ++k) {
+      key[k] = std::llround((X[k] - X[k % m->dim]) * inv_q);
+      h = (h ^ (uint64_t)key[k]) * 0xFF51AFD7ED558CCDull;
+      h ^= h >> 29;
+    }
+    int32_t found = -1;
+    auto range = table.equal_range(h);
+    for (auto it = range.first; it != range.second; ++it)
+      if (std::equal(key.begin(), key.end(), keys.begin() + (size_t)it->second * nv)) {
+        found = it->second;
+        break;
+      }
+    if (found < 0) {
+      found = (int32_t)rep.size();
+      rep.push_back((int32_t)e);
+      keys.insert(keys.end(), key.begin(), key.end());
+      table.emplace(h, found);
+    }
+    cls[(size_t)e] = found;
+  }
+  if ((int64_t)rep.size() == nel) return PYN_OK;   // nothing merged: identity, no tables
+  m->nclass = (int64_t)rep.size();
+  PYN_CHECK(m->elem_class.alloc(m->ctx, nel));
+  PYN_CHECK(m->elem_class.upload(cls.data(), nel));
+  PYN_CHECK(m->class_rep.alloc(m->ctx, m->nclass));
+  PYN_CHECK(m->class_rep.upload(rep.data(), m->nclass));
+  return PYN_OK;
+}
+
+int pyn_mesh_set_congruence(pyn_mesh* mesh, double tol, int64_t* nclass) {
+  PYN_REQUIRE(mesh, "pyn_mesh_set_congruence: null mesh");
+  const int64_t n = mesh->nel * (1 << mesh->dim) * mesh->dim;
+  std::vector<double> h((size_t)n);
+  PYN_CHECK(mesh->corners.download(h.data(), n));
+  PYN_CHECK(compute_classes(mesh, h.data(), tol));
+  if (nclass) *nclass = mesh->nclass;
+  return PYN_OK;
+}
+
+int pyn_mesh_get_congruence(pyn_mesh* mesh, double* tol, int64_t* nclass) {
+  PYN_REQUIRE(mesh, "pyn_mesh_get_congruence: null mesh");
+  if (tol) *tol = mesh->congruence_tol;
+  if (nclass) *nclass = mesh->nclass;
+  return PYN_OK;
+}
+
 int pyn_mesh_create(pyn_ctx* ctx, int dim, int ngl, int64_t nel, int64_t nnodes,
                     const double* corner_xyz, const int32_t* elem_nodes, pyn_mesh** out) {
   PYN_REQUIRE(ctx && corner_xyz && elem_nodes && out, "pyn_mesh_create: null argument");
@@ -247,6 +324,7 @@ int pyn_mesh_create(pyn_ctx* ctx, int dim, int ngl, int64_t nel, int64_t nnodes,
   if (rc == PYN_OK) rc = m->elem_nodes.upload(elem_nodes, nel * m->nn);
   if (rc == PYN_OK) rc = m->dofcls.alloc(ctx, nnodes * dim);
   if (rc == PYN_OK) rc = m->dofcls.zero();
+  if (rc == PYN_OK) rc = compute_classes(m, corner_xyz, kDefaultCongruenceTol);
   if (rc == PYN_OK) rc = build_n2e(m);
   if (rc == PYN_OK) {
     std::vector<int32_t> pb((size_t)m->nn * m->nn);
@@ -285,6 +363,10 @@ int pyn_mesh_set_dof_class(pyn_mesh* mesh, const uint8_t* cls) {
   const int64_t n = mesh->nnodes * mesh->dim;
   for (int64_t i = 0; i < n; ++i) PYN_REQUIRE(cls[i] < 4, "dof class %d at %lld", cls[i], (long long)i);
   PYN_CHECK(mesh->dofcls.upload(cls, n));
+  std::vector<uint8_t> pack((size_t)mesh->nnodes, 0);
+  for (int64_t i = 0; i < n; ++i) pack[(size_t)(i / mesh->dim)] |= (uint8_t)(cls[i] << (2 * (i % mesh->dim)));
+  PYN_CHECK(mesh->nodecls.alloc(mesh->ctx, mesh->nnodes));
+  PYN_CHECK(mesh->nodecls.upload(pack.data(), mesh->nnodes));
   PYN_CUDA(cudaStreamSynchronize(mesh->ctx->stream));
   mesh->has_cls = true;
   return PYN_OK;
@@ -298,12 +380,13 @@ int pyn_mesh_phase_ms(pyn_mesh* mesh, int phase, double* ms) {
 
 // ---- element export (parity / debug) ------------------------------------------------
 // block-major EBS -> the reference's dense row-major element matrix
-static void ebs_to_dense(const double* ebs, int64_t ne, int nn, int br, int bc, double* dense) {
+static void ebs_to_dense(const double* ebs, int stride, int off, int64_t ne, int nn, int br, int bc,
+                         double* dense) {
   const int64_t ld = (int64_t)nn * bc;
   for (int64_t e = 0; e < ne; ++e)
     for (int a = 0; a < nn; ++a)
       for (int b = 0; b < nn; ++b) {
-        const double* blk = ebs + (((int64_t)e * nn + a) * nn + b) * br * bc;
+        const double* blk = ebs + (((int64_t)e * nn + a) * nn + b) * stride + off;
         for (int i = 0; i < br; ++i)
           for (int j = 0; j < bc; ++j)
             dense[e * (int64_t)nn * br * ld + ((int64_t)a * br + i) * ld + (int64_t)b * bc + j] =
@@ -317,27 +400,15 @@ int pyn_elem_kle(pyn_mesh* mesh, int64_t e0, int64_t ne, double* K_e, double* Rw
   pyn_ctx* ctx = mesh->ctx;
   const int nn = mesh->nn, d = mesh->dim, dw = mesh->dim_w;
   const int64_t np = ne * nn * nn;
-  DevBuf<double> k, rw, rd;
-  PYN_CHECK(k.alloc(ctx, np * d * d));
-  PYN_CHECK(rw.alloc(ctx, np * d * dw));
-  PYN_CHECK(rd.alloc(ctx, np * d));
-  PYN_CHECK(launch_elem_kle(mesh, e0, ne, k.p, rw.p, rd.p));
-  std::vector<double> h;
-  if (K_e) {
-    h.resize(np * d * d);
-    PYN_CHECK(k.download(h.data(), np * d * d));
-    ebs_to_dense(h.data(), ne, nn, d, d, K_e);
-  }
-  if (Rw_e) {
-    h.resize(np * d * dw);
-    PYN_CHECK(rw.download(h.data(), np * d * dw));
-    ebs_to_dense(h.data(), ne, nn, d, dw, Rw_e);
-  }
-  if (Rd_e) {
-    h.resize(np * d);
-    PYN_CHECK(rd.download(h.data(), np * d));
-    ebs_to_dense(h.data(), ne, nn, d, 1, Rd_e);
-  }
+  const int rs = kle_record_stride(d);
+  DevBuf<double> ebs;
+  PYN_CHECK(ebs.alloc(ctx, np * rs));
+  PYN_CHECK(launch_elem_kle(mesh, e0, ne, nullptr, ebs.p));
+  std::vector<double> h((size_t)(np * rs));
+  PYN_CHECK(ebs.download(h.data(), np * rs));
+  if (K_e) ebs_to_dense(h.data(), rs, 0, ne, nn, d, d, K_e);
+  if (Rw_e) ebs_to_dense(h.data(), rs, kle_record_off_rw(d), ne, nn, d, dw, Rw_e);
+  if (Rd_e) ebs_to_dense(h.data(), rs, kle_record_off_rd(d), ne, nn, d, 1, Rd_e);
   PYN_CUDA(cudaStreamSynchronize(ctx->stream));
   return PYN_OK;
 }
@@ -371,7 +442,7 @@ int pyn_elem_ops(pyn_mesh* mesh, int64_t e0, int64_t ne, double* SrT_e, double* 
   PYN_CHECK(dv.alloc(ctx, np * ds * d));
   PYN_CHECK(c.alloc(ctx, np * dw * d));
   PYN_CHECK(w.alloc(ctx, ne * nn));
-  PYN_CHECK(launch_elem_ops(mesh, e0, ne, s.p, dv.p, c.p, w.p));
+  PYN_CHECK(launch_elem_ops(mesh, e0, ne, nullptr, s.p, dv.p, c.p, w.p));
   std::vector<int32_t> pb((size_t)nn * ppa);
   PYN_CHECK(mesh->stencil.pair_b.download(pb.data(), (int64_t)nn * ppa));
   std::vector<double> h;
@@ -396,13 +467,15 @@ int pyn_elem_ops(pyn_mesh* mesh, int64_t e0, int64_t ne, double* SrT_e, double* 
 }
 
 // ---- assembly ----------------------------------------------------------------------
-static MatSpec kle_spec(pyn_mesh* mesh, int br, int bc, const double* ebs, double sign, bool colcls,
+static MatSpec kle_spec(pyn_mesh* mesh, int br, int bc, const double* ebs, int off, double sign, bool colcls,
                         uint32_t pairmask, uint32_t diagmask, double d1, double d2, double d3) {
   MatSpec s;
   s.br = br;
   s.bc = bc;
   s.graph = &mesh->dense;
   s.ebs = ebs;
+  s.ebs_stride = kle_record_stride(mesh->dim);
+  s.ebs_off = off;
   s.ebs_pairs = (int64_t)mesh->nn * mesh->nn;
   s.ebs_ppa = 0;
   s.pair_map = nullptr;
@@ -428,42 +501,53 @@ int pyn_assemble_kle(pyn_mesh* mesh, int mode, pyn_mat** out8) {
   PYN_REQUIRE(mesh->has_cls, "pyn_assemble_kle: set the dof classes first");
   pyn_ctx* ctx = mesh->ctx;
   const int d = mesh->dim, dw = mesh->dim_w, nn = mesh->nn;
-  const int64_t np = mesh->nel * nn * nn;
+  const int64_t np = mesh->nclass * nn * nn;       // one set of blocks per congruence class
   for (int i = 0; i < 8; ++i) out8[i] = nullptr;
-  DevBuf<double> k, rw, rd;
-  PYN_CHECK(k.alloc(ctx, np * d * d));
-  PYN_CHECK(rw.alloc(ctx, np * d * dw));
-  PYN_CHECK(rd.alloc(ctx, np * d));
+  const int oK = 0, oW = kle_record_off_rw(d), oD = kle_record_off_rd(d);
+  DevBuf<double> ebs;
+  PYN_CHECK(ebs.alloc(ctx, np * kle_record_stride(d)));
   {
     PhaseTimer t(ctx);
-    PYN_CHECK(launch_elem_kle(mesh, 0, mesh->nel, k.p, rw.p, rd.p));
+    PYN_CHECK(launch_elem_kle(mesh, 0, mesh->nclass, mesh->class_rep.p, ebs.p));
     mesh->phase_ms[1] = t.stop();
   }
   PhaseTimer t(ctx);
   const uint32_t bc_all = 0xE;  // classes 1,2,3
   // K: free x free, +1 on every constrained diagonal (mat_fs.py:179-189, mat_ns.py:116-130)
-  MatSpec sK = kle_spec(mesh, d, d, k.p, 1.0, true, PM(0, 0), bc_all, 1.0, 1.0, 1.0);
+  MatSpec sK = kle_spec(mesh, d, d, ebs.p, oK, 1.0, true, PM(0, 0), bc_all, 1.0, 1.0, 1.0);
   // Krhs: -K_e[free, constrained], +1 on the constrained diagonal (mat_fs.py:174-177,188-189)
-  MatSpec sKrhs = kle_spec(mesh, d, d, k.p, -1.0, true, PM(0, 1) | PM(0, 2) | PM(0, 3), bc_all, 1.0, 1.0, 1.0);
+  MatSpec sKrhs = kle_spec(mesh, d, d, ebs.p, oK, -1.0, true, PM(0, 1) | PM(0, 2) | PM(0, 3), bc_all, 1.0, 1.0, 1.0);
   // Rw: free rows, all vorticity columns (mat_fs.py:185-186)
-  MatSpec sRw = kle_spec(mesh, d, dw, rw.p, 1.0, false, PM(0, 0), 0, 0, 0, 0);
+  MatSpec sRw = kle_spec(mesh, d, dw, ebs.p, oW, 1.0, false, PM(0, 0), 0, 0, 0, 0);
   // Rd: filled only by buildNS (mat_ns.py:125-127); empty in FS mode (mat_fs.py:155)
-  MatSpec sRd = kle_spec(mesh, d, 1, rd.p, 1.0, false, mode == 1 ? PM(0, 0) : 0u, 0, 0, 0, 0);
-  PYN_CHECK(assemble_matrix(mesh, sK, &out8[PYN_MAT_K]));
-  PYN_CHECK(assemble_matrix(mesh, sKrhs, &out8[PYN_MAT_KRHS]));
-  PYN_CHECK(assemble_matrix(mesh, sRw, &out8[PYN_MAT_RW]));
-  PYN_CHECK(assemble_matrix(mesh, sRd, &out8[PYN_MAT_RD]));
+  MatSpec sRd = kle_spec(mesh, d, 1, ebs.p, oD, 1.0, false, mode == 1 ? PM(0, 0) : 0u, 0, 0, 0, 0);
+  static_assert(PYN_MAT_K == 0 && PYN_MAT_KRHS == 1 && PYN_MAT_RW == 2 && PYN_MAT_RD == 3, "matrix order");
+  if (getenv("PYN_ASSEMBLE_PER_MATRIX") == nullptr) {
+    const MatSpec four[4] = {sK, sKrhs, sRw, sRd};
+    PYN_CHECK(assemble_kle_fused(mesh, four, out8));
+  } else {                                         // one gather pass per matrix (debug / comparison)
+    PYN_CHECK(assemble_matrix(mesh, sK, &out8[PYN_MAT_K]));
+    PYN_CHECK(assemble_matrix(mesh, sKrhs, &out8[PYN_MAT_KRHS]));
+    PYN_CHECK(assemble_matrix(mesh, sRw, &out8[PYN_MAT_RW]));
+    PYN_CHECK(assemble_matrix(mesh, sRd, &out8[PYN_MAT_RD]));
+  }
   if (mode == 1) {
     // Kfs: tang x free, free x tang, tang x tang, -1 on tang diagonal (mat_ns.py:86-97,132-133)
-    MatSpec sKfs = kle_spec(mesh, d, d, k.p, 1.0, true, PM(3, 0) | PM(0, 3) | PM(3, 3), 1u << 3, 0, 0, -1.0);
+    MatSpec sKfs = kle_spec(mesh, d, d, ebs.p, oK, 1.0, true, PM(3, 0) | PM(0, 3) | PM(3, 3), 1u << 3, 0, 0, -1.0);
     // Krhsfs: -K_e[tang|free, normal], 1 on the normal diagonal (mat_ns.py:107-114,140-142)
-    MatSpec sKrhsfs = kle_spec(mesh, d, d, k.p, -1.0, true, PM(3, 2) | PM(0, 2), 1u << 2, 0, 1.0, 0);
-    MatSpec sRwfs = kle_spec(mesh, d, dw, rw.p, 1.0, false, PM(3, 0), 0, 0, 0, 0);
-    MatSpec sRdfs = kle_spec(mesh, d, 1, rd.p, 1.0, false, PM(3, 0), 0, 0, 0, 0);
-    PYN_CHECK(assemble_matrix(mesh, sKfs, &out8[PYN_MAT_KFS]));
-    PYN_CHECK(assemble_matrix(mesh, sKrhsfs, &out8[PYN_MAT_KRHSFS]));
-    PYN_CHECK(assemble_matrix(mesh, sRwfs, &out8[PYN_MAT_RWFS]));
-    PYN_CHECK(assemble_matrix(mesh, sRdfs, &out8[PYN_MAT_RDFS]));
+    MatSpec sKrhsfs = kle_spec(mesh, d, d, ebs.p, oK, -1.0, true, PM(3, 2) | PM(0, 2), 1u << 2, 0, 1.0, 0);
+    MatSpec sRwfs = kle_spec(mesh, d, dw, ebs.p, oW, 1.0, false, PM(3, 0), 0, 0, 0, 0);
+    MatSpec sRdfs = kle_spec(mesh, d, 1, ebs.p, oD, 1.0, false, PM(3, 0), 0, 0, 0, 0);
+    static_assert(PYN_MAT_KFS == 4 && PYN_MAT_KRHSFS == 5 && PYN_MAT_RWFS == 6 && PYN_MAT_RDFS == 7, "matrix order");
+    if (getenv("PYN_ASSEMBLE_PER_MATRIX") == nullptr) {
+      const MatSpec four[4] = {sKfs, sKrhsfs, sRwfs, sRdfs};
+      PYN_CHECK(assemble_kle_fused(mesh, four, out8 + 4));
+    } else {
+      PYN_CHECK(assemble_matrix(mesh, sKfs, &out8[PYN_MAT_KFS]));
+      PYN_CHECK(assemble_matrix(mesh, sKrhsfs, &out8[PYN_MAT_KRHSFS]));
+      PYN_CHECK(assemble_matrix(mesh, sRwfs, &out8[PYN_MAT_RWFS]));
+      PYN_CHECK(assemble_matrix(mesh, sRdfs, &out8[PYN_MAT_RDFS]));
+    }
   }
   mesh->phase_ms[2] = t.stop();
   PYN_CUDA(cudaStreamSynchronize(ctx->stream));
@@ -477,16 +561,16 @@ int pyn_assemble_ops(pyn_mesh* mesh, int compact, pyn_mat** curl, pyn_mat** srt,
   PYN_CHECK(ensure_stencil(mesh));
   const int d = mesh->dim, dw = mesh->dim_w, ds = mesh->dim_s, nn = mesh->nn;
   const int ppa = mesh->stencil.ppa;
-  const int64_t np = mesh->nel * nn * ppa;
+  const int64_t np = mesh->nclass * nn * ppa;
   DevBuf<double> s, dv, c, we, winv;
   PYN_CHECK(s.alloc(ctx, np * ds * d));
   PYN_CHECK(dv.alloc(ctx, np * ds * d));
   PYN_CHECK(c.alloc(ctx, np * dw * d));
-  PYN_CHECK(we.alloc(ctx, mesh->nel * nn));
+  PYN_CHECK(we.alloc(ctx, mesh->nclass * nn));
   PYN_CHECK(winv.alloc(ctx, mesh->nnodes));
   {
     PhaseTimer t(ctx);
-    PYN_CHECK(launch_elem_ops(mesh, 0, mesh->nel, s.p, dv.p, c.p, we.p));
+    PYN_CHECK(launch_elem_ops(mesh, 0, mesh->nclass, mesh->class_rep.p, s.p, dv.p, c.p, we.p));
     mesh->phase_ms[3] = t.stop();
   }
   PhaseTimer t(ctx);

@@ -21,13 +21,20 @@ struct HostMat {
 };
 
 static int fetch_host(pyn_mat* m, HostMat* h, bool with_values) {
-  const NodeGraph* g = &m->mesh->dense;  // reference pattern = dense node graph (x) block
   h->rowptr.resize(m->nbrows + 1);
   h->colidx.resize(m->nblocks);
-  h->g_rowptr.resize(g->nrows + 1);
-  h->g_colidx.resize(g->nslots);
   PYN_CHECK(m->rowptr.download(h->rowptr.data(), m->nbrows + 1));
   PYN_CHECK(m->colidx.download(h->colidx.data(), m->nblocks));
+  if (m->free_pattern) {                 // reference pattern = the matrix's own blocks
+    if (with_values) {
+      h->val.resize(m->nblocks * m->br * m->bc);
+      PYN_CHECK(m->val.download(h->val.data(), m->nblocks * m->br * m->bc));
+    }
+    return PYN_OK;
+  }
+  const NodeGraph* g = &m->mesh->dense;  // reference pattern = dense node graph (x) block
+  h->g_rowptr.resize(g->nrows + 1);
+  h->g_colidx.resize(g->nslots);
   PYN_CHECK(g->rowptr.download(h->g_rowptr.data(), g->nrows + 1));
   PYN_CHECK(g->colidx.download(h->g_colidx.data(), g->nslots));
   if (with_values) {
@@ -53,6 +60,19 @@ static inline bool ref_entry(const pyn_mat* m, const HostMat& h, int64_t r, int3
 template <typename F>
 static void walk_reference(const pyn_mat* m, const HostMat& h, bool with_values, F fn) {
   const int br = m->br, bc = m->bc, bb = br * bc;
+  if (m->free_pattern) {
+    for (int64_t r = 0; r < m->nbrows; ++r) {
+      const int64_t p0 = h.rowptr[r], nb = h.rowptr[r + 1] - p0;
+      for (int i = 0; i < br; ++i)
+        for (int64_t u = 0; u < nb; ++u)
+          for (int j = 0; j < bc; ++j) {
+            if (m->diag_only && i != j) continue;
+            fn(r * br + i, (int64_t)h.colidx[p0 + u] * bc + j,
+               with_values ? h.val[p0 * bb + (int64_t)(i * bc + j) * nb + u] : 0.0);
+          }
+    }
+    return;
+  }
   for (int64_t r = 0; r < m->nbrows; ++r) {
     const int64_t p0 = h.rowptr[r], nb = h.rowptr[r + 1] - p0;
     for (int i = 0; i < br; ++i) {

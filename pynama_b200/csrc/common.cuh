@@ -5,7 +5,10 @@
 #include <stdio.h>
 #include <string.h>
 
+#include <algorithm>
+#include <cmath>
 #include <string>
+#include <unordered_map>
 #include <vector>
 
 #include "../../include/pynama_b200.h"

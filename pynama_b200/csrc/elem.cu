@@ -13,8 +13,10 @@
 //   evaluates just those ("stencil" pairs); every other entry of the
 //   reference's dense blocks is an exact 0.0.
 //
-// Element block store (EBS) layout: block-major, [element][pair][i][j], so the
-// assembly gather reads whole node blocks contiguously.
+// Element block store (EBS) layout of k1+k2: one record per (element, node pair),
+// [K (dim x dim) | pad] [Rw (dim x dim_w) | Rd (dim) | pad], 12 + 12 doubles in 3-D, 4 + 4 in 2-D
+// (KleRecord, elem.cuh): whole 32-byte sectors, so the assembly gather reads a pair's
+// three blocks with 256-bit loads.  k3 stores block-major, [element][pair][i][j].
 #include "elem.cuh"
 #include "elem_math.cuh"
 
@@ -121,7 +123,8 @@ struct PairMoments {
 
 // scr holds one BB-double block per lane (lane-major); write them to dst[blk*BB ..) so that
 // consecutive lanes of a store instruction touch consecutive doubles.  All 32 lanes call.
-template <int BB>
+// (lane l's block starts at scr + l*LD; LD = BB+1 keeps the lanes' writes off a common bank)
+template <int BB, int LD>
 __device__ __forceinline__ void warp_store_blocks(const double* scr, double* __restrict__ dst,
                                                   long long blk, bool valid, int lane) {
   __syncwarp();
@@ -131,7 +134,7 @@ __device__ __forceinline__ void warp_store_blocks(const double* scr, double* __r
     const int src = idx / BB, q = idx - src * BB;
     const long long bl = __shfl_sync(0xffffffffu, blk, src);
     const int ok = __shfl_sync(0xffffffffu, (int)valid, src);
-    if (ok) __stcs(dst + bl * BB + q, scr[idx]);
+    if (ok) __stcs(dst + bl * BB + q, scr[src * LD + q]);
   }
   __syncwarp();
 }
@@ -143,13 +146,14 @@ __device__ __forceinline__ void warp_store_blocks(const double* scr, double* __r
 template <int DIM, int AT, int NTH>
 __global__ void __launch_bounds__(NTH, 1)
 elem_kle_kernel(const ElemTables* __restrict__ tab, const double* __restrict__ corners,
-                int64_t e0, int natiles, int ntile, int GC, double* __restrict__ ebsK,
-                double* __restrict__ ebsRw, double* __restrict__ ebsRd) {
+                int64_t e0, const int32_t* __restrict__ rep, int natiles, int ntile, int GC,
+                double* __restrict__ ebs) {
   constexpr int NC = 1 << DIM;
   constexpr int DW = DIM == 2 ? 1 : 3;
   extern __shared__ __align__(16) double smem[];
   const int nn = tab->nn;
-  const int64_t el = blockIdx.x / natiles;          // local element in this batch
+  const int64_t el = blockIdx.x / natiles;          // position in this batch (= index in the store)
+  const int64_t esrc = rep ? (int64_t)rep[el] : e0 + el;   // element whose corners are used
   const int atile = blockIdx.x % natiles;
   const int tid = threadIdx.x;
 
@@ -164,7 +168,7 @@ elem_kle_kernel(const ElemTables* __restrict__ tab, const double* __restrict__ c
   uint32_t* sGpT = sCornT + 8;                               // [npts(full)] then [npts(red)]
   const int npts_full = tab->rule[RULE_FULL].npts;
 
-  if (tid < NC * DIM) sX[tid] = corners[(e0 + el) * NC * DIM + tid];
+  if (tid < NC * DIM) sX[tid] = corners[esrc * NC * DIM + tid];
   for (int i = tid; i < 2 * kMaxPts1d * kMaxNgl; i += NTH) {
     const int q = i / (kMaxPts1d * kMaxNgl), r = i % (kMaxPts1d * kMaxNgl);
     const Rule1D& rl = tab->rule[q == 0 ? RULE_FULL : RULE_RED];
@@ -313,12 +317,14 @@ elem_kle_kernel(const ElemTables* __restrict__ tab, const double* __restrict__ c
       }
     }
   }
-  // Epilogue: expand the moments and store block-major ([pair][i][j]).  A lane's block is BB
-  // consecutive doubles, so the warp transposes through a private shared-memory tile and writes
-  // runs of 32 consecutive doubles (the lanes' blocks are adjacent when their b are).
+  // Epilogue: expand the moments into the pair's record [K | pad | Rw | Rd | pad] (KleRecord) and
+  // store record-major.  A lane's record is RS consecutive doubles, so the warp transposes
+  // through a private shared-memory tile and writes runs of 32 consecutive doubles (the lanes'
+  // records are adjacent when their b are).
   __syncthreads();                                   // staging buffers are free now
+  constexpr int RS = KleRecord<DIM>::RS, OW = KleRecord<DIM>::OFF_RW, OD = KleRecord<DIM>::OFF_RD;
   const int lane = tid & 31;
-  double* scr = smem + (size_t)(tid >> 5) * 32 * (DIM * DIM);
+  double* scr = smem + (size_t)(tid >> 5) * 32 * (RS + 1);
 #pragma unroll
   for (int t = 0; t < AT; ++t) {
     const int a = a_first + t;
@@ -329,27 +335,30 @@ elem_kle_kernel(const ElemTables* __restrict__ tab, const double* __restrict__ c
 #pragma unroll
     for (int k = 1; k < DIM; ++k) tr += m.M[k][k];
     const double dg = m.L + kAlphaW * tr;
+    double* rec = scr + lane * (RS + 1);
 #pragma unroll
     for (int c = 0; c < DIM; ++c)
 #pragma unroll
       for (int e = 0; e < DIM; ++e) {
         double v = kAlphaD * m.M[c][e] - kAlphaW * m.M[e][c];
         if (c == e) v += dg;
-        scr[lane * (DIM * DIM) + c * DIM + e] = v;
+        rec[c * DIM + e] = v;
       }
-    warp_store_blocks<DIM * DIM>(scr, ebsK, blk, valid, lane);
 #pragma unroll
     for (int c = 0; c < DIM; ++c)
 #pragma unroll
       for (int e = 0; e < DW; ++e) {
         double v = 0.0;
         if (DIM == 2 || c != e) v = curl_w<DIM>(c, e, m.N) + kAlphaW * curl_v<DIM>(e, c, m.Q);
-        scr[lane * (DIM * DW) + c * DW + e] = v;
+        rec[OW + c * DW + e] = v;
       }
-    warp_store_blocks<DIM * DW>(scr, ebsRw, blk, valid, lane);
 #pragma unroll
-    for (int c = 0; c < DIM; ++c) scr[lane * DIM + c] = kAlphaD * m.Q[c] - m.N[c];
-    warp_store_blocks<DIM>(scr, ebsRd, blk, valid, lane);
+    for (int c = 0; c < DIM; ++c) rec[OD + c] = kAlphaD * m.Q[c] - m.N[c];
+#pragma unroll
+    for (int c = DIM * DIM; c < OW; ++c) rec[c] = 0.0;
+#pragma unroll
+    for (int c = OD + DIM; c < RS; ++c) rec[c] = 0.0;
+    warp_store_blocks<RS, RS + 1>(scr, ebs, blk, valid, lane);
   }
 }
 
@@ -357,7 +366,7 @@ template <int DIM>
 __global__ void __launch_bounds__(128)
 elem_ops_kernel(const ElemTables* __restrict__ tab, const double* __restrict__ corners,
                 const int32_t* __restrict__ pair_b, int ppa, int64_t e0,
-                double* __restrict__ ebsSrT, double* __restrict__ ebsDiv,
+                const int32_t* __restrict__ rep, double* __restrict__ ebsSrT, double* __restrict__ ebsDiv,
                 double* __restrict__ ebsCurl, double* __restrict__ ebsW) {
   constexpr int NC = 1 << DIM;
   constexpr int DW = DIM == 2 ? 1 : 3;
@@ -371,7 +380,8 @@ elem_ops_kernel(const ElemTables* __restrict__ tab, const double* __restrict__ c
   double* sWd = sJinv + nn * DIM * DIM;    // [nn]
   const Rule1D& rule = tab->rule[RULE_NODAL];
 
-  if (tid < NC * DIM) sX[tid] = corners[(e0 + el) * NC * DIM + tid];
+  const int64_t esrc = rep ? (int64_t)rep[el] : e0 + el;
+  if (tid < NC * DIM) sX[tid] = corners[esrc * NC * DIM + tid];
   __syncthreads();
   for (int g = tid; g < nn; g += nth) {
     double det;
@@ -430,13 +440,12 @@ static KleShape kle_launch_shape(const pyn_mesh* mesh) {
   s.gc = gc;
   s.smem = (size_t)(1 << dim) * dim * 8 + gc * per_pt + sizeof(KleSmemTab) +
            4 * ((size_t)nn + 8 + npts_max + mesh->htab.rule[RULE_RED].npts);
-  const size_t scratch = (size_t)s.nth * dim * dim * 8;      // epilogue transpose tiles
+  const size_t scratch = (size_t)s.nth * (kle_record_stride(dim) + 1) * 8;      // epilogue transpose tiles
   if (s.smem < scratch) s.smem = scratch;
   return s;
 }
 
-int launch_elem_kle(pyn_mesh* mesh, int64_t e0, int64_t ne, double* ebsK, double* ebsRw,
-                    double* ebsRd) {
+int launch_elem_kle(pyn_mesh* mesh, int64_t e0, int64_t ne, const int32_t* rep, double* ebs) {
   pyn_ctx* ctx = mesh->ctx;
   if (ne <= 0) return PYN_OK;
   const KleShape s = kle_launch_shape(mesh);
@@ -448,7 +457,7 @@ int launch_elem_kle(pyn_mesh* mesh, int64_t e0, int64_t ne, double* ebsK, double
     PYN_CUDA(cudaFuncSetAttribute(elem_kle_kernel<DIM, AT, NTH>,                                     \
                                   cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s.smem));        \
     elem_kle_kernel<DIM, AT, NTH><<<grid, NTH, s.smem, ctx->stream>>>(                               \
-        mesh->dtab.p, mesh->corners.p, e0, s.natiles, s.ntile, s.gc, ebsK, ebsRw, ebsRd);            \
+        mesh->dtab.p, mesh->corners.p, e0, rep, s.natiles, s.ntile, s.gc, ebs);            \
   } while (0)
   if (mesh->dim == 2) {
     if (s.nth == 256) KLE_CALL(2, 4, 256); else KLE_CALL(2, 2, 512);
@@ -461,8 +470,8 @@ int launch_elem_kle(pyn_mesh* mesh, int64_t e0, int64_t ne, double* ebsK, double
   return PYN_OK;
 }
 
-int launch_elem_ops(pyn_mesh* mesh, int64_t e0, int64_t ne, double* ebsSrT, double* ebsDiv,
-                    double* ebsCurl, double* ebsW) {
+int launch_elem_ops(pyn_mesh* mesh, int64_t e0, int64_t ne, const int32_t* rep, double* ebsSrT,
+                    double* ebsDiv, double* ebsCurl, double* ebsW) {
   pyn_ctx* ctx = mesh->ctx;
   if (ne <= 0) return PYN_OK;
   PYN_REQUIRE(mesh->has_stencil, "stencil graph not built");
@@ -473,12 +482,12 @@ int launch_elem_ops(pyn_mesh* mesh, int64_t e0, int64_t ne, double* ebsSrT, doub
     PYN_CUDA(cudaFuncSetAttribute(elem_ops_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     elem_ops_kernel<2><<<grid, block, smem, ctx->stream>>>(mesh->dtab.p, mesh->corners.p,
                                                            mesh->stencil.pair_b.p, mesh->stencil.ppa, e0,
-                                                           ebsSrT, ebsDiv, ebsCurl, ebsW);
+                                                           rep, ebsSrT, ebsDiv, ebsCurl, ebsW);
   } else {
     PYN_CUDA(cudaFuncSetAttribute(elem_ops_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     elem_ops_kernel<3><<<grid, block, smem, ctx->stream>>>(mesh->dtab.p, mesh->corners.p,
                                                            mesh->stencil.pair_b.p, mesh->stencil.ppa, e0,
-                                                           ebsSrT, ebsDiv, ebsCurl, ebsW);
+                                                           rep, ebsSrT, ebsDiv, ebsCurl, ebsW);
   }
   PYN_LAUNCHED(ctx);
   return PYN_OK;

@@ -22,6 +22,10 @@ struct NodeGraph {
   DevBuf<int32_t> colidx;         // [nslots]
   DevBuf<int64_t> cptr;           // [nslots+1]
   DevBuf<int2> csrc;              // [ncontrib] (element, local pair id)
+  // the same list with the element replaced by its congruence class (= its index in the
+  // element block store), rebuilt when the classes change; unused while nclass == nel
+  mutable DevBuf<int2> csrc_cls;
+  mutable int64_t cls_version = -1;
 };
 
 }  // namespace pyn
@@ -35,7 +39,17 @@ struct pyn_mesh {
   pyn::DevBuf<double> corners;             // [nel][2^dim][dim]
   pyn::DevBuf<int32_t> elem_nodes;         // [nel][nn]
   pyn::DevBuf<uint8_t> dofcls;             // [nnodes*dim]
+  pyn::DevBuf<uint8_t> nodecls;            // [nnodes] the dof classes of a node, 2 bits per dof
   bool has_cls = false;
+  // congruence classes of element shapes: elements whose corner offsets agree to
+  // congruence_tol share one set of element blocks (the reference recomputes identical
+  // blocks for every congruent cell).  nclass == nel: nothing merged,
+  // elem_class / class_rep unallocated.
+  int64_t nclass = 0;
+  int64_t class_version = 0;               // bumped by every change of the classes
+  double congruence_tol = 0.0;
+  pyn::DevBuf<int32_t> elem_class;         // [nel] class of the element
+  pyn::DevBuf<int32_t> class_rep;          // [nclass] lowest element of the class
   // node -> (element, local index), ascending element
   pyn::DevBuf<int64_t> n2e_ptr;            // [nnodes+1]
   pyn::DevBuf<int2> n2e;                   // [nel*nn]
@@ -69,6 +83,10 @@ struct pyn_mat {
   uint32_t pairmask = 0xFFFF;
   uint32_t diagmask = 0;
   bool ref_dense = true;           // reference pattern lives on the dense graph
+  // free_pattern: a matrix that does not come from a mesh graph (mesh == NULL; the immersed-
+  // boundary H, S, A): its reference AIJ pattern is its own blocks, only the diagonal entries
+  // of a block when diag_only (blocks w*I)
+  bool free_pattern = false, diag_only = false;
   // row-partitioned run: rows [0, halo->n_own) are this rank's; x gets its ghost entries
   // refreshed before every product (comm.cu)
   pyn_halo* halo = nullptr;

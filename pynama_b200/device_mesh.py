@@ -58,6 +58,21 @@ class DeviceMesh:
         call("pyn_mesh_phase_ms", self._h, PHASES[name], ctypes.byref(ms))
         return ms.value
 
+    def set_congruence(self, tol):
+        """Merge elements whose corner offsets agree to tol * (largest offset in the mesh) into one
+        congruence class evaluated once (default at creation: 1e-13); tol <= 0: every element is
+        evaluated on its own, as Domain.computeLocalKLEMats does per cell (domain.py:262-276).
+        Returns the number of classes."""
+        n = c_i64()
+        call("pyn_mesh_set_congruence", self._h, float(tol), ctypes.byref(n))
+        return n.value
+
+    def congruence(self):
+        """-> (tolerance in force, number of congruence classes)"""
+        t, n = c_dbl(), c_i64()
+        call("pyn_mesh_get_congruence", self._h, ctypes.byref(t), ctypes.byref(n))
+        return t.value, n.value
+
     def set_dof_class(self, cls):
         cls = np.ascontiguousarray(cls, dtype=np.uint8).ravel()
         if cls.size != self.nnodes * self.dim:

@@ -230,6 +230,11 @@ class Domain:
                 cls = cls[ldofs]
             else:
                 self._dmesh = DeviceMesh(m.dim, m.ngl, m.corner_xyz, m.elem_nodes, m.nnodes)
+            from ..petsc import Options
+            tol = Options().getReal("pynama_congruence_tol", None)
+            if tol is not None:
+                # -pynama_congruence_tol 0: evaluate every cell on its own (domain.py:262-276)
+                self._dmesh.set_congruence(tol)
             self._dmesh.set_dof_class(cls)
         return self._dmesh
 

@@ -100,3 +100,73 @@ def test_assembly_is_reproducible():
     a = dm.assemble_kle("FS")["K"].getValuesCSR()[2]
     b = dm.assemble_kle("FS")["K"].getValuesCSR()[2]
     assert np.array_equal(a, b)
+
+
+@pytest.mark.parametrize("nelem,ngl,upper", [([4, 3], 3, [1.0, 1.0]), ([3, 2, 4], 3, [3.0, 1.0, 1.0]),
+                                              ([2, 2, 2], 4, [1.0, 1.0, 1.0])])
+def test_congruence_classes_uniform_box(nelem, ngl, upper):
+    """a uniform box is ONE congruence class: element blocks are evaluated once and every
+    assembled matrix agrees with the element-by-element evaluation (and with the oracle, which
+    calls getElemKLEMatrices per cell as mat_fs.py:152-155 does) to 1e-12"""
+    mesh, dm, tab = _setup(nelem, ngl, 0.0, upper=upper)
+    tol, nclass = dm.congruence()
+    assert tol == 1e-13 and nclass == 1
+    cls = ns_classes(mesh, None)
+    dm.set_dof_class(cls)
+    merged = dm.assemble_kle("NS")
+    ops_m = dm.assemble_ops(compact=True)
+    assert dm.set_congruence(0.0) == mesh.nel
+    single = dm.assemble_kle("NS")
+    ops_s = dm.assemble_ops(compact=True)
+    want = assembly.assemble_kle(tab, mesh.corner_xyz, mesh.elem_nodes, mesh.nnodes, cls, "NS")
+    for name in ("K", "Krhs", "Rw", "Rd", "Kfs", "Krhsfs", "Rwfs", "Rdfs"):
+        a, b = csr_of(merged[name]), csr_of(single[name])
+        assert np.array_equal(a.indptr, b.indptr) and np.array_equal(a.indices, b.indices)
+        scale = max(np.abs(b.data).max(), 1e-300) if b.nnz else 1.0
+        assert b.nnz == 0 or np.abs(a.data - b.data).max() <= 1e-12 * scale
+        assert_same_csr(a, want[name], name=name)
+    for a, b in zip(ops_m[:3], ops_s[:3]):
+        a, b = csr_of(a), csr_of(b)
+        assert np.array_equal(a.indices, b.indices)
+        assert np.abs(a.data - b.data).max() <= 1e-12 * np.abs(b.data).max()
+    assert np.abs(ops_m[3].getArray() - ops_s[3].getArray()).max() <= 1e-13 * ops_s[3].getArray().max()
+    assert dm.set_congruence(1e-13) == 1
+
+
+def test_congruence_classes_mixed_mesh():
+    """cells with a displaced corner are never merged (every cell of a 3x3x2 box touches an
+    interior corner); a box with two element sizes along x has two classes"""
+    mesh, dm, _ = _setup([3, 3, 2], 3, 0.15)
+    assert dm.congruence()[1] == mesh.nel
+    from pynama_b200.device_mesh import DeviceMesh
+    from pynama_b200.domain.box_mesh import BoxMesh
+    m2 = BoxMesh([4, 2], [0.0, 0.0], [1.0, 1.0], 3)
+    cx = m2.corner_xyz.copy().reshape(m2.nel, 4, 2)
+    # stretch the x >= 0.5 half by 2: two congruence classes, still a conforming mesh
+    cx[..., 0] = np.where(cx[..., 0] > 0.5, 0.5 + 2.0 * (cx[..., 0] - 0.5), cx[..., 0])
+    dm2 = DeviceMesh(2, 3, cx, m2.elem_nodes, m2.nnodes)
+    assert dm2.congruence()[1] == 2
+    tab = sem.SpectralTables(3, 2)
+    cls = np.zeros(m2.nnodes * 2, np.uint8)
+    cls[: 2 * 3] = 1
+    dm2.set_dof_class(cls)
+    got = dm2.assemble_kle("FS")
+    want = assembly.assemble_kle(tab, cx, m2.elem_nodes, m2.nnodes, cls, "FS")
+    for name in ("K", "Krhs", "Rw"):
+        assert_same_csr(csr_of(got[name]), want[name], name=name)
+
+
+@pytest.mark.parametrize("mode,nelem,ngl,perturb", [("FS", [3, 3, 2], 3, 0.15), ("NS", [4, 3], 4, 0.0),
+                                                     ("NS", [2, 2, 2], 3, 0.1)])
+def test_fused_kle_pass_equals_per_matrix_pass(mode, nelem, ngl, perturb, monkeypatch):
+    """K, Krhs, Rw, Rd from the single pass over the node graph are bit-identical to the
+    one-gather-per-matrix kernels (same blocks, same ascending-element summation order)"""
+    mesh, dm, _ = _setup(nelem, ngl, perturb)
+    dm.set_dof_class(ns_classes(mesh, None) if mode == "NS" else fs_classes(mesh))
+    fused = dm.assemble_kle(mode)
+    monkeypatch.setenv("PYN_ASSEMBLE_PER_MATRIX", "1")
+    per = dm.assemble_kle(mode)
+    for name in ("K", "Krhs", "Rw", "Rd"):
+        a, b = fused[name].getValuesCSR(), per[name].getValuesCSR()
+        for x, y in zip(a, b):
+            assert np.array_equal(x, y), name

@@ -1,4 +1,4 @@
-"""Assembly phase timings on one GPU (development aid): python tools/probe_asm.py [nel] [ngl] [reps]"""
+"""Assembly phase timings on one GPU (development aid): python tools/probe_asm.py [nel] [ngl] [reps] [perturb]"""
 import sys, os
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np
@@ -9,8 +9,9 @@ from pynama_b200.petsc import Context
 nel = int(sys.argv[1]) if len(sys.argv) > 1 else 16
 ngl = int(sys.argv[2]) if len(sys.argv) > 2 else 4
 reps = int(sys.argv[3]) if len(sys.argv) > 3 else 3
+perturb = float(sys.argv[4]) if len(sys.argv) > 4 else 0.15
 dim = 3
-mesh = BoxMesh([nel] * 3, [0] * 3, [1] * 3, ngl, perturb=0.15)
+mesh = BoxMesh([nel] * 3, [0] * 3, [1] * 3, ngl, perturb=perturb)
 ctx = Context.get()
 dm = DeviceMesh(dim, ngl, mesh.corner_xyz, mesh.elem_nodes, mesh.nnodes)
 cls = np.zeros(mesh.nnodes * dim, np.uint8)
@@ -18,7 +19,7 @@ b = mesh.getBordersNodes()
 for d in range(dim):
     cls[b * dim + d] = 1
 dm.set_dof_class(cls)
-print(f"{nel}^3 ngl={ngl}: symbolic {dm.phase_ms('symbolic'):.2f} ms", flush=True)
+print(f"{nel}^3 ngl={ngl} perturb={perturb}: {dm.congruence()[1]} congruence classes, symbolic {dm.phase_ms('symbolic'):.2f} ms", flush=True)
 for r in range(reps):
     ctx.prof_enable(True)
     mats = dm.assemble_kle("FS")
