@@ -163,6 +163,21 @@ class Domain:
     def getCellCentroid(self, cell):
         return self._mesh.corner_xyz[cell].mean(axis=0)
 
+    def getCellCentroids(self):
+        """every cell at once: [nel, dim]"""
+        return self._mesh.corner_xyz.mean(axis=1)
+
+    def getNodesCoordsFromEntities(self, entities):
+        """nodes of a set of cells (ascending ids) and their coordinates (domain.py:185-188)"""
+        ents = np.asarray(list(entities), dtype=np.int64)
+        nodes = np.unique(self._mesh.elem_nodes[ents].ravel()) if len(ents) else np.zeros(0, np.int64)
+        return nodes, self._mesh.coords[nodes]
+
+    def getNodeSeparationIBM(self):
+        """width of the first edge of the mesh over the number of GLL intervals (domain.py:212-217)"""
+        c = self._mesh.corner_xyz[0]
+        return float(np.linalg.norm(c[1] - c[0])) / (self._ngl - 1)
+
     def getBorderNodes(self, borderName):
         return list(self._mesh.getBorderNodes(borderName))
 

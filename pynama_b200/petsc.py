@@ -732,6 +732,11 @@ class Mat:
         call("pyn_mat_export_csr", self._h, ptr(rowptr), ptr(col), ptr(val))
         return rowptr, col, val
 
+    def getRow(self, row):
+        """(column indices, values) of one row of the reference pattern (host-side diagnostic)"""
+        ip, ix, v = self.getValuesCSR()
+        return ix[ip[row]:ip[row + 1]], v[ip[row]:ip[row + 1]]
+
     def getInfo(self):
         nnz, nb = self.nnz()
         stored, _ = self.bytes()

@@ -31,7 +31,12 @@ def timeSolving(config, FemProblem, **kwargs):
     if not fem.comm.rank:
         fem.logger.info("Solving problem...")
     fem.timer.tic()
-    fem.ts.solve(fem.vort)
+    if hasattr(fem, "startSolver"):
+        # immersed-boundary cases own their time loop (immersed_boundary.py:56-81, :303-331); the
+        # reference selects them at run_case.py:20-23
+        fem.startSolver()
+    else:
+        fem.ts.solve(fem.vort)
     if not fem.comm.rank:
         fem.logger.info(f"Solver Finished in {fem.timer.toc()} seconds")
         fem.logger.info(f"Total time: {fem.timerTotal.toc()} seconds")
@@ -55,6 +60,10 @@ def main(argv=None):
         return 2
     if runTests:
         from .cases.base_problem import BaseProblemTest as FemProblem
+    elif config.get("name") in ("ibm-static", "ibm-dynamic") or case in ("ibm-static", "ibm-dynamic"):
+        from .cases import immersed_boundary as ib
+        dynamic = "dynamic" in (case if case in ("ibm-static", "ibm-dynamic") else config.get("name"))
+        FemProblem = ib.ImmersedBoundaryDynamic if dynamic else ib.ImmersedBoundaryStatic
     else:
         from .cases.base_problem import BaseProblem as FemProblem
     if runTests == "kle":
