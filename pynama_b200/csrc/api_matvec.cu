@@ -109,7 +109,7 @@ int pyn_mat_shape(pyn_mat* m, int64_t* nrows, int64_t* ncols, int* br, int* bc) 
 
 int pyn_mat_nnz(pyn_mat* m, int64_t* nnz_ref, int64_t* nblocks) {
   PYN_REQUIRE(m, "null mat");
-  if (nblocks) *nblocks = m->nblocks;
+  if (nblocks) *nblocks = m->free_pattern ? m->nblocks : m->nblocks_real;   // without padding
   if (nnz_ref) {
     HostMat h;
     PYN_CHECK(fetch_host(m, &h, false));
@@ -190,8 +190,10 @@ int pyn_mat_bytes(pyn_mat* m, int64_t* stored_bytes, int64_t* spmv_bytes) {
   if (stored_bytes) *stored_bytes = m->nblocks * (8 * bb + 4 + 8) + (m->nbrows + 1) * 8;
   // compulsory SpMV traffic of the stored format: values + block
   // column ids + row pointers + y written + x read once
+  // (the padding blocks of the rows are stored and read but not credited)
+  const int64_t nreal = m->free_pattern ? m->nblocks : m->nblocks_real;
   if (spmv_bytes)
-    *spmv_bytes = m->nblocks * (8 * bb + 4) + m->nbrows * (8 * m->br + 8) + m->nbcols * 8 * m->bc;
+    *spmv_bytes = nreal * (8 * bb + 4) + m->nbrows * (8 * m->br + 8) + m->nbcols * 8 * m->bc;
   return PYN_OK;
 }
 

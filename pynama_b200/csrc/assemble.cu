@@ -15,6 +15,9 @@ struct DiagAdd {
   double v[4];
 };
 
+// rows hold a multiple of 4 blocks: padding blocks after the kept ones
+__host__ __device__ __forceinline__ int pad_blocks(int kept) { return (4 - (kept & 3)) & 3; }
+
 __device__ __forceinline__ bool block_kept(int br, int bc, int64_t r, int32_t c,
                                            const uint8_t* __restrict__ cls, bool use_rowcls,
                                            bool use_colcls, uint32_t pairmask, uint32_t diagmask) {
@@ -35,7 +38,8 @@ template <int PASS>
 __global__ void filter_kernel(int br, int bc, int64_t nrows, const int64_t* __restrict__ g_rowptr,
                               const int32_t* __restrict__ g_colidx, const uint8_t* __restrict__ cls,
                               bool use_rowcls, bool use_colcls, uint32_t pairmask, uint32_t diagmask,
-                              int32_t* __restrict__ rowlen, const int64_t* __restrict__ m_rowptr,
+                              int32_t* __restrict__ rowlen, unsigned long long* __restrict__ nreal,
+                              const int64_t* __restrict__ m_rowptr,
                               int32_t* __restrict__ m_colidx, int64_t* __restrict__ m_base) {
   const int lane = threadIdx.x & 31;
   const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -44,6 +48,7 @@ __global__ void filter_kernel(int br, int bc, int64_t nrows, const int64_t* __re
     const int64_t p0 = g_rowptr[r], len = g_rowptr[r + 1] - p0;
     int64_t out = PASS ? m_rowptr[r] : 0;
     int total = 0;
+    int32_t lastc = 0;
     for (int64_t u0 = 0; u0 < len; u0 += 32) {
       const int64_t u = u0 + lane;
       bool keep = false;
@@ -58,10 +63,19 @@ __global__ void filter_kernel(int br, int bc, int64_t nrows, const int64_t* __re
         m_colidx[pos] = c;
         m_base[pos] = p0 + u;
       }
+      if (bal) lastc = __shfl_sync(0xffffffffu, c, 31 - __clz(bal));
       out += __popc(bal);
       total += __popc(bal);
     }
-    if (!PASS && lane == 0) rowlen[r] = total;
+    const int npad = pad_blocks(total);
+    if (PASS && lane < npad) {                       // zero blocks repeating the last column
+      m_colidx[out + lane] = lastc;
+      m_base[out + lane] = -1;
+    }
+    if (!PASS && lane == 0) {
+      rowlen[r] = total + npad;
+      if (total) atomicAdd(nreal, (unsigned long long)total);
+    }
   }
 }
 
@@ -72,6 +86,7 @@ struct FilterTarget {
   int use_colcls;
   uint32_t pairmask, diagmask;
   int32_t* rowlen;           // pass 0
+  unsigned long long* nreal; // pass 0: kept blocks of the whole matrix
   const int64_t* rowptr;     // pass 1
   int32_t* colidx;
   int64_t* base;
@@ -113,6 +128,7 @@ __global__ void filter4_kernel(int64_t nrows, const int64_t* __restrict__ g_rowp
 #pragma unroll
     for (int k = 0; k < 4; ++k) out[k] = PASS ? T.t[k].rowptr[r] : 0;
     int total[4] = {0, 0, 0, 0};
+    int32_t lastc[4] = {0, 0, 0, 0};
     for (int u0 = 0; u0 < len; u0 += 32) {
       const int u = u0 + lane;
       int32_t c = 0;
@@ -133,13 +149,22 @@ __global__ void filter4_kernel(int64_t nrows, const int64_t* __restrict__ g_rowp
           T.t[k].colidx[pos] = c;
           T.t[k].base[pos] = p0 + u;
         }
+        if (bal) lastc[k] = __shfl_sync(0xffffffffu, c, 31 - __clz(bal));
         out[k] += __popc(bal);
         total[k] += __popc(bal);
       }
     }
-    if (!PASS && lane == 0) {
 #pragma unroll
-      for (int k = 0; k < 4; ++k) T.t[k].rowlen[r] = total[k];
+    for (int k = 0; k < 4; ++k) {
+      const int npad = pad_blocks(total[k]);
+      if (PASS && lane < npad) {                     // zero blocks repeating the last column
+        T.t[k].colidx[out[k] + lane] = lastc[k];
+        T.t[k].base[out[k] + lane] = -1;
+      }
+      if (!PASS && lane == 0) {
+        T.t[k].rowlen[r] = total[k] + npad;
+        if (total[k]) atomicAdd(T.t[k].nreal, (unsigned long long)total[k]);
+      }
     }
   }
 }
@@ -170,6 +195,11 @@ numeric_kernel(int64_t nrows, const int64_t* __restrict__ m_rowptr,
     for (int64_t u = lane; u < nb; u += G) {
       const int64_t s = m_base[p0 + u];
       const int32_t c = m_colidx[p0 + u];
+      if (s < 0) {                                   // padding block
+#pragma unroll
+        for (int q = 0; q < BB; ++q) val[p0 * BB + (int64_t)q * nb + u] = 0.0;
+        continue;
+      }
       double acc[BB];
 #pragma unroll
       for (int q = 0; q < BB; ++q) acc[q] = 0.0;
@@ -249,20 +279,28 @@ int make_pattern(pyn_mesh* mesh, const NodeGraph* graph, int br, int bc, bool us
   if (use_rowcls || use_colcls)
     PYN_REQUIRE(mesh->has_cls, "dof classes not set (pyn_mesh_set_dof_class)");
   DevBuf<int32_t> rowlen;
+  DevBuf<unsigned long long> nreal;
   PYN_CHECK(rowlen.alloc(ctx, graph->nrows));
+  PYN_CHECK(nreal.alloc(ctx, 1));
+  PYN_CHECK(nreal.zero());
   PYN_CHECK(m->rowptr.alloc(ctx, graph->nrows + 1));
   const int grid = grid_for(ctx, graph->nrows * 32, 256);
   filter_kernel<0><<<grid, 256, 0, ctx->stream>>>(br, bc, graph->nrows, graph->rowptr.p,
                                                   graph->colidx.p, mesh->dofcls.p, use_rowcls,
-                                                  use_colcls, pairmask, diagmask, rowlen.p, nullptr,
-                                                  nullptr, nullptr);
+                                                  use_colcls, pairmask, diagmask, rowlen.p, nreal.p,
+                                                  nullptr, nullptr, nullptr);
   PYN_LAUNCHED(ctx);
+  {
+    unsigned long long h = 0;
+    PYN_CHECK(nreal.download(&h, 1));
+    m->nblocks_real = (int64_t)h;
+  }
   PYN_CHECK(exclusive_scan_i32_to_i64(ctx, rowlen.p, m->rowptr.p, graph->nrows, &m->nblocks));
   PYN_CHECK(m->colidx.alloc(ctx, m->nblocks));
   PYN_CHECK(m->base_slot.alloc(ctx, m->nblocks));
   filter_kernel<1><<<grid, 256, 0, ctx->stream>>>(br, bc, graph->nrows, graph->rowptr.p,
                                                   graph->colidx.p, mesh->dofcls.p, use_rowcls,
-                                                  use_colcls, pairmask, diagmask, nullptr,
+                                                  use_colcls, pairmask, diagmask, nullptr, nullptr,
                                                   m->rowptr.p, m->colidx.p, m->base_slot.p);
   PYN_LAUNCHED(ctx);
   PYN_CHECK(m->val.alloc(ctx, m->nblocks * br * bc));
@@ -302,6 +340,9 @@ static int make_patterns4(pyn_mesh* mesh, const MatSpec* sp, pyn_mat** m) {
   const NodeGraph* graph = sp[0].graph;
   PYN_REQUIRE(mesh->has_cls, "dof classes not set (pyn_mesh_set_dof_class)");
   DevBuf<int32_t> rowlen[4];
+  DevBuf<unsigned long long> nreal;
+  PYN_CHECK(nreal.alloc(ctx, 4));
+  PYN_CHECK(nreal.zero());
   FilterTargets T;
   for (int k = 0; k < 4; ++k) {
     pyn_mat* a = m[k];
@@ -323,6 +364,7 @@ static int make_patterns4(pyn_mesh* mesh, const MatSpec* sp, pyn_mat** m) {
     T.t[k].pairmask = sp[k].pairmask;
     T.t[k].diagmask = sp[k].diagmask;
     T.t[k].rowlen = rowlen[k].p;
+    T.t[k].nreal = nreal.p + k;
     T.t[k].rowptr = nullptr;
     T.t[k].colidx = nullptr;
     T.t[k].base = nullptr;
@@ -335,8 +377,11 @@ static int make_patterns4(pyn_mesh* mesh, const MatSpec* sp, pyn_mat** m) {
     filter4_kernel<0, 3><<<grid, 256, 0, ctx->stream>>>(graph->nrows, graph->rowptr.p, graph->colidx.p,
                                                         mesh->nodecls.p, T);
   PYN_LAUNCHED(ctx);
+  unsigned long long real_h[4] = {0, 0, 0, 0};
+  PYN_CHECK(nreal.download(real_h, 4));
   for (int k = 0; k < 4; ++k) {
     pyn_mat* a = m[k];
+    a->nblocks_real = (int64_t)real_h[k];
     PYN_CHECK(exclusive_scan_i32_to_i64(ctx, rowlen[k].p, a->rowptr.p, graph->nrows, &a->nblocks));
     PYN_CHECK(a->colidx.alloc(ctx, a->nblocks));
     PYN_CHECK(a->base_slot.alloc(ctx, a->nblocks));
@@ -448,6 +493,15 @@ __device__ __forceinline__ void kle_emit(const KleTarget& t, bool valid, bool di
       }
   }
   out += __popc(bal);
+}
+
+template <int BB>
+__device__ __forceinline__ void kle_zero_pad(const KleTarget& t, int64_t p0, int nb, int out, int lane) {
+  if (out + lane < nb) {
+    double* dst = t.val + p0 * BB + (out + lane);
+#pragma unroll
+    for (int q = 0; q < BB; ++q, dst += nb) __stcs(dst, 0.0);
+  }
 }
 
 // 32 bytes of a record, one sector, through the non-coherent path
@@ -587,6 +641,11 @@ numeric_kle_kernel(int64_t nrows, const int64_t* __restrict__ g_rowptr,
       cur = nxt;
       a2 = a3;
     }
+    // padding blocks of the row (rows hold a multiple of 4 blocks)
+    kle_zero_pad<D * D>(T.K, pK, nK, oK, lane);
+    kle_zero_pad<D * D>(T.Krhs, pKr, nKr, oKr, lane);
+    kle_zero_pad<D * DW>(T.Rw, pW, nW, oW, lane);
+    kle_zero_pad<D>(T.Rd, pD, nD, oD, lane);
   }
 }
 
@@ -625,12 +684,10 @@ int assemble_kle_fused(pyn_mesh* mesh, const MatSpec* sp, pyn_mat** out) {
   const int64_t npairs = (int64_t)mesh->nn * mesh->nn;
   const int2* src = nullptr;
   PYN_CHECK(class_sources(mesh, &g, &src));
-  // resident CTAs per SM the kernel is compiled for: 2 (128 registers, no spills) measured
-  // fastest on B200; PYN_NKLE_MINB=3|4 for comparison
-  const char* mb = getenv("PYN_NKLE_MINB");
-  int minb = mb ? atoi(mb) : 2;
-  if (minb < 2 || minb > 4) minb = 2;
-  const int grid = grid_for(ctx, g.nrows * 32, 256, minb);   // one resident wave
+  // compiled for 2 resident CTAs per SM (128 registers, no spills): measured fastest on B200
+  // (3 CTAs at 80 registers spill the pipeline state: 0.93 against 0.78 ms at 16^3, ngl = 4;
+  // two half passes K|Krhs and Rw|Rd: 0.82 ms)
+  const int grid = grid_for(ctx, g.nrows * 32, 256, 2);   // one resident wave
   // 32-bit contribution / record indices when they fit
   const bool idx32 = g.ncontrib < (int64_t)0x7fffffff &&
                      mesh->nclass * npairs * kle_record_stride(d) < (int64_t)0x7fffffff;
@@ -644,8 +701,6 @@ int assemble_kle_fused(pyn_mesh* mesh, const MatSpec* sp, pyn_mat** out) {
   } while (0)
   prof_begin(ctx, PROF_NUMERIC);
   if (d == 2) NKLE_CALL(2, 1, 2);
-  else if (minb == 3) NKLE_CALL(3, 3, 3);
-  else if (minb == 4) NKLE_CALL(3, 3, 4);
   else NKLE_CALL(3, 3, 2);
 #undef NKLE_CALL
 #undef NKLE_ARGS

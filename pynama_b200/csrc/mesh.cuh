@@ -65,13 +65,18 @@ struct pyn_mesh {
 
 // Node-block sparse matrix, "row-plane" BSR: the blocks of block-row r are
 // stored as br*bc planes of nb_r doubles each (plane q = i*bc+j), so that a
-// warp walking the blocks of a row reads every plane coalesced.
+// warp walking the blocks of a row reads every plane coalesced.  Rows assembled
+// from a node graph are padded to a multiple of 4 blocks (zero blocks repeating
+// the row's last column, base_slot -1), so every plane starts on a 32-byte sector:
+// unaligned 256-byte runs cost B200 about half of its write bandwidth and 6 % extra
+// read sectors (profiles/README.md).
 struct pyn_mat {
   pyn_ctx* ctx = nullptr;
   pyn_mesh* mesh = nullptr;        // for the reference (dense) graph + dof classes
   int br = 0, bc = 0;
   int64_t nbrows = 0, nbcols = 0;  // nodes
-  int64_t nblocks = 0;
+  int64_t nblocks = 0;             // stored blocks, padding included
+  int64_t nblocks_real = 0;        // without the padding blocks
   pyn::DevBuf<int64_t> rowptr;     // [nbrows+1] block offsets
   pyn::DevBuf<int32_t> colidx;     // [nblocks]
   pyn::DevBuf<double> val;         // [nblocks*br*bc] row-plane layout

@@ -216,6 +216,7 @@ __global__ void diag_blocks_kernel(int64_t nbrows, const int64_t* __restrict__ r
       if (c == r) { pos = mid; break; }
       if (c < r) lo = mid + 1; else hi = mid - 1;
     }
+    while (pos > 0 && colidx[p0 + pos - 1] == (int32_t)r) --pos;   // not a padding repeat of the column
     for (int q = 0; q < B * B; ++q)
       dblk[r * B * B + q] = pos >= 0 ? val[p0 * B * B + (int64_t)q * nb + pos] : 0.0;
   }
@@ -267,7 +268,7 @@ int scale_rows(pyn_mat* m, const double* l) {
 __global__ void mark_slots_kernel(const int64_t* __restrict__ base, int64_t n, int64_t* __restrict__ pos) {
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
        i += (int64_t)gridDim.x * blockDim.x)
-    pos[base[i]] = i;
+    if (base[i] >= 0) pos[base[i]] = i;            // padding blocks have no slot
 }
 
 // one warp per row of C: for every block find the source positions in A and B
@@ -286,7 +287,7 @@ __global__ void add_values_kernel(int bb, int64_t nbrows, const int64_t* __restr
     const int64_t bp0 = b_rowptr[r], bnb = b_rowptr[r + 1] - bp0;
     for (int64_t u = lane; u < nb; u += 32) {
       const int64_t s = c_base[p0 + u];
-      const int64_t pa = a_pos[s], pb = b_pos[s];
+      const int64_t pa = s >= 0 ? a_pos[s] : -1, pb = s >= 0 ? b_pos[s] : -1;
       for (int q = 0; q < bb; ++q) {
         double v = 0.0;
         if (pa >= 0) v += a_val[ap0 * bb + (int64_t)q * anb + (pa - ap0)];
