@@ -662,17 +662,29 @@ static KleTarget kle_target(const MatSpec& sp, const pyn_mat* m) {
 
 // specs / out in the order K, Krhs, Rw, Rd; all on the dense graph with row classes, K and
 // Krhs also with column classes (pyn_assemble_kle)
+static int assemble_kle_fused_impl(pyn_mesh* mesh, const MatSpec* sp, pyn_mat** out);
+
 int assemble_kle_fused(pyn_mesh* mesh, const MatSpec* sp, pyn_mat** out) {
+  for (int i = 0; i < 4; ++i) out[i] = nullptr;
+  const int rc = assemble_kle_fused_impl(mesh, sp, out);
+  if (rc != PYN_OK)
+    for (int i = 0; i < 4; ++i) {                  // nothing half-built leaves the library
+      delete out[i];
+      out[i] = nullptr;
+    }
+  return rc;
+}
+
+static int assemble_kle_fused_impl(pyn_mesh* mesh, const MatSpec* sp, pyn_mat** out) {
   pyn_ctx* ctx = mesh->ctx;
   const int d = mesh->dim;
-  for (int i = 0; i < 4; ++i) {
+  for (int i = 0; i < 4; ++i)
     PYN_REQUIRE(sp[i].graph == &mesh->dense && sp[i].use_rowcls && sp[i].ebs_ppa == 0 &&
                     !sp[i].pair_map && !sp[i].row_scale && sp[i].br == d &&
                     sp[i].use_colcls == (i < 2) && sp[i].ebs == sp[0].ebs &&
                     sp[i].ebs_stride == kle_record_stride(d),
                 "assemble_kle_fused: unexpected matrix spec");
-    out[i] = new pyn_mat();
-  }
+  for (int i = 0; i < 4; ++i) out[i] = new pyn_mat();
   PYN_CHECK(make_patterns4(mesh, sp, out));
   KleTargets T;
   T.K = kle_target(sp[0], out[0]);
