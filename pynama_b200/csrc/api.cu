@@ -1,5 +1,6 @@
 // api.cu -- extern "C" entry points: context, mesh, element export, assembly.
 #include "elem.cuh"
+#include "classes.cuh"
 #include "spmv.cuh"
 #include "vec.cuh"
 
@@ -215,57 +216,17 @@ int pyn_mem_used(pyn_ctx* ctx, int64_t* bytes) {
 }
 
 // ---- mesh ------------------------------------------------------------------------
-// Congruence classes of element shapes.  Two elements are congruent when the offsets of
-// their corners from corner 0, rounded to multiples of tol * (largest offset in the mesh),
-// are equal; the class representative is its lowest element.  tol <= 0: no merging.
+// Congruence classes of element shapes (classes.cuh) -> elem_class / class_rep on the device.
 static int compute_classes(pyn_mesh* m, const double* corners, double tol) {
-  const int64_t nel = m->nel;
-  const int nv = (1 << m->dim) * m->dim;
   m->congruence_tol = tol;
   m->class_version++;
   m->elem_class.release();
   m->class_rep.release();
-  m->nclass = nel;
-  if (!(tol > 0.0) || nel < 2) return PYN_OK;
-  double scale = 0.0;
-  for (int64_t e = 0; e < nel; ++e) {
-    const double* X = corners + e * nv;
-    for (int k = m->dim; k < nv; ++k) scale = std::max(scale, std::fabs(X[k] - X[k % m->dim]));
-  }
-  if (!(scale > 0.0) || !std::isfinite(scale)) return PYN_OK;
-  const double inv_q = 1.0 / (tol * scale);
-  std::vector<int64_t> keys;                       // [nclass][nv] quantised offsets of the representatives
-  std::vector<int32_t> cls((size_t)nel), rep;
-  std::unordered_multimap<uint64_t, int32_t> table;
-  table.reserve(1024);
-  std::vector<int64_t> key((size_t)nv);
-  for (int64_t e = 0; e < nel; ++e) {
-    const double* X = corners + e * nv;
-    uint64_t h = 0x9E3779B97F4A7C15ull;
-    for (int k = 0; k < nv; ++k) {
-      key[k] = std::llround((X[k] - X[k % m->dim]) * inv_q);
-      h = (h ^ (uint64_t)key[k]) * 0xFF51AFD7ED558CCDull;
-      h ^= h >> 29;
-    }
-    int32_t found = -1;
-    auto range = table.equal_range(h);
-    for (auto it = range.first; it != range.second; ++it)
-      if (std::equal(key.begin(), key.end(), keys.begin() + (size_t)it->second * nv)) {
-        found = it->second;
-        break;
-      }
-    if (found < 0) {
-      found = (int32_t)rep.size();
-      rep.push_back((int32_t)e);
-      keys.insert(keys.end(), key.begin(), key.end());
-      table.emplace(h, found);
-    }
-    cls[(size_t)e] = found;
-  }
-  if ((int64_t)rep.size() == nel) return PYN_OK;   // nothing merged: identity, no tables
-  m->nclass = (int64_t)rep.size();
-  PYN_CHECK(m->elem_class.alloc(m->ctx, nel));
-  PYN_CHECK(m->elem_class.upload(cls.data(), nel));
+  std::vector<int32_t> cls, rep;
+  m->nclass = congruence_classes(m->dim, m->nel, corners, tol, &cls, &rep);
+  if (m->nclass == m->nel) return PYN_OK;          // nothing merged: identity, no tables
+  PYN_CHECK(m->elem_class.alloc(m->ctx, m->nel));
+  PYN_CHECK(m->elem_class.upload(cls.data(), m->nel));
   PYN_CHECK(m->class_rep.alloc(m->ctx, m->nclass));
   PYN_CHECK(m->class_rep.upload(rep.data(), m->nclass));
   return PYN_OK;

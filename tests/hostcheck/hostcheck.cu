@@ -4,6 +4,7 @@
 // golden vectors in the build container (no GPU there).  It is not part of
 // libpynama_b200.so and nothing in the product loads it.
 #include "../../pynama_b200/csrc/elem_math.cuh"
+#include "../../pynama_b200/csrc/classes.cuh"
 
 using namespace pyn;
 
@@ -69,6 +70,14 @@ static void ops_host(const ElemTables& t, const double* X, double* S, double* D,
 }
 
 extern "C" {
+// congruence classes of element shapes (classes.cuh): cls[nel], rep[>= nclass]; returns nclass
+long long hc_congruence_classes(int dim, long long nel, const double* corners, double tol, int* cls, int* rep) {
+  std::vector<int32_t> c, r;
+  const int64_t n = congruence_classes(dim, nel, corners, tol, &c, &r);
+  for (long long e = 0; e < nel; ++e) cls[e] = c[(size_t)e];
+  for (int64_t k = 0; k < n; ++k) rep[k] = r[(size_t)k];
+  return n;
+}
 int hc_kle(int dim, int ngl, const double* X, double* K, double* Rw, double* Rd) {
   ElemTables t;
   if (build_elem_tables(dim, ngl, &t) != 0) return -1;

@@ -85,3 +85,56 @@ def test_element_arithmetic_host_build_vs_reference(dim, ngl):
             ref = g[f"c{ci}_{name}"]
             err = np.abs(arr - ref).max() / np.abs(ref).max()
             assert err <= 1e-12, (name, ci, err)
+
+
+def _classes(mesh_corners, dim, tol):
+    hc = _hc()
+    hc.hc_congruence_classes.restype = ctypes.c_longlong
+    hc.hc_congruence_classes.argtypes = [ctypes.c_int, ctypes.c_longlong, ctypes.c_void_p, ctypes.c_double,
+                                         ctypes.c_void_p, ctypes.c_void_p]
+    cx = np.ascontiguousarray(mesh_corners, dtype=np.float64).reshape(-1, 2 ** dim, dim)
+    cls, rep = np.zeros(len(cx), np.int32), np.zeros(len(cx), np.int32)
+    n = hc.hc_congruence_classes(dim, len(cx), cx.ctypes.data, tol, cls.ctypes.data, rep.ctypes.data)
+    return n, cls, rep[:n]
+
+
+def test_congruence_classes_host():
+    """pynama_b200/csrc/classes.cuh (the host code behind pyn_mesh_set_congruence) on the box
+    generator's meshes: uniform = one class, stretched = one per element size, displaced corners
+    = never merged, tol <= 0 = off; representatives are the lowest elements of their classes"""
+    from pynama_b200.domain.box_mesh import BoxMesh
+    for nelem, lo, up in (([5, 4], [0, 0], [1, 1]), ([4, 3, 5], [0, 0, 0], [3, 1, 1]), ([16, 16, 16], [0] * 3, [1] * 3)):
+        m = BoxMesh(nelem, lo, up, 3)
+        n, cls, rep = _classes(m.corner_xyz, m.dim, 1e-13)
+        assert n == 1 and not cls.any() and rep.tolist() == [0]
+        n, cls, rep = _classes(m.corner_xyz, m.dim, 0.0)
+        assert n == m.nel and np.array_equal(cls, np.arange(m.nel)) and np.array_equal(rep, np.arange(m.nel))
+    # every cell of these boxes touches a displaced interior corner
+    m = BoxMesh([3, 3, 2], [0, 0, 0], [1, 1, 1], 3, perturb=0.15)
+    assert _classes(m.corner_xyz, 3, 1e-13)[0] == m.nel
+    # cells away from the displaced corners keep a common class: 6x6 with only the middle displaced
+    m = BoxMesh([6, 6], [0, 0], [1, 1], 2)
+    cx = m.corner_xyz.copy().reshape(m.nel, 4, 2)
+    hit = np.all(np.isclose(cx, [0.5, 0.5]), axis=2)
+    cx[hit] += [0.01, -0.02]
+    n, cls, rep = _classes(cx, 2, 1e-13)
+    assert n == 5 and (cls == 0).sum() == m.nel - 4
+    # two element sizes along x
+    m = BoxMesh([4, 2], [0.0, 0.0], [1.0, 1.0], 3)
+    cx = m.corner_xyz.copy().reshape(m.nel, 4, 2)
+    cx[..., 0] = np.where(cx[..., 0] > 0.5, 0.5 + 2.0 * (cx[..., 0] - 0.5), cx[..., 0])
+    n, cls, rep = _classes(cx, 2, 1e-13)
+    assert n == 2
+    for k in range(n):
+        assert rep[k] == np.nonzero(cls == k)[0].min()
+    # translation and tiny noise do not split a class, a visible change does
+    m = BoxMesh([3, 3], [10.0, -7.0], [11.0, -6.0], 2)
+    rng = np.random.default_rng(1)
+    noisy = m.corner_xyz + 1e-15 * rng.uniform(-1, 1, m.corner_xyz.shape)
+    assert _classes(noisy, 2, 1e-13)[0] == 1
+    assert _classes(m.corner_xyz + 1e-9 * rng.uniform(-1, 1, m.corner_xyz.shape), 2, 1e-13)[0] == m.nel
+    # degenerate input: no merging, no crash
+    assert _classes(np.zeros((4, 4, 2)), 2, 1e-13)[0] == 4
+    bad = m.corner_xyz.copy()
+    bad[0, 0, 0] = np.nan
+    assert _classes(bad, 2, 1e-13)[0] == m.nel
