@@ -211,3 +211,71 @@ def test_domain_node_separation_ibm():
     box = {"ngl": 3, "box-mesh": {"nelem": [5, 5], "lower": [-5, -5], "upper": [8, 8]}}
     dom = _dom(UNIFORM, box=box)                                 # test_domain.py:245-255
     assert dom.getNodeSeparationIBM() == pytest.approx((8 - -5) / 5 / 2, abs=1e-15)
+
+
+# ---- test_dmplex_wrapper.py on the box generator: sides on asymmetric meshes ---------------------
+def _box(nelem, upper, ngl):
+    from pynama_b200.domain.box_mesh import BoxMesh
+    return BoxMesh(nelem, [0.0] * len(nelem), upper, ngl)
+
+
+def test_box_2d_borders_and_corners():
+    m = _box([3, 4], [0.6, 0.8], 3)                               # test_dmplex_wrapper.py:10-59
+    assert m.nel == 12
+    assert np.allclose(m.getCellCornersCoords(0).ravel(), [0, 0, 0.2, 0, 0.2, 0.2, 0, 0.2], atol=1e-13)
+    assert len(set(np.asarray(m.getBordersNodes()).tolist())) == 28
+    for b in m.getBordersNames():
+        assert len(m.getBorderNodes(b)) == (7 if b in ("up", "down") else 9), b
+    # which side is which: 'down' is y = lower, 'left' is x = lower (boundary.py:151-162)
+    assert np.allclose(m.coords[m.getBorderNodes("down")][:, 1], 0.0)
+    assert np.allclose(m.coords[m.getBorderNodes("up")][:, 1], 0.8)
+    assert np.allclose(m.coords[m.getBorderNodes("left")][:, 0], 0.0)
+    assert np.allclose(m.coords[m.getBorderNodes("right")][:, 0], 0.6)
+
+
+@pytest.mark.parametrize("ngl", [2, 4, 6, 8])
+def test_box_2d_border_counts_per_ngl(ngl):
+    m = _box([2, 3], [0.6, 0.8], ngl)                             # :61-88
+    assert len(set(np.asarray(m.getBordersNodes()).tolist())) == 10 + 10 * (ngl - 2)
+    for b in m.getBordersNames():
+        want = 3 + 2 * (ngl - 2) if b in ("up", "down") else 4 + 3 * (ngl - 2)
+        assert len(m.getBorderNodes(b)) == want, b
+
+
+def test_box_3d_borders_and_corners():
+    m = _box([3, 4, 5], [0.6, 0.8, 1.0], 3)                       # :90-147
+    assert m.getDimension() == 3 and m.nel == 60
+    want = [0, 0, 0, 0, 0.2, 0, 0.2, 0.2, 0, 0.2, 0, 0, 0, 0, 0.2, 0.2, 0, 0.2, 0.2, 0.2, 0.2, 0, 0.2, 0.2]
+    assert np.allclose(m.getCellCornersCoords(0).ravel(), want, atol=1e-13)
+    names = m.getBordersNames()
+    assert len(names) == 6 and set(names) == {"up", "down", "left", "right", "front", "back"}
+    assert len(set(np.asarray(m.getBordersNodes()).tolist())) == 28 * 11 + 35 * 2
+    for b in names:
+        want = 7 * 11 if b in ("up", "down") else (9 * 11 if b in ("left", "right") else 7 * 9)
+        assert len(m.getBorderNodes(b)) == want, b
+    for b, axis, val in (("down", 1, 0.0), ("up", 1, 0.8), ("left", 0, 0.0), ("right", 0, 0.6)):
+        assert np.allclose(m.coords[m.getBorderNodes(b)][:, axis], val), b
+    z = {b: np.unique(np.round(m.coords[m.getBorderNodes(b)][:, 2], 12)) for b in ("front", "back")}
+    assert all(len(v) == 1 for v in z.values()) and {float(z["front"][0]), float(z["back"][0])} == {0.0, 1.0}
+
+
+@pytest.mark.parametrize("ngl", [2, 4, 6])
+def test_box_3d_border_counts_per_ngl(ngl):
+    m = _box([2, 3, 4], [0.6, 0.8, 1.0], ngl)                     # :161-195
+    q = ngl - 2
+    assert len(set(np.asarray(m.getBordersNodes()).tolist())) == 54 + (36 + 68) * q + 52 * q * q
+    for b in m.getBordersNames():
+        if b in ("up", "down"):
+            want = 15 + 22 * q + 8 * q * q
+        elif b in ("left", "right"):
+            want = 20 + 31 * q + 12 * q * q
+        else:
+            want = 12 + 17 * q + 6 * q * q
+        assert len(m.getBorderNodes(b)) == want, b
+
+
+def test_edge_width_is_the_node_separation_base():
+    for nelem, upper in (([4, 4], [0.6, 0.8]), ([4, 4, 4], [0.8, 0.8, 0.8])):    # :49-59, :149-159
+        box = {"ngl": 3, "box-mesh": {"nelem": nelem, "lower": [0] * len(nelem), "upper": upper}}
+        dom = _dom(box=box)
+        assert dom.getNodeSeparationIBM() * 2 == pytest.approx(upper[0] / nelem[0], abs=1e-16)
