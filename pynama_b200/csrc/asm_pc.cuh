@@ -1,0 +1,32 @@
+// asm_pc.cuh -- element-block additive Schwarz preconditioner for the KLE operator (-pc_type asm)
+#pragma once
+#include "mesh.cuh"
+
+namespace pyn {
+
+// z = sum_e R_e^T W_e inv(R_e K R_e^T) W_e R_e r, W = 1/sqrt(elements sharing the node).
+// Elements whose assembled blocks R_e K R_e^T are bitwise equal share one inverse (27 on a
+// uniform box with one boundary-condition kind per side).
+struct AsmPc {
+  pyn_mesh* mesh = nullptr;
+  int B = 0, ld = 0;               // dofs per node, dofs per element (nn * B)
+  int64_t nclass = 0, ntiles = 0;
+  DevBuf<double> inv;              // [nclass][ld][ld], symmetric
+  DevBuf<int32_t> tile_elems;      // [ntiles][kAsmTile] elements of one class, -1 padded
+  DevBuf<int32_t> tile_class;      // [ntiles]
+  DevBuf<double> wnode;            // [nnodes]
+  DevBuf<double> ybuf;             // [nel][ld] element-local results of the last apply
+  size_t smem = 0;
+};
+
+constexpr int kAsmTile = 16;       // elements per CTA tile of the dense product
+// more distinct element blocks than this (bytes of inverses) is refused: the apply would read
+// more than the SpMV it is meant to save
+constexpr int64_t kAsmMaxInverseBytes = (int64_t)1 << 30;
+
+int asm_setup(pyn_ctx* ctx, const pyn_mat* A, AsmPc** out);
+// z = M^-1 r.  dots != NULL: dots[0] = r.z, dots[1] = z.z (device).  done != NULL: a device flag;
+// when non-zero the apply is skipped (iterations launched after convergence).
+int asm_apply(pyn_ctx* ctx, AsmPc* pc, const double* r, double* z, double* dots, const double* done);
+
+}  // namespace pyn

@@ -15,6 +15,7 @@
 #include <stdlib.h>
 #include "vec.cuh"
 #include "comm.cuh"
+#include "asm_pc.cuh"
 #include <memory>
 #include <algorithm>
 
@@ -556,12 +557,21 @@ struct pyn_ksp {
   DevBuf<double> kv[4];
   std::vector<std::unique_ptr<DevBuf<double>>> gv;
   DevBuf<double> gcoef;
+  AsmPc* asmpc = nullptr;               // -pc_type asm (asm_pc.cuh)
+  ~pyn_ksp() { delete asmpc; }
 };
 
 template <int B>
 static int ksp_setup_pc(pyn_ksp* k) {
   pyn_ctx* ctx = k->ctx;
   if (k->pc == PYN_PC_NONE) {
+    k->pc_ready = true;
+    return PYN_OK;
+  }
+  if (k->pc == PYN_PC_ASM) {
+    delete k->asmpc;
+    k->asmpc = nullptr;
+    PYN_CHECK(asm_setup(ctx, k->A, &k->asmpc));
     k->pc_ready = true;
     return PYN_OK;
   }
@@ -573,6 +583,17 @@ static int ksp_setup_pc(pyn_ksp* k) {
   PYN_LAUNCHED(ctx);
   PYN_CUDA(cudaStreamSynchronize(ctx->stream));
   k->pc_ready = true;
+  return PYN_OK;
+}
+
+// z = M^-1 r ; out[0] = r.z ; out[1] = z.z
+template <int B>
+static int ksp_pc_dots(pyn_ksp* k, const double* r, double* z, int64_t nn, int gridn, double* out) {
+  pyn_ctx* ctx = k->ctx;
+  if (k->pc == PYN_PC_ASM) return asm_apply(ctx, k->asmpc, r, z, out, nullptr);
+  pc_apply_dots_kernel<B><<<gridn, 256, 0, ctx->stream>>>(k->pc, k->pcd.p, r, z, nn, ctx->red_partials,
+                                                          ctx->red_ticket, out);
+  PYN_LAUNCHED(ctx);
   return PYN_OK;
 }
 
@@ -590,7 +611,12 @@ static int ksp_solve_cg(pyn_ksp* k, const double* b, double* x, int* its, int* r
   double* S = k->S.p;
   const int gridn = grid_for(ctx, nn > 0 ? nn : 1, 256);
   if (!k->pc_ready) PYN_CHECK(ksp_setup_pc<B>(k));
-  if (k->single_reduction && k->sr_s.n < k->n) PYN_CHECK(k->sr_s.alloc(ctx, k->n));
+  // The Schwarz preconditioner is not node-local, so it cannot ride inside the vector kernel:
+  // the update runs unpreconditioned and leaves the bookkeeping to cg_scalars_kernel, exactly as
+  // on the row-partitioned path (there an allreduce, here the preconditioner sits in between).
+  const bool asmpc = k->pc == PYN_PC_ASM;
+  const bool single_reduction = k->single_reduction && !asmpc;
+  if (single_reduction && k->sr_s.n < k->n) PYN_CHECK(k->sr_s.alloc(ctx, k->n));
   const bool fischer = k->fischer_m > 0;
   const int gridv = grid_for(ctx, n > 0 ? n : 1, 256);
   if (fischer && k->fischer_n > 0) {        // x <- sum_i (x~_i . b) x~_i
@@ -611,25 +637,21 @@ static int ksp_solve_cg(pyn_ksp* k, const double* b, double* x, int* its, int* r
     PYN_CHECK(vec_set(ctx, x, n, 0.0));
   }
   // ||M^-1 b|| for the threshold (KSPConvergedDefault with the preconditioned norm)
-  pc_apply_dots_kernel<B><<<gridn, 256, 0, ctx->stream>>>(k->pc, k->pcd.p, b, k->z.p, nn, ctx->red_partials,
-                                                          ctx->red_ticket, k->tmp2.p + 2);
-  PYN_LAUNCHED(ctx);
+  PYN_CHECK(ksp_pc_dots<B>(k, b, k->z.p, nn, gridn, k->tmp2.p + 2));
   // r = b - A x ; z = M^-1 r ; p = z
   PYN_CHECK(spmv(k->A, -1.0, x, 1.0, b, k->r.p));
   if (fischer) {                            // keep the guess and its residual for the basis update
     PYN_CUDA(cudaMemcpyAsync(k->x0.p, x, sizeof(double) * n, cudaMemcpyDeviceToDevice, ctx->stream));
     PYN_CUDA(cudaMemcpyAsync(k->r0.p, k->r.p, sizeof(double) * n, cudaMemcpyDeviceToDevice, ctx->stream));
   }
-  pc_apply_dots_kernel<B><<<gridn, 256, 0, ctx->stream>>>(k->pc, k->pcd.p, k->r.p, k->z.p, nn,
-                                                          ctx->red_partials, ctx->red_ticket, k->tmp2.p);
-  PYN_LAUNCHED(ctx);
+  PYN_CHECK(ksp_pc_dots<B>(k, k->r.p, k->z.p, nn, gridn, k->tmp2.p));
   if (dist) PYN_CHECK(comm_allreduce_sum(ctx, k->tmp2.p, 4));
   cg_init_scalars_kernel<<<1, 1, 0, ctx->stream>>>(S, k->tmp2.p, k->tmp2.p + 2, k->rtol, k->atol, k->dtol, 0);
   PYN_LAUNCHED(ctx);
   PYN_CUDA(cudaMemcpyAsync(k->p.p, k->z.p, sizeof(double) * n, cudaMemcpyDeviceToDevice, ctx->stream));
 
   // single-reduction CG over peer memory: halo exchange fused into the two kernels of an iteration
-  const bool fuse_halo = k->single_reduction && p2p && k->A->halo->p2p && k->A->halo->nneigh > 0 &&
+  const bool fuse_halo = single_reduction && p2p && k->A->halo->p2p && k->A->halo->nneigh > 0 &&
                          getenv("PYN_FUSED_HALO_OFF") == nullptr;
   bool halo_ready = false;
   HaloWait hw;
@@ -642,7 +664,7 @@ static int ksp_solve_cg(pyn_ksp* k, const double* b, double* x, int* its, int* r
     for (int j = 0; j < todo; ++j, ++it) {
       const int parity = it & 1;
       P2PRed red = p2p ? p2p_next(ctx) : red_off;
-      if (k->single_reduction) {
+      if (single_reduction) {
         // w = A u with w.u fused; then the whole recurrence (and r.u, u.u of the next iterate)
         // in one vector kernel.  Over peer memory the halo exchange of u rides in the same two
         // kernels: pushed by the vector kernel, awaited by the next product.
@@ -666,11 +688,17 @@ static int ksp_solve_cg(pyn_ksp* k, const double* b, double* x, int* its, int* r
       PYN_CHECK(spmv_dot(k->A, k->p.p, k->w.p, S + S_PW, S + S_DONE, &red));
       if (dist && !p2p) PYN_CHECK(comm_allreduce_sum(ctx, S + S_PW, 1));
       prof_begin(ctx, PROF_CG_UPDATE);
-      cg_update_kernel<B><<<gridn, 256, 0, ctx->stream>>>(k->pc, k->pcd.p, k->p.p, k->w.p, x, k->r.p,
-                                                          k->z.p, nn, S, parity, k->maxit,
-                                                          ctx->red_partials, ctx->red_ticket, dist, red);
+      cg_update_kernel<B><<<gridn, 256, 0, ctx->stream>>>(asmpc ? PYN_PC_NONE : k->pc, k->pcd.p, k->p.p,
+                                                          k->w.p, x, k->r.p, k->z.p, nn, S, parity, k->maxit,
+                                                          ctx->red_partials, ctx->red_ticket,
+                                                          dist || asmpc ? 1 : 0, red);
       prof_end(ctx);
       PYN_LAUNCHED(ctx);
+      if (asmpc) {                    // z = M^-1 r, r.z and z.z into the partial slots, bookkeeping
+        PYN_CHECK(asm_apply(ctx, k->asmpc, k->r.p, k->z.p, S + S_LRZ, S + S_DONE));
+        cg_scalars_kernel<<<1, 1, 0, ctx->stream>>>(S, parity, k->maxit);
+        PYN_LAUNCHED(ctx);
+      }
       if (dist && !p2p) {
         PYN_CHECK(comm_allreduce_sum(ctx, S + S_LRZ, 2));
         cg_scalars_kernel<<<1, 1, 0, ctx->stream>>>(S, parity, k->maxit);
@@ -784,6 +812,7 @@ struct KrylovOps {
     return pc(k->w.p, z);
   }
   int pc(const double* r, double* z) {
+    if (k->pc == PYN_PC_ASM) return asm_apply(ctx, k->asmpc, r, z, nullptr, nullptr);
     pc_apply_kernel<B><<<gridn, 256, 0, ctx->stream>>>(k->pc, k->pcd.p, r, z, nn);
     PYN_LAUNCHED(ctx);
     return PYN_OK;
@@ -993,7 +1022,15 @@ extern "C" {
 int pyn_ksp_create(pyn_ctx* ctx, pyn_mat* a, int type, int pc, pyn_ksp** out) {
   PYN_REQUIRE(ctx && a && out, "pyn_ksp_create: null argument");
   PYN_REQUIRE(a->br == a->bc && a->nbrows == a->nbcols, "KSP operator must be square");
-  PYN_REQUIRE(pc >= PYN_PC_NONE && pc <= PYN_PC_BJACOBI, "unknown pc type %d", pc);
+  PYN_REQUIRE(pc >= PYN_PC_NONE && pc <= PYN_PC_ASM, "unknown pc type %d", pc);
+  if (pc == PYN_PC_ASM) {
+    PYN_REQUIRE(a->mesh && !a->free_pattern && (a->br == 2 || a->br == 3),
+                "pc asm needs a 2-D or 3-D operator assembled from a mesh");
+    if (a->halo && ctx->nranks > 1) {
+      set_error("pc asm is not available on row-partitioned operators yet (single GPU only); use bjacobi");
+      return PYN_E_UNSUPPORTED;
+    }
+  }
   if (type != PYN_KSP_CG && type != PYN_KSP_GMRES && type != PYN_KSP_BCGS) {
     set_error("KSP type %d is not available (cg, gmres, bcgs)", type);
     return PYN_E_UNSUPPORTED;

@@ -788,12 +788,13 @@ class KSP:
 
     Types: cg (production path: the KLE operator is SPD), gmres (restart
     ``-ksp_gmres_restart``, default 30) and bcgs, all left-preconditioned with
-    none / jacobi / bjacobi.  ``-pc_type lu`` -- the reference default, a direct
+    none / jacobi / bjacobi / asm (additive Schwarz over the spectral elements, one
+    GPU).  ``-pc_type lu`` -- the reference default, a direct
     solve -- is mapped to CG + node-block Jacobi at rtol 1e-12 and logged, because
     a sparse direct factorisation is not part of the B200 path.
     """
     _TYPES = {"cg": 0, "gmres": 1, "bcgs": 2, "preonly": 3}
-    _PCS = {"none": 0, "jacobi": 1, "bjacobi": 2, "pbjacobi": 2}
+    _PCS = {"none": 0, "jacobi": 1, "bjacobi": 2, "pbjacobi": 2, "asm": 3}
 
     def __init__(self):
         self._h = None
@@ -896,7 +897,7 @@ class KSP:
         if ktype not in self._TYPES:
             raise PynamaError(f"unknown KSP type '{ktype}'")
         if pctype not in self._PCS:
-            raise PynamaError(f"unsupported PC type '{pctype}' (none, jacobi, bjacobi/pbjacobi)")
+            raise PynamaError(f"unsupported PC type '{pctype}' (none, jacobi, bjacobi/pbjacobi, asm)")
         h = vp()
         call("pyn_ksp_create", Context.get().handle, self._mat._h, self._TYPES[ktype], self._PCS[pctype],
              ctypes.byref(h))

@@ -5,6 +5,9 @@
 // libpynama_b200.so and nothing in the product loads it.
 #include "../../pynama_b200/csrc/elem_math.cuh"
 #include "../../pynama_b200/csrc/classes.cuh"
+#include "../../pynama_b200/csrc/asm_host.cuh"
+
+#include <string.h>
 
 using namespace pyn;
 
@@ -77,6 +80,43 @@ long long hc_congruence_classes(int dim, long long nel, const double* corners, d
   for (long long e = 0; e < nel; ++e) cls[e] = c[(size_t)e];
   for (int64_t k = 0; k < n; ++k) rep[k] = r[(size_t)k];
   return n;
+}
+// host arithmetic of the element-block Schwarz preconditioner (asm_host.cuh)
+int hc_asm_dense_inverse(int n, double* a, int symmetrise) {
+  const int rc = asm_dense_inverse(n, a);
+  if (rc == 0 && symmetrise) asm_symmetrise(n, a);
+  return rc;
+}
+// the two hashes of a dense ld x ld block, entries visited in the order perm[] (NULL: natural)
+void hc_asm_block_hash(int ld, const double* a, const long long* perm, unsigned long long* out) {
+  uint64_t h0 = 0, h1 = 0;
+  for (long long t = 0; t < (long long)ld * ld; ++t) {
+    const long long pos = perm ? perm[t] : t;
+    const double v = a[pos];
+    if (v == 0.0) continue;
+    uint64_t bits;
+    memcpy(&bits, &v, 8);
+    h0 += asm_hash_entry(bits, (uint64_t)pos, 0);
+    h1 += asm_hash_entry(bits, (uint64_t)pos, 1);
+  }
+  out[0] = h0;
+  out[1] = h1;
+}
+long long hc_asm_group_by_hash(long long nel, const unsigned long long* h, int* cls, int* rep) {
+  std::vector<int32_t> c, r;
+  const int64_t n = asm_group_by_hash(nel, reinterpret_cast<const uint64_t*>(h), &c, &r);
+  for (long long e = 0; e < nel; ++e) cls[e] = c[(size_t)e];
+  for (int64_t k = 0; k < n; ++k) rep[k] = r[(size_t)k];
+  return n;
+}
+// tile_elems[>= (nel + nclass*te)], tile_class[>= nel + nclass]; returns the number of tiles
+long long hc_asm_make_tiles(long long nel, const int* cls, long long nclass, int te, int* tile_elems,
+                            int* tile_class) {
+  std::vector<int32_t> tev, tcv;
+  const int64_t nt = asm_make_tiles(nel, cls, nclass, te, &tev, &tcv);
+  for (size_t i = 0; i < tev.size(); ++i) tile_elems[i] = tev[i];
+  for (size_t i = 0; i < tcv.size(); ++i) tile_class[i] = tcv[i];
+  return nt;
 }
 int hc_kle(int dim, int ngl, const double* X, double* K, double* Rw, double* Rd) {
   ElemTables t;

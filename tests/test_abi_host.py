@@ -138,3 +138,106 @@ def test_congruence_classes_host():
     bad = m.corner_xyz.copy()
     bad[0, 0, 0] = np.nan
     assert _classes(bad, 2, 1e-13)[0] == m.nel
+
+
+# ---- host arithmetic of the element-block Schwarz preconditioner (pynama_b200/csrc/asm_host.cuh) ----
+def test_asm_dense_inverse_host():
+    hc = _hc()
+    hc.hc_asm_dense_inverse.restype = ctypes.c_int
+    rng = np.random.default_rng(3)
+    for n in (1, 2, 7, 48, 192):
+        q = rng.standard_normal((n, n))
+        spd = q @ q.T + n * np.eye(n)
+        # a matrix that needs row exchanges: zero leading entry
+        gen = rng.standard_normal((n, n)) + 0.1 * np.eye(n)
+        gen[0, 0] = 0.0 if n > 1 else 2.0
+        for a, sym in ((spd, 1), (gen, 0)):
+            inv = np.ascontiguousarray(a.copy())
+            assert hc.hc_asm_dense_inverse(n, inv.ctypes.data_as(ctypes.c_void_p), sym) == 0
+            assert np.abs(inv @ a - np.eye(n)).max() < 1e-9 * np.linalg.cond(a)
+            np.testing.assert_allclose(inv, np.linalg.inv(a), rtol=0, atol=1e-10 * np.abs(np.linalg.inv(a)).max()
+                                       * np.linalg.cond(a))
+            if sym:
+                assert np.array_equal(inv, inv.T)          # exactly symmetric: CG needs it
+    # K rows of constrained dofs are identity rows: the inverse keeps them
+    a = np.eye(5)
+    a[1:4, 1:4] = [[4, 1, 0], [1, 3, 1], [0, 1, 2]]
+    inv = a.copy()
+    assert hc.hc_asm_dense_inverse(5, inv.ctypes.data_as(ctypes.c_void_p), 1) == 0
+    assert inv[0, 0] == 1.0 and inv[4, 4] == 1.0 and not inv[0, 1:].any() and not inv[4, :4].any()
+    # singular, zero, non-finite: refused
+    for bad in (np.zeros((3, 3)), np.ones((3, 3)) * np.nan, np.array([[1.0, 2.0], [2.0, 4.0]]) * 0 + [[0, 0], [0, 1]]):
+        b = np.ascontiguousarray(bad, dtype=np.float64)
+        assert hc.hc_asm_dense_inverse(b.shape[0], b.ctypes.data_as(ctypes.c_void_p), 0) == -1
+
+
+def _block_hash(hc, a, perm=None):
+    a = np.ascontiguousarray(a, dtype=np.float64)
+    out = (ctypes.c_ulonglong * 2)()
+    p = None
+    if perm is not None:
+        perm = np.ascontiguousarray(perm, dtype=np.int64)
+        p = perm.ctypes.data_as(ctypes.c_void_p)
+    hc.hc_asm_block_hash(a.shape[0], a.ctypes.data_as(ctypes.c_void_p), p, out)
+    return out[0], out[1]
+
+
+def test_asm_block_hash_and_grouping_host():
+    """the device hashes an element block with one warp per row node and atomic integer adds, so the
+    hash must not depend on the visiting order, must see the position of an entry and its last bit"""
+    hc = _hc()
+    hc.hc_asm_group_by_hash.restype = ctypes.c_longlong
+    rng = np.random.default_rng(5)
+    ld = 24
+    a = rng.standard_normal((ld, ld))
+    a[rng.uniform(size=a.shape) < 0.3] = 0.0
+    h = _block_hash(hc, a)
+    assert h == _block_hash(hc, a, rng.permutation(ld * ld))
+    b = a.copy()
+    i, j = np.argwhere(a != 0)[5]
+    b[i, j] = np.nextafter(b[i, j], np.inf)
+    assert _block_hash(hc, b) != h                                  # one ulp
+    assert _block_hash(hc, a.T.copy()) != h                         # same values elsewhere
+    z = a.copy()
+    z[a == 0] = -0.0
+    assert _block_hash(hc, z) == h                                  # signed zeros are structural zeros
+    h0, h1 = h
+    assert h0 != h1
+    # grouping: classes numbered by lowest member, representatives = lowest members
+    blocks = [a, b, a.T.copy(), a, b, a, np.zeros((ld, ld))]
+    hh = np.array([_block_hash(hc, x) for x in blocks], dtype=np.uint64)
+    cls = np.zeros(len(blocks), np.int32)
+    rep = np.zeros(len(blocks), np.int32)
+    n = hc.hc_asm_group_by_hash(len(blocks), hh.ctypes.data_as(ctypes.c_void_p), cls.ctypes.data_as(ctypes.c_void_p),
+                                rep.ctypes.data_as(ctypes.c_void_p))
+    assert n == 4 and cls.tolist() == [0, 1, 2, 0, 1, 0, 3] and rep[:4].tolist() == [0, 1, 2, 6]
+    # agreeing in one of the two hashes is not enough
+    hh2 = np.array([[1, 2], [1, 3], [1, 2]], dtype=np.uint64)
+    n = hc.hc_asm_group_by_hash(3, hh2.ctypes.data_as(ctypes.c_void_p), cls.ctypes.data_as(ctypes.c_void_p),
+                                rep.ctypes.data_as(ctypes.c_void_p))
+    assert n == 2 and cls[:3].tolist() == [0, 1, 0]
+
+
+def test_asm_tiles_host():
+    hc = _hc()
+    hc.hc_asm_make_tiles.restype = ctypes.c_longlong
+    rng = np.random.default_rng(9)
+    for nel, nclass, te in ((1, 1, 16), (64, 27, 16), (4096, 27, 16), (37, 37, 16), (100, 3, 4)):
+        cls = rng.integers(0, nclass, nel).astype(np.int32)
+        cls[:min(nel, nclass)] = np.arange(min(nel, nclass))        # every class used
+        tile_elems = np.full((nel + nclass) * te, -7, np.int32)
+        tile_class = np.full(nel + nclass, -7, np.int32)
+        nt = hc.hc_asm_make_tiles(nel, cls.ctypes.data_as(ctypes.c_void_p), nclass, te,
+                                  tile_elems.ctypes.data_as(ctypes.c_void_p),
+                                  tile_class.ctypes.data_as(ctypes.c_void_p))
+        want = sum(-(-int((cls == c).sum()) // te) for c in range(nclass))
+        assert nt == want
+        te_ = tile_elems[:nt * te].reshape(nt, te)
+        real = te_[te_ >= 0]
+        assert np.array_equal(np.sort(real), np.arange(nel))        # every element exactly once
+        assert set(te_[te_ < 0].tolist()) <= {-1}
+        for t in range(nt):
+            m = te_[t][te_[t] >= 0]
+            assert len(m) > 0 and np.all(cls[m] == tile_class[t]) and np.all(np.diff(m) > 0)
+            assert np.all(te_[t][len(m):] == -1)                    # padding only at the end
+        assert np.all(np.diff(tile_class[:nt]) >= 0)
