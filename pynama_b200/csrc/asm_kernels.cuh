@@ -1,0 +1,212 @@
+// asm_kernels.cuh -- the kernels of the element-block Schwarz preconditioner (asm_pc.cu).  In a
+// header so that tests/hostcheck can run them on CPU threads through its CUDA emulation shim
+// (tests/hostcheck/cuda_emu.h) in the build container, where there is no GPU.
+#pragma once
+#include "asm_host.cuh"
+#include "vec.cuh"
+
+#ifdef PYN_CUDA_EMU
+#define PYN_DYN_SMEM(T, name) T* name = static_cast<T*>(cuda_emu::ts.dyn_smem)
+#else
+#define PYN_DYN_SMEM(T, name) extern __shared__ __align__(16) T name[]
+#endif
+
+namespace pyn {
+
+constexpr int kAsmTile = 16;       // elements per CTA tile of the dense product
+constexpr int kAsmKC = 16;         // k-chunk of the inverse staged in shared memory
+constexpr int kAsmRG = 64;         // row groups (threads along the rows of a panel)
+constexpr int kAsmRM = 3;          // rows per thread
+constexpr int kAsmRP = kAsmRG * kAsmRM;   // rows per panel
+constexpr int kAsmEM = 4;          // elements per thread (kAsmTile / 4 thread columns)
+static_assert(kAsmTile == 4 * kAsmEM, "thread layout: 4 element groups x 64 row groups");
+
+// MODE 0: hash the block of every element of the list into hash[e][2]
+// MODE 1: write the dense block of list element li to dense[li][ld][ld]
+// One warp per (list element, local row node).
+template <int B, int MODE>
+__global__ void __launch_bounds__(256)
+asm_blocks_kernel(int64_t nlist, const int32_t* __restrict__ list, const int32_t* __restrict__ elem_nodes,
+                  int nn, const int64_t* __restrict__ rowptr, const int32_t* __restrict__ colidx,
+                  const double* __restrict__ val, unsigned long long* __restrict__ hash,
+                  double* __restrict__ dense) {
+  constexpr int BB = B * B;
+  const int ld = nn * B;
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  for (int64_t w = warp; w < nlist * nn; w += nwarps) {
+    const int64_t li = w / nn;
+    const int a = (int)(w - li * nn);
+    const int64_t e = list ? (int64_t)list[li] : li;
+    const int32_t* en = elem_nodes + e * nn;
+    const int64_t r = en[a];
+    const int64_t p0 = rowptr[r];
+    const int nb = (int)(rowptr[r + 1] - p0);
+    unsigned long long h0 = 0ull, h1 = 0ull;
+    for (int b = lane; b < nn; b += 32) {
+      const int32_t c = en[b];
+      int lo = 0, hi = nb;                       // first block of the row with column >= c
+      while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (colidx[p0 + mid] < c) lo = mid + 1;
+        else hi = mid;
+      }
+      const bool found = lo < nb && colidx[p0 + lo] == c;
+#pragma unroll
+      for (int q = 0; q < BB; ++q) {
+        const double v = found ? val[p0 * BB + (int64_t)q * nb + lo] : 0.0;
+        const int i = q / B, j = q - i * B;
+        const int64_t pos = (int64_t)(a * B + i) * ld + (b * B + j);
+        if (MODE == 0) {
+          if (v != 0.0) {
+            const unsigned long long bits = (unsigned long long)__double_as_longlong(v);
+            h0 += asm_hash_entry(bits, (uint64_t)pos, 0);
+            h1 += asm_hash_entry(bits, (uint64_t)pos, 1);
+          }
+        } else {
+          dense[li * (int64_t)ld * ld + pos] = v;
+        }
+      }
+    }
+    if (MODE == 0) {
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        h0 += __shfl_xor_sync(0xffffffffu, h0, o);
+        h1 += __shfl_xor_sync(0xffffffffu, h1, o);
+      }
+      if (lane == 0) {                           // wrapping integer sums: order-independent
+        atomicAdd(hash + 2 * e, h0);
+        atomicAdd(hash + 2 * e + 1, h1);
+      }
+    }
+  }
+}
+
+__global__ void asm_weights_kernel(int64_t nnodes, const int64_t* __restrict__ n2e_ptr,
+                                   double* __restrict__ wnode) {
+  for (int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; n < nnodes;
+       n += (int64_t)gridDim.x * blockDim.x) {
+    const double m = (double)(n2e_ptr[n + 1] - n2e_ptr[n]);
+    wnode[n] = m > 0.0 ? 1.0 / sqrt(m) : 0.0;
+  }
+}
+
+// Y[:, el] = inv(K_c) (W r)[dofs of el] for the 16 elements of a tile; 256 threads = 4 element
+// groups (4 elements each) x 64 row groups (3 rows each, 64 apart) per panel of 192 rows.
+// Shared memory: Xs[ld][16] gathered right-hand sides, As[16][192] one k-chunk of the inverse
+// (symmetric: row k of the inverse is read for column k).
+template <int B>
+__global__ void __launch_bounds__(256)
+asm_mult_kernel(int64_t ntiles, const int32_t* __restrict__ tile_elems, const int32_t* __restrict__ tile_class,
+                const int32_t* __restrict__ elem_nodes, int nn, const double* __restrict__ inv,
+                const double* __restrict__ wnode, const double* __restrict__ r, double* __restrict__ ybuf,
+                const double* __restrict__ done) {
+  PYN_DYN_SMEM(double, asm_sm);
+  if (done && *done != 0.0) return;
+  const int ld = nn * B;
+  double* Xs = asm_sm;                              // [ld][kAsmTile]
+  double* As = asm_sm + (size_t)ld * kAsmTile;      // [kAsmKC][kAsmRP]
+  const int tid = threadIdx.x;
+  const int tx = tid & 3, ty = tid >> 2;
+  for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    const int32_t* te = tile_elems + tile * kAsmTile;
+    const double* A = inv + (int64_t)tile_class[tile] * ld * ld;
+    __syncthreads();                                // the previous tile is done with Xs
+    for (int idx = tid; idx < nn * kAsmTile; idx += 256) {
+      const int el = idx % kAsmTile, a = idx / kAsmTile;
+      const int e = te[el];
+      double x[B];
+#pragma unroll
+      for (int c = 0; c < B; ++c) x[c] = 0.0;
+      if (e >= 0) {
+        const int64_t node = elem_nodes[(int64_t)e * nn + a];
+        const double w = wnode[node];
+#pragma unroll
+        for (int c = 0; c < B; ++c) x[c] = w * r[node * B + c];
+      }
+#pragma unroll
+      for (int c = 0; c < B; ++c) Xs[(a * B + c) * kAsmTile + el] = x[c];
+    }
+    for (int row0 = 0; row0 < ld; row0 += kAsmRP) {
+      const int prows = ld - row0 < kAsmRP ? ld - row0 : kAsmRP;
+      double acc[kAsmRM][kAsmEM];
+#pragma unroll
+      for (int m = 0; m < kAsmRM; ++m)
+#pragma unroll
+        for (int j = 0; j < kAsmEM; ++j) acc[m][j] = 0.0;
+      for (int k0 = 0; k0 < ld; k0 += kAsmKC) {
+        __syncthreads();                            // As free again; Xs complete on the first pass
+        for (int idx = tid; idx < kAsmKC * kAsmRP; idx += 256) {
+          const int kk = idx / kAsmRP, i = idx - kk * kAsmRP;
+          As[idx] = (k0 + kk < ld && i < prows) ? A[(int64_t)(k0 + kk) * ld + row0 + i] : 0.0;
+        }
+        __syncthreads();
+        const int kmax = ld - k0 < kAsmKC ? ld - k0 : kAsmKC;
+        for (int kk = 0; kk < kmax; ++kk) {
+          const double2 xa = *reinterpret_cast<const double2*>(Xs + (k0 + kk) * kAsmTile + tx * kAsmEM);
+          const double2 xb = *reinterpret_cast<const double2*>(Xs + (k0 + kk) * kAsmTile + tx * kAsmEM + 2);
+#pragma unroll
+          for (int m = 0; m < kAsmRM; ++m) {
+            const double av = As[kk * kAsmRP + ty + kAsmRG * m];
+            acc[m][0] += av * xa.x;
+            acc[m][1] += av * xa.y;
+            acc[m][2] += av * xb.x;
+            acc[m][3] += av * xb.y;
+          }
+        }
+      }
+#pragma unroll
+      for (int m = 0; m < kAsmRM; ++m) {
+        const int i = ty + kAsmRG * m;
+        if (i < prows) {
+#pragma unroll
+          for (int j = 0; j < kAsmEM; ++j) {
+            const int e = te[tx * kAsmEM + j];
+            if (e >= 0) {
+              const int64_t node = elem_nodes[(int64_t)e * nn + (row0 + i) / B];
+              ybuf[(int64_t)e * ld + row0 + i] = acc[m][j] * wnode[node];
+            }
+          }
+        }
+      }
+    }
+  }
+}
+
+// z[node] = sum over the elements of the node, ascending, of their local results
+template <int B>
+__global__ void __launch_bounds__(256)
+asm_sum_kernel(int64_t nnodes, const int64_t* __restrict__ n2e_ptr, const int2* __restrict__ n2e,
+               const double* __restrict__ ybuf, int ld, const double* __restrict__ r, double* __restrict__ z,
+               double* partials, unsigned int* ticket, double* dots, const double* __restrict__ done) {
+  __shared__ double sm[64];
+  if (done && *done != 0.0) return;
+  double v[2] = {0.0, 0.0};
+  for (int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; n < nnodes;
+       n += (int64_t)gridDim.x * blockDim.x) {
+    double zz[B];
+#pragma unroll
+    for (int c = 0; c < B; ++c) zz[c] = 0.0;
+    for (int64_t k = n2e_ptr[n]; k < n2e_ptr[n + 1]; ++k) {
+      const int2 ea = n2e[k];
+      const double* y = ybuf + (int64_t)ea.x * ld + ea.y * B;
+#pragma unroll
+      for (int c = 0; c < B; ++c) zz[c] += y[c];
+    }
+#pragma unroll
+    for (int c = 0; c < B; ++c) {
+      z[n * B + c] = zz[c];
+      if (dots) {
+        v[0] += r[n * B + c] * zz[c];
+        v[1] += zz[c] * zz[c];
+      }
+    }
+  }
+  if (dots) {
+    block_reduce<2>(v, sm);
+    grid_reduce_finish<2>(v, partials, ticket, dots);
+  }
+}
+
+}  // namespace pyn

@@ -12,14 +12,13 @@ struct AsmPc {
   int B = 0, ld = 0;               // dofs per node, dofs per element (nn * B)
   int64_t nclass = 0, ntiles = 0;
   DevBuf<double> inv;              // [nclass][ld][ld], symmetric
-  DevBuf<int32_t> tile_elems;      // [ntiles][kAsmTile] elements of one class, -1 padded
+  DevBuf<int32_t> tile_elems;      // [ntiles][kAsmTile (asm_kernels.cuh)] elements of one class, -1 padded
   DevBuf<int32_t> tile_class;      // [ntiles]
   DevBuf<double> wnode;            // [nnodes]
   DevBuf<double> ybuf;             // [nel][ld] element-local results of the last apply
   size_t smem = 0;
 };
 
-constexpr int kAsmTile = 16;       // elements per CTA tile of the dense product
 // more distinct element blocks than this (bytes of inverses) is refused: the apply would read
 // more than the SpMV it is meant to save
 constexpr int64_t kAsmMaxInverseBytes = (int64_t)1 << 30;

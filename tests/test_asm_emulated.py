@@ -1,0 +1,186 @@
+"""The CUDA kernels of the element-block additive Schwarz preconditioner (-pc_type asm,
+pynama_b200/csrc/asm_kernels.cuh) run on CPU threads through tests/hostcheck/cuda_emu.h and
+compared with a numpy statement of the same preconditioner on the oracle's K.  There is no GPU in
+the build container: this is how the kernels' indexing, tiling, padding and reduction logic is
+checked before they reach one.  Operators: the oracle's free-slip KLE matrix,
+converted to the product's row-plane BSR layout (rows padded to a multiple of 4 blocks)."""
+import ctypes
+import os
+
+import numpy as np
+import pytest
+import scipy.sparse as sp
+
+from oracle import timestep
+from pynama_b200.domain.box_mesh import BoxMesh
+from tests.study_precond import element_schwarz
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+EMU = os.path.join(ROOT, "tests", "hostcheck", "libemu_asm.so")
+
+
+def _emu():
+    if not os.path.exists(EMU):
+        pytest.skip("tests/hostcheck/libemu_asm.so not built (run __graft_entry__.build())")
+    lib = ctypes.CDLL(EMU)
+    lib.emu_asm_apply.restype = ctypes.c_int
+    return lib
+
+
+def row_plane_bsr(K, B, pad=4, drop_zero_blocks=True):
+    """scipy matrix -> (rowptr, colidx, val) in the layout of pyn_mat (mesh.cuh): block columns
+    ascending, rows padded to a multiple of `pad` blocks by zero blocks repeating the last column,
+    val[p0*B*B + q*nb + u]"""
+    K = K.tocsr().copy()
+    if drop_zero_blocks:
+        K.eliminate_zeros()
+    M = sp.bsr_matrix(K, blocksize=(B, B))
+    M.sort_indices()
+    nrows = M.shape[0] // B
+    rowptr = np.zeros(nrows + 1, np.int64)
+    cols, vals = [], []
+    for r in range(nrows):
+        lo, hi = M.indptr[r], M.indptr[r + 1]
+        c = M.indices[lo:hi].astype(np.int32)
+        d = M.data[lo:hi]                              # [nb][B][B]
+        npad = (-len(c)) % pad if len(c) else 0
+        if npad:
+            c = np.concatenate([c, np.full(npad, c[-1], np.int32)])
+            d = np.concatenate([d, np.zeros((npad, B, B))])
+        nb = len(c)
+        rowptr[r + 1] = rowptr[r] + nb
+        cols.append(c)
+        vals.append(d.reshape(nb, B * B).T.ravel())    # plane q = i*B+j holds nb doubles
+    return rowptr, np.concatenate(cols), np.concatenate(vals)
+
+
+def node_to_elements(elem_nodes, nnodes):
+    nel, nn = elem_nodes.shape
+    pairs = [[] for _ in range(nnodes)]
+    for e in range(nel):
+        for a in range(nn):
+            pairs[elem_nodes[e, a]].append((e, a))
+    ptr = np.zeros(nnodes + 1, np.int64)
+    ptr[1:] = np.cumsum([len(p) for p in pairs])
+    flat = np.array([x for p in pairs for x in p], dtype=np.int32).reshape(-1, 2)
+    return ptr, flat
+
+
+def _vp(a):
+    return a.ctypes.data_as(ctypes.c_void_p)
+
+
+def run_emulated(mesh, K, B, r, grid=3, napply=1, want_inv=False, drop_zero_blocks=True):
+    lib = _emu()
+    nel, nn = mesh.elem_nodes.shape
+    nnodes = mesh.nnodes
+    en = np.ascontiguousarray(mesh.elem_nodes, dtype=np.int32)
+    rowptr, colidx, val = row_plane_bsr(K, B, drop_zero_blocks=drop_zero_blocks)
+    ptr, n2e = node_to_elements(en, nnodes)
+    z = np.full(nnodes * B, np.nan)
+    dots = np.zeros(2)
+    nclass = ctypes.c_longlong()
+    cls = np.zeros(nel, np.int32)
+    ld = nn * B
+    inv = np.zeros((nel, ld, ld)) if want_inv else None
+    r = np.ascontiguousarray(r, dtype=np.float64)
+    rc = lib.emu_asm_apply(B, nn, nel, nnodes, _vp(en), _vp(rowptr), _vp(colidx), _vp(val), _vp(ptr), _vp(n2e), _vp(r),
+                           grid, napply, _vp(z), _vp(dots), ctypes.byref(nclass), _vp(cls),
+                           _vp(inv) if want_inv else None)
+    assert rc == 0, f"emulated pipeline failed an internal check ({rc})"
+    return z, dots, nclass.value, cls, (inv[:nclass.value] if want_inv else None)
+
+
+def kle_operator(dim, nelem, ngl):
+    mesh = BoxMesh(nelem, [0.0] * dim, [1.0] * dim, ngl)
+    prob = timestep.OracleProblem(dim, ngl, mesh.corner_xyz, mesh.elem_nodes, mesh.coords, mesh.getBordersNodes(),
+                                  rho=0.5, mu=0.01, solver="direct")
+    return mesh, prob.K.tocsr()
+
+
+def element_blocks(K, elem_nodes, B):
+    nel, nn = elem_nodes.shape
+    dofs = (elem_nodes[:, :, None] * B + np.arange(B)[None, None, :]).reshape(nel, nn * B)
+    return np.stack([K[dofs[e]][:, dofs[e]].toarray() for e in range(nel)])
+
+
+CASES = [
+    # dim, elements, ngl          ld    what the shape exercises
+    (3, [3, 3, 2], 3),          # 81    partial panel, partial last k-chunk, 18 elements over several CTAs
+    (3, [2, 2, 2], 4),          # 192   exactly one full panel of 192 rows, 12 full k-chunks (the bench shape)
+    (3, [2, 1, 1], 5),          # 375   two panels (192 + 183), 24 k-chunks with a partial one
+    (2, [5, 4], 3),             # 18    2x2 blocks, rows far below one panel, 20 elements: tiles of several classes
+    (2, [3, 2], 4),             # 32
+]
+
+
+@pytest.mark.parametrize("dim,nelem,ngl", CASES)
+def test_emulated_kernels_match_numpy_schwarz(dim, nelem, ngl):
+    mesh, K = kle_operator(dim, nelem, ngl)
+    B = dim
+    nel = mesh.elem_nodes.shape[0]
+    rng = np.random.default_rng(11)
+    r = rng.standard_normal(K.shape[0])
+    z, dots, nclass, cls, inv = run_emulated(mesh, K, B, r, grid=3, want_inv=True)
+    ref_apply, _ = element_schwarz(K, mesh.elem_nodes, B, weighted=True)
+    zref = ref_apply(r)
+    scale = np.abs(zref).max()
+    assert np.abs(z - zref).max() < 1e-11 * scale
+    assert abs(dots[0] - r @ zref) < 1e-10 * abs(r @ zref)
+    assert abs(dots[1] - zref @ zref) < 1e-10 * (zref @ zref)
+    assert dots[0] > 0                                    # SPD
+    # classes: exactly the sets of bitwise equal element blocks, numbered by lowest member
+    blocks = element_blocks(K, mesh.elem_nodes, B)
+    assert 1 <= nclass <= nel
+    for e in range(nel):
+        for f in range(e):
+            assert (cls[e] == cls[f]) == np.array_equal(blocks[e], blocks[f])
+    first = [int(np.nonzero(cls == c)[0].min()) for c in range(nclass)]
+    assert first == sorted(first)
+    # the inverses the kernels were given
+    for c in range(nclass):
+        a = blocks[first[c]]
+        assert np.abs(inv[c] @ a - np.eye(a.shape[0])).max() < 1e-8
+        assert np.array_equal(inv[c], inv[c].T)
+
+
+def test_emulated_apply_is_symmetric_reproducible_and_grid_independent():
+    mesh, K = kle_operator(3, [3, 2, 2], 3)
+    rng = np.random.default_rng(2)
+    n = K.shape[0]
+    r1, r2 = rng.standard_normal(n), rng.standard_normal(n)
+    z1, d1, _, _, _ = run_emulated(mesh, K, 3, r1, grid=2)
+    z2, _, _, _, _ = run_emulated(mesh, K, 3, r2, grid=2)
+    assert abs(r2 @ z1 - r1 @ z2) < 1e-12 * abs(r2 @ z1)           # M^-1 symmetric: CG may use it
+    # bitwise the same for any grid size and on repeated applies (fixed summation orders)
+    for grid, napply in ((1, 1), (5, 2), (7, 1)):
+        z, d, _, _, _ = run_emulated(mesh, K, 3, r1, grid=grid, napply=napply)
+        assert np.array_equal(z, z1)
+        assert d[1] == pytest.approx(d1[1], rel=1e-14)              # the dots fold per-CTA partials
+    # explicit zero blocks stored in the matrix (nothing dropped) change nothing
+    z, _, _, _, _ = run_emulated(mesh, K, 3, r1, grid=2, drop_zero_blocks=False)
+    assert np.array_equal(z, z1)
+
+
+def test_emulated_preconditioner_cuts_cg_iterations():
+    """what the option is for: fewer CG iterations than node-block Jacobi on the bench operator's
+    small sibling (tests/study_precond.py has the table for 4^3 and 8^3 elements)"""
+    import scipy.sparse.linalg as spl
+    from tests.study_precond import node_block_jacobi
+    mesh, K = kle_operator(3, [3, 3, 3], 3)
+    n = K.shape[0]
+    rng = np.random.default_rng(4)
+    b = K @ rng.standard_normal(n)
+
+    def count(M):
+        its = [0]
+
+        def cb(_):
+            its[0] += 1
+        x, info = spl.cg(K, b, rtol=1e-10, atol=0.0, maxiter=2000, M=spl.LinearOperator((n, n), matvec=M), callback=cb)
+        assert info == 0 and np.linalg.norm(b - K @ x) < 1e-8 * np.linalg.norm(b)
+        return its[0]
+
+    its_bj = count(node_block_jacobi(K, 3))
+    its_asm = count(lambda r: run_emulated(mesh, K, 3, r, grid=2)[0])
+    assert its_asm < 0.7 * its_bj, (its_asm, its_bj)
