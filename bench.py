@@ -46,7 +46,7 @@ def parse_args():
     ap.add_argument("--ngl", type=int, default=4)
     ap.add_argument("--rtol", type=float, default=1e-10, help="KSP relative tolerance")
     ap.add_argument("--dt", type=float, default=1e-3, help="fixed time step (-ts_adapt_type none)")
-    ap.add_argument("--pc", default="bjacobi", choices=["jacobi", "bjacobi", "none"])
+    ap.add_argument("--pc", default="bjacobi", choices=["jacobi", "bjacobi", "none", "asm"])
     ap.add_argument("--cpu-nelem", type=int, default=8, help="mesh of the bounded CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")

@@ -92,6 +92,7 @@ class OracleProblem:
         self.mats = assembly.assemble_kle(tab, corner_xyz, elem_nodes, nnodes, cls, "FS", reuse=reuse)
         self.ops = assembly.assemble_ops(tab, corner_xyz, elem_nodes, nnodes, reuse=reuse)
         self.solver, self.rtol, self.pc = solver, rtol, pc
+        self.elem_nodes = np.asarray(elem_nodes, dtype=np.int64)
         self.K = self.mats["K"].tocsr()
         if solver == "direct":
             self._lu = spl.splu(self.K.tocsc())
@@ -110,6 +111,21 @@ class OracleProblem:
         if self.pc == "jacobi":
             dinv = 1.0 / self.K.diagonal()
             self._M = spl.LinearOperator((n, n), matvec=lambda r: dinv * r)
+        elif self.pc == "asm":
+            # PETSc PCASM with one subdomain per spectral element, symmetrically weighted by
+            # 1/sqrt(elements sharing the dof):  sum_e R_e^T W inv(R_e K R_e^T) W R_e
+            en = self.elem_nodes
+            nel, nn = en.shape
+            dofs = (en[:, :, None] * d + np.arange(d)[None, None, :]).reshape(nel, nn * d)
+            inv = np.stack([np.linalg.inv(self.K[dofs[e]][:, dofs[e]].toarray()) for e in range(nel)])
+            wl = (1.0 / np.sqrt(np.bincount(dofs.ravel(), minlength=n)))[dofs]
+
+            def apply(r):
+                z = np.einsum("eij,ej->ei", inv, r[dofs] * wl) * wl
+                out = np.zeros_like(r)
+                np.add.at(out, dofs.ravel(), z.ravel())
+                return out
+            self._M = spl.LinearOperator((n, n), matvec=apply)
         else:                       # node-block Jacobi
             import scipy.sparse as sp
             B = sp.bsr_matrix(self.K, blocksize=(d, d))
