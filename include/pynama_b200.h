@@ -281,6 +281,11 @@ int pyn_ksp_set_tolerances(pyn_ksp* k, double rtol, double atol, int maxit, int 
  * iteration merged into one reduction (fused into the product kernel) and the rest of the
  * recurrence in one vector kernel: 2 launches and 1 reduction per iteration instead of 3 and 2. */
 int pyn_ksp_set_cg_single_reduction(pyn_ksp* k, int on);
+/* -pc_asm_coarse <steps> (PYN_PC_ASM only): adds a second level to the Schwarz preconditioner, the Q1
+ * space on the element corners with the Galerkin operator P^T K P (probed through K's own product,
+ * one product per colour and component), solved approximately by <steps> Chebyshev steps with point
+ * Jacobi -- a fixed polynomial, so the preconditioner stays linear and symmetric.  0 = one level. */
+int pyn_ksp_set_asm_coarse(pyn_ksp* k, int steps);
 int pyn_ksp_set_fischer_guess(pyn_ksp* k, int model, int size);
 /* x: initial guess in, solution out (KSP.__call__(b, x), kle_solver.py:35).
  * reason > 0 converged (2 rtol, 3 atol), < 0 diverged (-3 max iterations). */

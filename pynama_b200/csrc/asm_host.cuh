@@ -7,7 +7,7 @@
 #include <algorithm>
 #include <unordered_map>
 #include <vector>
-#include "common.cuh"
+#include "tables.cuh"
 
 namespace pyn {
 
@@ -120,6 +120,197 @@ inline int64_t asm_make_tiles(int64_t nel, const int32_t* cls, int64_t nclass, i
     }
   }
   return (int64_t)tile_class->size();
+}
+
+// ---- Q1 coarse space on the element corners (second level of the preconditioner) -----------------
+// Coarse vertices = the fine nodes that are a corner of some element, numbered by ascending node.
+struct AsmCoarseTables {
+  int64_t nv = 0;
+  int ncolors = 0;
+  std::vector<int32_t> vert_node;    // [nv] fine node of coarse vertex v
+  std::vector<int32_t> elem_verts;   // [nel][ncorner]
+  std::vector<int64_t> v2e_ptr;      // [nv+1]
+  std::vector<int32_t> v2e;          // [.][2] (element, corner) of vertex v, ascending element
+  std::vector<int64_t> adj_ptr;      // [nv+1] vertices sharing an element with v (v included), ascending
+  std::vector<int32_t> adj;
+  std::vector<int32_t> color;        // [nv] no two vertices adjacent to a common vertex share a colour
+};
+
+inline void asm_coarse_tables(int64_t nel, int64_t nnodes, int nn, int ncorner, const int32_t* elem_nodes,
+                              const int* corner_local, AsmCoarseTables* t) {
+  std::vector<int32_t> vid((size_t)nnodes, -1);
+  for (int64_t e = 0; e < nel; ++e)
+    for (int c = 0; c < ncorner; ++c) vid[(size_t)elem_nodes[e * nn + corner_local[c]]] = 0;
+  t->vert_node.clear();
+  for (int64_t n = 0; n < nnodes; ++n)
+    if (vid[(size_t)n] == 0) {
+      vid[(size_t)n] = (int32_t)t->vert_node.size();
+      t->vert_node.push_back((int32_t)n);
+    }
+  const int64_t nv = t->nv = (int64_t)t->vert_node.size();
+  t->elem_verts.assign((size_t)(nel * ncorner), 0);
+  t->v2e_ptr.assign((size_t)nv + 1, 0);
+  for (int64_t e = 0; e < nel; ++e)
+    for (int c = 0; c < ncorner; ++c) {
+      const int32_t v = vid[(size_t)elem_nodes[e * nn + corner_local[c]]];
+      t->elem_verts[(size_t)(e * ncorner + c)] = v;
+      t->v2e_ptr[(size_t)v + 1]++;
+    }
+  for (int64_t v = 0; v < nv; ++v) t->v2e_ptr[(size_t)v + 1] += t->v2e_ptr[(size_t)v];
+  t->v2e.assign((size_t)(2 * t->v2e_ptr[(size_t)nv]), 0);
+  std::vector<int64_t> fill(t->v2e_ptr.begin(), t->v2e_ptr.end() - 1);
+  for (int64_t e = 0; e < nel; ++e)              // ascending element inside every list
+    for (int c = 0; c < ncorner; ++c) {
+      const int32_t v = t->elem_verts[(size_t)(e * ncorner + c)];
+      const int64_t k = fill[(size_t)v]++;
+      t->v2e[(size_t)(2 * k)] = (int32_t)e;
+      t->v2e[(size_t)(2 * k + 1)] = c;
+    }
+  t->adj_ptr.assign((size_t)nv + 1, 0);
+  t->adj.clear();
+  std::vector<int32_t> tmp;
+  for (int64_t v = 0; v < nv; ++v) {
+    tmp.clear();
+    for (int64_t k = t->v2e_ptr[(size_t)v]; k < t->v2e_ptr[(size_t)v + 1]; ++k) {
+      const int64_t e = t->v2e[(size_t)(2 * k)];
+      for (int c = 0; c < ncorner; ++c) tmp.push_back(t->elem_verts[(size_t)(e * ncorner + c)]);
+    }
+    std::sort(tmp.begin(), tmp.end());
+    tmp.erase(std::unique(tmp.begin(), tmp.end()), tmp.end());
+    t->adj.insert(t->adj.end(), tmp.begin(), tmp.end());
+    t->adj_ptr[(size_t)v + 1] = (int64_t)t->adj.size();
+  }
+  // greedy distance-2 colouring: a colour may be used by v only if no vertex within two adjacency
+  // steps has it, so every vertex sees at most one vertex of a colour among its neighbours
+  t->color.assign((size_t)nv, -1);
+  t->ncolors = 0;
+  std::vector<int64_t> stamp;
+  for (int64_t v = 0; v < nv; ++v) {
+    stamp.assign((size_t)t->ncolors + 1, -1);
+    for (int64_t k = t->adj_ptr[(size_t)v]; k < t->adj_ptr[(size_t)v + 1]; ++k) {
+      const int64_t w = t->adj[(size_t)k];
+      for (int64_t k2 = t->adj_ptr[(size_t)w]; k2 < t->adj_ptr[(size_t)w + 1]; ++k2) {
+        const int32_t cw = t->color[(size_t)t->adj[(size_t)k2]];
+        if (cw >= 0) stamp[(size_t)cw] = v;
+      }
+    }
+    int c = 0;
+    while (c < t->ncolors && stamp[(size_t)c] == v) ++c;
+    t->color[(size_t)v] = c;
+    if (c == t->ncolors) t->ncolors++;
+  }
+}
+
+// corner_local[c] = local node sitting on corner c; phi[a*ncorner + c] = value at local node a of
+// the multilinear shape function of corner c (the Q1 prolongation weights)
+inline int asm_coarse_phi(const ElemTables& t, int* corner_local, std::vector<double>* phi) {
+  const Rule1D& nodal = t.rule[RULE_NODAL];
+  phi->assign((size_t)t.nn * t.ncorner, 0.0);
+  for (int c = 0; c < t.ncorner; ++c) {
+    corner_local[c] = -1;
+    for (int a = 0; a < t.nn; ++a) {
+      bool here = true;
+      double w = 1.0;
+      for (int d = 0; d < t.dim; ++d) {
+        here = here && t.node_t[a][d] == t.corn_t[c][d] * (t.ngl - 1);
+        w *= nodal.hc[t.node_t[a][d]][t.corn_t[c][d]];
+      }
+      if (fabs(w) < 1e-14) w = 0.0;             // the other corners' functions vanish on a face
+      (*phi)[(size_t)a * t.ncorner + c] = w;
+      if (here) corner_local[c] = a;
+    }
+    if (corner_local[c] < 0) return -1;
+  }
+  return 0;
+}
+
+// position of column w in the (ascending) list of row v, or -1
+inline int64_t asm_coarse_find(const int64_t* ptr, const int32_t* col, int64_t v, int32_t w) {
+  const int32_t* lo = col + ptr[v];
+  const int32_t* hi = col + ptr[v + 1];
+  const int32_t* it = std::lower_bound(lo, hi, w);
+  return (it != hi && *it == w) ? (int64_t)(it - col) : -1;
+}
+
+// block (v,w) <- (block (v,w) + block (w,v)^T)/2 of a block CSR with a symmetric pattern
+inline void asm_coarse_symmetrise(int64_t nv, int B, const int64_t* ptr, const int32_t* col, double* val) {
+  for (int64_t v = 0; v < nv; ++v)
+    for (int64_t k = ptr[v]; k < ptr[v + 1]; ++k) {
+      const int32_t w = col[k];
+      if (w < v) continue;
+      const int64_t k2 = w == v ? k : asm_coarse_find(ptr, col, w, (int32_t)v);
+      if (k2 < 0) continue;
+      for (int i = 0; i < B; ++i)
+        for (int j = 0; j < B; ++j) {
+          if (k2 == k && j < i) continue;
+          double& a = val[(k * B + i) * B + j];
+          double& b = val[(k2 * B + j) * B + i];
+          const double m = 0.5 * (a + b);
+          a = b = m;
+        }
+    }
+}
+
+// dinv[v*B+i] = 1/Ac[(v,i),(v,i)], or 0 for an inactive coarse dof (empty column of P: every fine dof
+// it would reach is constrained)
+inline void asm_coarse_jacobi(int64_t nv, int B, const int64_t* ptr, const int32_t* col, const double* val,
+                              double* dinv) {
+  double dmax = 0.0;
+  for (int64_t v = 0; v < nv; ++v) {
+    const int64_t k = asm_coarse_find(ptr, col, v, (int32_t)v);
+    for (int i = 0; i < B; ++i) {
+      const double d = k >= 0 ? val[(k * B + i) * B + i] : 0.0;
+      dinv[v * B + i] = d;
+      dmax = std::max(dmax, d);
+    }
+  }
+  for (int64_t i = 0; i < nv * B; ++i) dinv[i] = dinv[i] > 1e-12 * dmax ? 1.0 / dinv[i] : 0.0;
+}
+
+// largest eigenvalue of D^-1 A (A block CSR over the adjacency lists, B x B blocks row-major, D its
+// diagonal) by power iteration from a fixed start; dinv[i] = 0 marks an inactive coarse dof
+inline double asm_power_lmax(int64_t nv, int B, const int64_t* ptr, const int32_t* col, const double* val,
+                             const double* dinv, int iters) {
+  const int64_t n = nv * B;
+  std::vector<double> x((size_t)n), y((size_t)n);
+  for (int64_t i = 0; i < n; ++i) x[(size_t)i] = dinv[i] != 0.0 ? 1.0 + 0.37 * (double)((i * 7919) % 13) : 0.0;
+  double lam = 0.0;
+  for (int it = 0; it < iters; ++it) {
+    double nx = 0.0;
+    for (int64_t i = 0; i < n; ++i) nx += x[(size_t)i] * x[(size_t)i];
+    nx = sqrt(nx);
+    if (!(nx > 0.0)) return 0.0;
+    for (int64_t i = 0; i < n; ++i) x[(size_t)i] /= nx;
+    for (int64_t v = 0; v < nv; ++v)
+      for (int i = 0; i < B; ++i) {
+        double s = 0.0;
+        for (int64_t k = ptr[v]; k < ptr[v + 1]; ++k)
+          for (int j = 0; j < B; ++j) s += val[(k * B + i) * B + j] * x[(size_t)(col[k] * (int64_t)B + j)];
+        y[(size_t)(v * B + i)] = dinv[v * B + i] * s;
+      }
+    double ny = 0.0;
+    for (int64_t i = 0; i < n; ++i) ny += y[(size_t)i] * y[(size_t)i];
+    lam = sqrt(ny);
+    x.swap(y);
+  }
+  return lam;
+}
+
+// coefficients of k Chebyshev steps on [lmin, lmax] (zero start):
+//   d_0 = c2[0] D^-1 r;  step s = 1..k: x += d, r -= A d, d = c1[s] d + c2[s] D^-1 r
+inline void asm_cheb_coefficients(int k, double lmin, double lmax, std::vector<double>* c1, std::vector<double>* c2) {
+  const double theta = 0.5 * (lmax + lmin), delta = 0.5 * (lmax - lmin);
+  const double sigma = theta / delta;
+  double rho = 1.0 / sigma;
+  c1->assign((size_t)k + 1, 0.0);
+  c2->assign((size_t)k + 1, 0.0);
+  (*c2)[0] = 1.0 / theta;
+  for (int s = 1; s <= k; ++s) {
+    const double rho_new = 1.0 / (2.0 * sigma - rho);
+    (*c1)[(size_t)s] = rho_new * rho;
+    (*c2)[(size_t)s] = 2.0 * rho_new / delta;
+    rho = rho_new;
+  }
 }
 
 }  // namespace pyn

@@ -174,12 +174,23 @@ asm_mult_kernel(int64_t ntiles, const int32_t* __restrict__ tile_elems, const in
   }
 }
 
-// z[node] = sum over the elements of the node, ascending, of their local results
+// second level: prolongation of the coarse correction xc (Q1 on the element corners), added by
+// asm_sum_kernel.  xc == NULL: one-level preconditioner.
+struct AsmProlong {
+  const double* xc;             // [nv][B]
+  const int32_t* elem_verts;    // [nel][ncorner] coarse vertex of corner q of element e
+  const double* phi;            // [nn][ncorner] corner (multilinear) basis at the local nodes
+  const double* keep;           // [nnodes*B] 1 free dof, 0 constrained (identity row of K)
+  int ncorner;
+};
+
+// z[node] = sum over the elements of the node, ascending, of their local results (+ P xc)
 template <int B>
 __global__ void __launch_bounds__(256)
 asm_sum_kernel(int64_t nnodes, const int64_t* __restrict__ n2e_ptr, const int2* __restrict__ n2e,
                const double* __restrict__ ybuf, int ld, const double* __restrict__ r, double* __restrict__ z,
-               double* partials, unsigned int* ticket, double* dots, const double* __restrict__ done) {
+               double* partials, unsigned int* ticket, double* dots, const double* __restrict__ done,
+               AsmProlong cp) {
   __shared__ double sm[64];
   if (done && *done != 0.0) return;
   double v[2] = {0.0, 0.0};
@@ -194,6 +205,18 @@ asm_sum_kernel(int64_t nnodes, const int64_t* __restrict__ n2e_ptr, const int2* 
 #pragma unroll
       for (int c = 0; c < B; ++c) zz[c] += y[c];
     }
+    if (cp.xc && n2e_ptr[n + 1] > n2e_ptr[n]) {    // + P xc through the node's first element
+      const int2 ea = n2e[n2e_ptr[n]];
+      const int32_t* ev = cp.elem_verts + (int64_t)ea.x * cp.ncorner;
+      for (int q = 0; q < cp.ncorner; ++q) {
+        const double w = cp.phi[ea.y * cp.ncorner + q];
+        if (w != 0.0) {
+          const double* x = cp.xc + (int64_t)ev[q] * B;
+#pragma unroll
+          for (int c = 0; c < B; ++c) zz[c] += cp.keep[n * B + c] * w * x[c];
+        }
+      }
+    }
 #pragma unroll
     for (int c = 0; c < B; ++c) {
       z[n * B + c] = zz[c];
@@ -206,6 +229,146 @@ asm_sum_kernel(int64_t nnodes, const int64_t* __restrict__ n2e_ptr, const int2* 
   if (dots) {
     block_reduce<2>(v, sm);
     grid_reduce_finish<2>(v, partials, ticket, dots);
+  }
+}
+
+// keep[n*B+i] = 1 when row i of node n couples to anything but its own diagonal entry, else 0
+// (the identity rows K keeps for constrained dofs).  One warp per node.
+template <int B>
+__global__ void __launch_bounds__(256)
+asm_free_dofs_kernel(int64_t nnodes, const int64_t* __restrict__ rowptr, const int32_t* __restrict__ colidx,
+                     const double* __restrict__ val, double* __restrict__ keep) {
+  constexpr int BB = B * B;
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  for (int64_t n = warp; n < nnodes; n += nwarps) {
+    const int64_t p0 = rowptr[n];
+    const int nb = (int)(rowptr[n + 1] - p0);
+    int flag[B];
+#pragma unroll
+    for (int i = 0; i < B; ++i) flag[i] = 0;
+    for (int u = lane; u < nb; u += 32) {
+      const int64_t c = colidx[p0 + u];
+#pragma unroll
+      for (int q = 0; q < BB; ++q) {
+        const int i = q / B, j = q - i * B;
+        if (val[p0 * BB + (int64_t)q * nb + u] != 0.0 && !(c == n && i == j)) flag[i] = 1;
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < B; ++i) {
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) flag[i] |= __shfl_xor_sync(0xffffffffu, flag[i], o);
+      if (lane == 0) keep[n * B + i] = flag[i] ? 1.0 : 0.0;
+    }
+  }
+}
+
+// rc = P^T (keep r): one warp per coarse vertex over its (element, corner) list; a fine node
+// contributes through its first element only (the one asm_sum_kernel prolongs through), lanes
+// over the local nodes, fixed reduction tree
+template <int B>
+__global__ void __launch_bounds__(256)
+asm_restrict_kernel(int64_t nv, const int64_t* __restrict__ v2e_ptr, const int2* __restrict__ v2e,
+                    const int32_t* __restrict__ elem_nodes, int nn, int ncorner, const double* __restrict__ phi,
+                    const int64_t* __restrict__ n2e_ptr, const int2* __restrict__ n2e,
+                    const double* __restrict__ keep, const double* __restrict__ r, double* __restrict__ rc,
+                    const double* __restrict__ done) {
+  if (done && *done != 0.0) return;
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  for (int64_t v = warp; v < nv; v += nwarps) {
+    double acc[B];
+#pragma unroll
+    for (int i = 0; i < B; ++i) acc[i] = 0.0;
+    for (int64_t k = v2e_ptr[v]; k < v2e_ptr[v + 1]; ++k) {
+      const int2 ec = v2e[k];
+      for (int a = lane; a < nn; a += 32) {
+        const double w = phi[a * ncorner + ec.y];
+        if (w == 0.0) continue;
+        const int64_t n = elem_nodes[(int64_t)ec.x * nn + a];
+        const int2 first = n2e[n2e_ptr[n]];
+        if (first.x != ec.x || first.y != a) continue;
+#pragma unroll
+        for (int i = 0; i < B; ++i) acc[i] += w * keep[n * B + i] * r[n * B + i];
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < B; ++i) {
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) acc[i] += __shfl_xor_sync(0xffffffffu, acc[i], o);
+      if (lane == 0) rc[v * B + i] = acc[i];
+    }
+  }
+}
+
+// Chebyshev iteration on the coarse problem Ac xc = rc with point Jacobi (Ac: block CSR over the
+// vertex adjacency, B x B blocks row-major).  first: xc = 0, d_new = c2 D^-1 rc.  Otherwise one
+// step: xc += d_old, rc -= Ac d_old, d_new = c1 d_old + c2 D^-1 rc.  One thread per vertex.
+template <int B>
+__global__ void __launch_bounds__(256)
+asm_cheb_kernel(int64_t nv, const int64_t* __restrict__ ptr, const int32_t* __restrict__ col,
+                const double* __restrict__ val, const double* __restrict__ dinv, int first, double c1, double c2,
+                double* __restrict__ rc, double* __restrict__ xc, const double* __restrict__ d_old,
+                double* __restrict__ d_new, const double* __restrict__ done) {
+  if (done && *done != 0.0) return;
+  for (int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v < nv; v += (int64_t)gridDim.x * blockDim.x) {
+    if (first) {
+#pragma unroll
+      for (int i = 0; i < B; ++i) {
+        xc[v * B + i] = 0.0;
+        d_new[v * B + i] = c2 * dinv[v * B + i] * rc[v * B + i];
+      }
+      continue;
+    }
+    double ad[B];
+#pragma unroll
+    for (int i = 0; i < B; ++i) ad[i] = 0.0;
+    for (int64_t k = ptr[v]; k < ptr[v + 1]; ++k) {
+      const double* a = val + k * B * B;
+      const double* d = d_old + (int64_t)col[k] * B;
+#pragma unroll
+      for (int i = 0; i < B; ++i)
+#pragma unroll
+        for (int j = 0; j < B; ++j) ad[i] += a[i * B + j] * d[j];
+    }
+#pragma unroll
+    for (int i = 0; i < B; ++i) {
+      const double dv = d_old[v * B + i];
+      xc[v * B + i] += dv;
+      const double rn = rc[v * B + i] - ad[i];
+      rc[v * B + i] = rn;
+      d_new[v * B + i] = c1 * dv + c2 * dinv[v * B + i] * rn;
+    }
+  }
+}
+
+// xf = keep (P xc): prolongation alone (set-up: probing the Galerkin coarse operator)
+template <int B>
+__global__ void __launch_bounds__(256)
+asm_prolong_kernel(int64_t nnodes, const int64_t* __restrict__ n2e_ptr, const int2* __restrict__ n2e,
+                   AsmProlong cp, double* __restrict__ xf) {
+  for (int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; n < nnodes;
+       n += (int64_t)gridDim.x * blockDim.x) {
+    double zz[B];
+#pragma unroll
+    for (int c = 0; c < B; ++c) zz[c] = 0.0;
+    if (n2e_ptr[n + 1] > n2e_ptr[n]) {
+      const int2 ea = n2e[n2e_ptr[n]];
+      const int32_t* ev = cp.elem_verts + (int64_t)ea.x * cp.ncorner;
+      for (int q = 0; q < cp.ncorner; ++q) {
+        const double w = cp.phi[ea.y * cp.ncorner + q];
+        if (w != 0.0) {
+          const double* x = cp.xc + (int64_t)ev[q] * B;
+#pragma unroll
+          for (int c = 0; c < B; ++c) zz[c] += cp.keep[n * B + c] * w * x[c];
+        }
+      }
+    }
+#pragma unroll
+    for (int c = 0; c < B; ++c) xf[n * B + c] = zz[c];
   }
 }
 

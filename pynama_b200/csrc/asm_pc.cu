@@ -16,11 +16,12 @@
 //                    (fixed order: run-to-run reproducible, no atomics), optionally r.z and z.z
 #include "asm_pc.cuh"
 #include "asm_kernels.cuh"
+#include "spmv.cuh"
 
 namespace pyn {
 
 template <int B>
-static int asm_setup_impl(pyn_ctx* ctx, const pyn_mat* A, AsmPc* pc) {
+static int asm_setup_impl(pyn_ctx* ctx, pyn_mat* A, AsmPc* pc) {
   pyn_mesh* mesh = A->mesh;
   const int nn = mesh->nn, ld = nn * B;
   const int64_t nel = mesh->nel;
@@ -83,7 +84,105 @@ static int asm_setup_impl(pyn_ctx* ctx, const pyn_mat* A, AsmPc* pc) {
   return PYN_OK;
 }
 
-int asm_setup(pyn_ctx* ctx, const pyn_mat* A, AsmPc** out) {
+template <int B>
+static AsmProlong asm_prolong_args(const AsmPc* pc, const double* xc) {
+  AsmProlong cp;
+  cp.xc = xc;
+  cp.elem_verts = pc->elem_verts.p;
+  cp.phi = pc->phi.p;
+  cp.keep = pc->keep.p;
+  cp.ncorner = pc->ncorner;
+  return cp;
+}
+
+template <int B>
+static int asm_restrict(pyn_ctx* ctx, AsmPc* pc, const double* r, double* rc, const double* done) {
+  pyn_mesh* mesh = pc->mesh;
+  asm_restrict_kernel<B><<<grid_for(ctx, pc->nv * 32, 256), 256, 0, ctx->stream>>>(
+      pc->nv, pc->v2e_ptr.p, pc->v2e.p, mesh->elem_nodes.p, mesh->nn, pc->ncorner, pc->phi.p, mesh->n2e_ptr.p,
+      mesh->n2e.p, pc->keep.p, r, rc, done);
+  PYN_LAUNCHED(ctx);
+  return PYN_OK;
+}
+
+// Second level: tables, the free-dof mask, the Galerkin operator by coloured probing (one product
+// with K per colour and component: same-coloured coarse functions never meet in a coarse row),
+// its Jacobi diagonal, the Chebyshev interval.
+template <int B>
+static int asm_coarse_setup(pyn_ctx* ctx, pyn_mat* A, AsmPc* pc) {
+  pyn_mesh* mesh = pc->mesh;
+  const int nn = mesh->nn, ncorner = mesh->htab.ncorner;
+  const int64_t nel = mesh->nel, nnodes = mesh->nnodes;
+  pc->ncorner = ncorner;
+  int corner_local[8];
+  std::vector<double> phi;
+  PYN_REQUIRE(asm_coarse_phi(mesh->htab, corner_local, &phi) == 0, "pc asm: element corner nodes not found");
+  std::vector<int32_t> en((size_t)(nel * nn));
+  PYN_CHECK(mesh->elem_nodes.download(en.data(), nel * nn));
+  AsmCoarseTables T;
+  asm_coarse_tables(nel, nnodes, nn, ncorner, en.data(), corner_local, &T);
+  const int64_t nv = pc->nv = T.nv;
+  pc->ncolors = T.ncolors;
+  PYN_CHECK(pc->phi.alloc(ctx, (int64_t)phi.size()));
+  PYN_CHECK(pc->phi.upload(phi.data(), (int64_t)phi.size()));
+  PYN_CHECK(pc->elem_verts.alloc(ctx, nel * ncorner));
+  PYN_CHECK(pc->elem_verts.upload(T.elem_verts.data(), nel * ncorner));
+  PYN_CHECK(pc->v2e_ptr.alloc(ctx, nv + 1));
+  PYN_CHECK(pc->v2e_ptr.upload(T.v2e_ptr.data(), nv + 1));
+  static_assert(sizeof(int2) == 2 * sizeof(int32_t), "int2 layout");
+  const int64_t nv2e = T.v2e_ptr[(size_t)nv];
+  PYN_CHECK(pc->v2e.alloc(ctx, nv2e));
+  PYN_CHECK(pc->v2e.upload(reinterpret_cast<const int2*>(T.v2e.data()), nv2e));
+  PYN_CHECK(pc->keep.alloc(ctx, nnodes * B));
+  asm_free_dofs_kernel<B><<<grid_for(ctx, nnodes * 32, 256), 256, 0, ctx->stream>>>(nnodes, A->rowptr.p, A->colidx.p,
+                                                                                    A->val.p, pc->keep.p);
+  PYN_LAUNCHED(ctx);
+  PYN_CHECK(pc->rc.alloc(ctx, nv * B));
+  PYN_CHECK(pc->xc.alloc(ctx, nv * B));
+  PYN_CHECK(pc->d0.alloc(ctx, nv * B));
+  PYN_CHECK(pc->d1.alloc(ctx, nv * B));
+  // probing
+  const int64_t nnzb = T.adj_ptr[(size_t)nv];
+  std::vector<double> val((size_t)(nnzb * B * B), 0.0), xh((size_t)(nv * B)), th((size_t)(nv * B));
+  DevBuf<double> xf, yf;
+  PYN_CHECK(xf.alloc(ctx, nnodes * B));
+  PYN_CHECK(yf.alloc(ctx, nnodes * B));
+  const int gridn = grid_for(ctx, nnodes, 256);
+  for (int color = 0; color < T.ncolors; ++color)
+    for (int j = 0; j < B; ++j) {
+      for (int64_t v = 0; v < nv; ++v)
+        for (int i = 0; i < B; ++i) xh[(size_t)(v * B + i)] = (T.color[(size_t)v] == color && i == j) ? 1.0 : 0.0;
+      PYN_CHECK(pc->xc.upload(xh.data(), nv * B));
+      asm_prolong_kernel<B><<<gridn, 256, 0, ctx->stream>>>(nnodes, mesh->n2e_ptr.p, mesh->n2e.p,
+                                                            asm_prolong_args<B>(pc, pc->xc.p), xf.p);
+      PYN_LAUNCHED(ctx);
+      PYN_CHECK(spmv(A, 1.0, xf.p, 0.0, nullptr, yf.p));
+      PYN_CHECK(asm_restrict<B>(ctx, pc, yf.p, pc->rc.p, nullptr));
+      PYN_CHECK(pc->rc.download(th.data(), nv * B));
+      for (int64_t v = 0; v < nv; ++v)
+        for (int64_t k = T.adj_ptr[(size_t)v]; k < T.adj_ptr[(size_t)v + 1]; ++k)
+          if (T.color[(size_t)T.adj[(size_t)k]] == color)
+            for (int i = 0; i < B; ++i) val[(size_t)((k * B + i) * B + j)] = th[(size_t)(v * B + i)];
+    }
+  asm_coarse_symmetrise(nv, B, T.adj_ptr.data(), T.adj.data(), val.data());
+  std::vector<double> dinv((size_t)(nv * B), 0.0);
+  asm_coarse_jacobi(nv, B, T.adj_ptr.data(), T.adj.data(), val.data(), dinv.data());
+  pc->lmax = 1.1 * asm_power_lmax(nv, B, T.adj_ptr.data(), T.adj.data(), val.data(), dinv.data(), 40);
+  PYN_REQUIRE(pc->lmax > 0.0 && std::isfinite(pc->lmax), "pc asm: the coarse operator is empty or not finite");
+  asm_cheb_coefficients(pc->coarse_steps, 0.1 * pc->lmax, pc->lmax, &pc->c1, &pc->c2);
+  PYN_CHECK(pc->ac_ptr.alloc(ctx, nv + 1));
+  PYN_CHECK(pc->ac_ptr.upload(T.adj_ptr.data(), nv + 1));
+  PYN_CHECK(pc->ac_col.alloc(ctx, nnzb));
+  PYN_CHECK(pc->ac_col.upload(T.adj.data(), nnzb));
+  PYN_CHECK(pc->ac_val.alloc(ctx, nnzb * B * B));
+  PYN_CHECK(pc->ac_val.upload(val.data(), nnzb * B * B));
+  PYN_CHECK(pc->ac_dinv.alloc(ctx, nv * B));
+  PYN_CHECK(pc->ac_dinv.upload(dinv.data(), nv * B));
+  PYN_CUDA(cudaStreamSynchronize(ctx->stream));
+  return PYN_OK;
+}
+
+int asm_setup(pyn_ctx* ctx, pyn_mat* A, int coarse_steps, AsmPc** out) {
   *out = nullptr;
   PYN_REQUIRE(A->mesh && !A->free_pattern, "pc asm needs an operator assembled from a mesh");
   PYN_REQUIRE(A->br == A->bc && A->nbrows == A->mesh->nnodes, "pc asm: operator is not square over the mesh nodes");
@@ -92,10 +191,15 @@ int asm_setup(pyn_ctx* ctx, const pyn_mat* A, AsmPc** out) {
     return PYN_E_UNSUPPORTED;
   }
   AsmPc* pc = new AsmPc();
+  pc->coarse_steps = coarse_steps > 0 ? coarse_steps : 0;
   int rc;
-  if (A->br == 3) rc = asm_setup_impl<3>(ctx, A, pc);
-  else if (A->br == 2) rc = asm_setup_impl<2>(ctx, A, pc);
-  else {
+  if (A->br == 3) {
+    rc = asm_setup_impl<3>(ctx, A, pc);
+    if (rc == PYN_OK && pc->coarse_steps > 0) rc = asm_coarse_setup<3>(ctx, A, pc);
+  } else if (A->br == 2) {
+    rc = asm_setup_impl<2>(ctx, A, pc);
+    if (rc == PYN_OK && pc->coarse_steps > 0) rc = asm_coarse_setup<2>(ctx, A, pc);
+  } else {
     set_error("pc asm: unsupported block size %d", A->br);
     rc = PYN_E_UNSUPPORTED;
   }
@@ -116,9 +220,24 @@ static int asm_apply_impl(pyn_ctx* ctx, AsmPc* pc, const double* r, double* z, d
       pc->ntiles, pc->tile_elems.p, pc->tile_class.p, mesh->elem_nodes.p, mesh->nn, pc->inv.p, pc->wnode.p, r,
       pc->ybuf.p, done);
   PYN_LAUNCHED(ctx);
+  const double* xc = nullptr;
+  if (pc->coarse_steps > 0) {                  // xc ~ Ac^-1 P^T r by coarse_steps Chebyshev steps
+    PYN_CHECK(asm_restrict<B>(ctx, pc, r, pc->rc.p, done));
+    const int gridc = grid_for(ctx, pc->nv, 256);
+    double* dold = pc->d0.p;
+    double* dnew = pc->d1.p;
+    for (int s = 0; s <= pc->coarse_steps; ++s) {
+      asm_cheb_kernel<B><<<gridc, 256, 0, ctx->stream>>>(pc->nv, pc->ac_ptr.p, pc->ac_col.p, pc->ac_val.p,
+                                                         pc->ac_dinv.p, s == 0 ? 1 : 0, pc->c1[(size_t)s],
+                                                         pc->c2[(size_t)s], pc->rc.p, pc->xc.p, dold, dnew, done);
+      PYN_LAUNCHED(ctx);
+      std::swap(dold, dnew);
+    }
+    xc = pc->xc.p;
+  }
   asm_sum_kernel<B><<<grid_for(ctx, mesh->nnodes, 256), 256, 0, ctx->stream>>>(
       mesh->nnodes, mesh->n2e_ptr.p, mesh->n2e.p, pc->ybuf.p, pc->ld, r, z, ctx->red_partials, ctx->red_ticket,
-      dots, done);
+      dots, done, asm_prolong_args<B>(pc, xc));
   PYN_LAUNCHED(ctx);
   return PYN_OK;
 }

@@ -1,5 +1,6 @@
 // asm_pc.cuh -- element-block additive Schwarz preconditioner for the KLE operator (-pc_type asm)
 #pragma once
+#include <vector>
 #include "mesh.cuh"
 
 namespace pyn {
@@ -17,13 +18,29 @@ struct AsmPc {
   DevBuf<double> wnode;            // [nnodes]
   DevBuf<double> ybuf;             // [nel][ld] element-local results of the last apply
   size_t smem = 0;
+  // second level (coarse_steps > 0): Q1 space on the element corners, Galerkin operator
+  // Ac = P^T K P probed through K's own product, coarse_steps Chebyshev steps with point Jacobi
+  int coarse_steps = 0;
+  int64_t nv = 0;
+  int ncorner = 0, ncolors = 0;
+  double lmax = 0.0;
+  DevBuf<int32_t> elem_verts;      // [nel][ncorner]
+  DevBuf<double> phi, keep;        // [nn][ncorner], [nnodes*B]
+  DevBuf<int64_t> v2e_ptr;
+  DevBuf<int2> v2e;
+  DevBuf<int64_t> ac_ptr;          // block CSR of Ac over the vertex adjacency
+  DevBuf<int32_t> ac_col;
+  DevBuf<double> ac_val, ac_dinv;
+  DevBuf<double> rc, xc, d0, d1;
+  std::vector<double> c1, c2;      // Chebyshev coefficients (asm_host.cuh)
 };
 
 // more distinct element blocks than this (bytes of inverses) is refused: the apply would read
 // more than the SpMV it is meant to save
 constexpr int64_t kAsmMaxInverseBytes = (int64_t)1 << 30;
 
-int asm_setup(pyn_ctx* ctx, const pyn_mat* A, AsmPc** out);
+// coarse_steps: 0 = one level; k > 0 = plus the coarse correction with k Chebyshev steps
+int asm_setup(pyn_ctx* ctx, pyn_mat* A, int coarse_steps, AsmPc** out);
 // z = M^-1 r.  dots != NULL: dots[0] = r.z, dots[1] = z.z (device).  done != NULL: a device flag;
 // when non-zero the apply is skipped (iterations launched after convergence).
 int asm_apply(pyn_ctx* ctx, AsmPc* pc, const double* r, double* z, double* dots, const double* done);

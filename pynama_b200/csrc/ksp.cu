@@ -558,6 +558,7 @@ struct pyn_ksp {
   std::vector<std::unique_ptr<DevBuf<double>>> gv;
   DevBuf<double> gcoef;
   AsmPc* asmpc = nullptr;               // -pc_type asm (asm_pc.cuh)
+  int asm_coarse = 0;                   // -pc_asm_coarse <k>: Chebyshev steps of the coarse level (0: off)
   ~pyn_ksp() { delete asmpc; }
 };
 
@@ -571,7 +572,7 @@ static int ksp_setup_pc(pyn_ksp* k) {
   if (k->pc == PYN_PC_ASM) {
     delete k->asmpc;
     k->asmpc = nullptr;
-    PYN_CHECK(asm_setup(ctx, k->A, &k->asmpc));
+    PYN_CHECK(asm_setup(ctx, k->A, k->asm_coarse, &k->asmpc));
     k->pc_ready = true;
     return PYN_OK;
   }
@@ -1072,6 +1073,14 @@ int pyn_ksp_set_tolerances(pyn_ksp* k, double rtol, double atol, int maxit, int 
   if (atol >= 0) k->atol = atol;
   if (maxit > 0) k->maxit = maxit;
   if (restart > 0) k->restart = restart;
+  return PYN_OK;
+}
+
+int pyn_ksp_set_asm_coarse(pyn_ksp* k, int steps) {
+  PYN_REQUIRE(k, "null ksp");
+  PYN_REQUIRE(steps >= 0 && steps <= 64, "pc asm: coarse Chebyshev steps %d out of range [0,64]", steps);
+  if (steps != k->asm_coarse) k->pc_ready = false;
+  k->asm_coarse = steps;
   return PYN_OK;
 }
 

@@ -809,6 +809,7 @@ class KSP:
         self._guess_nonzero = True
         self._fischer = (0, 0)              # (model, size); KSPSetUseFischerGuess, off by default
         self._cg_single_reduction = False   # KSPCGUseSingleReduction
+        self._asm_coarse = 0                # -pc_asm_coarse: Chebyshev steps of the Schwarz coarse level
         self._log = logging.getLogger("KSP")
 
     def create(self, comm=None):
@@ -859,9 +860,15 @@ class KSP:
         self._cg_single_reduction = bool(flag)
         self._drop()
 
+    def setASMCoarse(self, steps):
+        """second level of -pc_type asm: Q1 coarse space, `steps` Chebyshev steps (0 = off)"""
+        self._asm_coarse = int(steps)
+        self._drop()
+
     def setFromOptions(self):
         o = Options()
         self._type = o.getString("ksp_type", self._type)
+        self._asm_coarse = o.getInt("pc_asm_coarse", self._asm_coarse)
         sr = o.getBool("ksp_cg_single_reduction", None)
         if sr is not None:
             self._cg_single_reduction = sr
@@ -908,6 +915,8 @@ class KSP:
             call("pyn_ksp_set_fischer_guess", h, self._fischer[0], min(self._fischer[1], 32))
         if self._cg_single_reduction and ktype == "cg":
             call("pyn_ksp_set_cg_single_reduction", h, 1)
+        if pctype == "asm" and self._asm_coarse > 0:
+            call("pyn_ksp_set_asm_coarse", h, self._asm_coarse)
 
     def solve(self, b, x):
         self.setUp()

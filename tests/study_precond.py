@@ -13,6 +13,9 @@ Preconditioners:
   schwarz-w    the same, symmetrically weighted by 1/sqrt(multiplicity)
   +coarse      additive Q1 coarse-grid correction on the element corners (Galerkin P^T K P)
   +coarse/m    the same on macro cells of m x m x m elements
+  +coarse(ngl2)  the coarse operator assembled on the ngl = 2 mesh instead of the Galerkin product
+  +coarse~chebK  the Galerkin coarse problem solved by K Chebyshev steps with Jacobi (a fixed polynomial:
+               still a linear symmetric preconditioner) instead of exactly
 "its warm": the next solve of the time loop (boundary values one stage later) started from the
 previous solution.
 """
@@ -99,6 +102,51 @@ def coarse_correction(K, P, bdofs):
     return lambda r: Pk @ lu.solve(Pk.T @ r), Ac.shape[0]
 
 
+def coarse_rediscretised(mesh, prob, P, d):
+    """the same KLE operator assembled on the ngl = 2 mesh of the same corners (what the existing
+    assembly kernels could build on the device) instead of the Galerkin product; P maps its
+    lexicographic vertex grid to the fine nodes"""
+    nel = round(mesh.elem_nodes.shape[0] ** (1 / 3))
+    cm = BoxMesh([nel] * 3, [0, 0, 0], [1, 1, 1], 2)
+    cp = timestep.OracleProblem(3, 2, cm.corner_xyz, cm.elem_nodes, cm.coords, cm.getBordersNodes(),
+                                rho=prob.rho, mu=prob.mu, solver="direct")
+    # P's columns are numbered (ix*g + iy)*g + iz on the unit box: match the coarse mesh's nodes by coordinates
+    g = nel + 1
+    ijk = np.rint(cm.coords * nel).astype(int)
+    col_of_node = (ijk[:, 0] * g + ijk[:, 1]) * g + ijk[:, 2]
+    # P was built with columns (vertex, component) in grid order; reorder so column = coarse node*d + c
+    order = (col_of_node[:, None] * d + np.arange(d)[None, :]).ravel()
+    Pn = P.tocsc()[:, order].tocsr()
+    lu = spl.splu(cp.K.tocsc())
+    free = np.ones(cp.K.shape[0])
+    free[cp.bdofs] = 0.0                        # constrained coarse dofs carry no correction
+    keep = np.ones(P.shape[0])
+    keep[prob.bdofs] = 0.0
+    return lambda r: keep * (Pn @ (free * lu.solve(free * (Pn.T @ (keep * r)))))
+
+
+def chebyshev_inverse(A, dinv_apply, k, lmax, lmin_frac=0.1):
+    """k steps of Chebyshev iteration on the Jacobi-preconditioned A, zero start: a fixed
+    polynomial in A, hence a linear symmetric operator usable inside CG"""
+    lmin = lmin_frac * lmax
+    theta, delta = 0.5 * (lmax + lmin), 0.5 * (lmax - lmin)
+
+    def apply(b):
+        x = np.zeros_like(b)
+        r = b.copy()
+        sigma = theta / delta
+        rho = 1.0 / sigma
+        dvec = dinv_apply(r) / theta
+        for _ in range(k):
+            x = x + dvec
+            r = r - A @ dvec
+            rho_new = 1.0 / (2.0 * sigma - rho)
+            dvec = rho_new * rho * dvec + 2.0 * rho_new / delta * dinv_apply(r)
+            rho = rho_new
+        return x
+    return apply
+
+
 def run_cg(K, b, M, rtol, x0=None):
     its = [0]
 
@@ -141,6 +189,22 @@ def main():
     rows.append(("bjacobi+coarse", lambda r: bj(r) + cc(r)))
     rows.append(("schwarz+coarse", lambda r: sw(r) + cc(r)))
     rows.append(("schwarz-w+coarse", lambda r: swb(r) + cc(r)))
+    P1 = q1_prolongation(mesh, d, nel)
+    cr = coarse_rediscretised(mesh, prob, P1, d)
+    rows.append(("schwarz-w+coarse(ngl2)", lambda r: swb(r) + cr(r)))
+    # the Galerkin coarse problem solved only approximately: k Chebyshev steps with node-block Jacobi
+    keepv = np.ones(K.shape[0])
+    keepv[prob.bdofs] = 0.0
+    Pk = (sp.diags(keepv) @ P1).tocsr()
+    nzc = np.flatnonzero(np.asarray(abs(Pk).sum(0)).ravel() > 0)
+    Pk = Pk[:, nzc].tocsr()
+    Ac = (Pk.T @ K @ Pk).tocsr()
+    dinv = 1.0 / Ac.diagonal()
+    lmax = 1.1 * spl.eigsh(spl.LinearOperator(Ac.shape, matvec=lambda v: dinv * (Ac @ v)), k=1, which="LM",
+                           return_eigenvectors=False, tol=1e-3)[0]
+    for kc in (5, 10, 20):
+        ch = chebyshev_inverse(Ac, lambda v: dinv * v, kc, lmax)
+        rows.append((f"schwarz-w+coarse~cheb{kc}", lambda r, ch=ch: swb(r) + Pk @ ch(Pk.T @ r)))
     for m in (2, 4):
         if nel % m == 0 and nel // m >= 2:
             ccm, ncm = coarse_correction(K, q1_prolongation(mesh, d, nel // m), prob.bdofs)
@@ -151,11 +215,11 @@ def main():
     prob.vel[prob.bdofs] = timestep.tg_velocity(Xb, a1)
     b1 = prob.mats["Rw"] @ prob.vort + prob.mats["Krhs"] @ prob.vel
     xprev = spl.splu(K.tocsc()).solve(b)
-    print(f"{'preconditioner':22s} {'its cold':>9s} {'true rel. residual':>20s} {'its warm':>9s} {'s':>7s}")
+    print(f"{'preconditioner':26s} {'its cold':>9s} {'true rel. residual':>20s} {'its warm':>9s} {'s':>7s}")
     for name, M in rows:
         its, info, res, secs = run_cg(K, b, M, rtol)
         itw, infow, _, secw = run_cg(K, b1, M, rtol, x0=xprev)
-        print(f"{name:22s} {its:9d} {res:20.2e} {itw:9d} {secs + secw:7.1f}" +
+        print(f"{name:26s} {its:9d} {res:20.2e} {itw:9d} {secs + secw:7.1f}" +
               ("" if info == 0 and infow == 0 else f"  (info {info} {infow})"))
 
 
