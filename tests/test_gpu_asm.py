@@ -115,6 +115,33 @@ def test_asm_is_reproducible_and_composes_with_the_other_options():
         assert np.linalg.norm(x3.getArray() - r) <= 1e-7 * np.linalg.norm(r)
 
 
+@pytest.mark.parametrize("nelem,ngl,perturb", [([4, 4, 4], 3, 0.0), ([4, 4, 4], 4, 0.0), ([3, 3, 2], 3, 0.1),
+                                                ([8, 6], 4, 0.0)])
+def test_cg_two_level_asm_vs_direct(nelem, ngl, perturb):
+    """-pc_asm_coarse 5: same solution, no more iterations than the one-level preconditioner"""
+    from pynama_b200.petsc import Vec
+    mesh, dm, mats, want = _setup(nelem, ngl, perturb)
+    dim = len(nelem)
+    n = mesh.nnodes * dim
+    # a smooth right-hand side (what the time loop produces): the coarse space has something to do
+    X = 2 * np.pi * mesh.coords
+    xs = np.stack([np.sin(X[:, d]) * np.cos(X[:, (d + 1) % dim]) for d in range(dim)], 1).ravel()
+    Kref = want["K"].tocsr()
+    b = Kref @ xs
+    its = {}
+    for steps in (0, 5):
+        ksp = _ksp(mats["K"], "cg", "asm", 1e-11, setASMCoarse=(steps,))
+        x = Vec(n)
+        ksp.solve(Vec().createWithArray(b), x)
+        assert ksp.getConvergedReason() > 0, (steps, ksp.getConvergedReason(), ksp.getIterationNumber())
+        assert np.linalg.norm(x.getArray() - xs) <= 1e-8 * np.linalg.norm(xs), steps
+        its[steps] = ksp.getIterationNumber()
+        x2 = Vec(n)                                            # reproducible
+        ksp.solve(Vec().createWithArray(b), x2)
+        assert np.array_equal(x.getArray(), x2.getArray())
+    assert its[5] <= its[0] + 1, its
+
+
 @pytest.mark.parametrize("ktype", ["gmres", "bcgs"])
 def test_gmres_and_bcgs_with_asm(ktype):
     from pynama_b200.petsc import Vec
