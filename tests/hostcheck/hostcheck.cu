@@ -118,6 +118,36 @@ long long hc_asm_make_tiles(long long nel, const int* cls, long long nclass, int
   for (size_t i = 0; i < tcv.size(); ++i) tile_class[i] = tcv[i];
   return nt;
 }
+// coarse tables of the two-level preconditioner: returns nv; out arrays sized by the caller
+// (vert_node[nnodes], elem_verts[nel*ncorner], color[nnodes], adj_ptr[nnodes+1], adj[nnodes*125]); info = {ncolors}
+long long hc_asm_coarse_tables(int dim, int ngl, long long nel, long long nnodes, const int* elem_nodes, int* vert_node,
+                               int* elem_verts, int* color, long long* adj_ptr, int* adj, int* info, double* phi_out) {
+  ElemTables t;
+  if (build_elem_tables(dim, ngl, &t) != 0) return -1;
+  int corner_local[8];
+  std::vector<double> phi;
+  if (asm_coarse_phi(t, corner_local, &phi) != 0) return -2;
+  for (size_t i = 0; i < phi.size(); ++i) phi_out[i] = phi[i];
+  AsmCoarseTables T;
+  asm_coarse_tables(nel, nnodes, t.nn, t.ncorner, elem_nodes, corner_local, &T);
+  for (int64_t v = 0; v < T.nv; ++v) {
+    vert_node[v] = T.vert_node[(size_t)v];
+    color[v] = T.color[(size_t)v];
+  }
+  for (size_t i = 0; i < T.elem_verts.size(); ++i) elem_verts[i] = T.elem_verts[i];
+  for (int64_t v = 0; v <= T.nv; ++v) adj_ptr[v] = T.adj_ptr[(size_t)v];
+  for (size_t i = 0; i < T.adj.size(); ++i) adj[i] = T.adj[i];
+  info[0] = T.ncolors;
+  return T.nv;
+}
+void hc_asm_cheb_coefficients(int k, double lmin, double lmax, double* c1, double* c2) {
+  std::vector<double> a, b;
+  asm_cheb_coefficients(k, lmin, lmax, &a, &b);
+  for (int s = 0; s <= k; ++s) {
+    c1[s] = a[(size_t)s];
+    c2[s] = b[(size_t)s];
+  }
+}
 int hc_kle(int dim, int ngl, const double* X, double* K, double* Rw, double* Rd) {
   ElemTables t;
   if (build_elem_tables(dim, ngl, &t) != 0) return -1;

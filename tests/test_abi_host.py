@@ -241,3 +241,66 @@ def test_asm_tiles_host():
             assert len(m) > 0 and np.all(cls[m] == tile_class[t]) and np.all(np.diff(m) > 0)
             assert np.all(te_[t][len(m):] == -1)                    # padding only at the end
         assert np.all(np.diff(tile_class[:nt]) >= 0)
+
+
+def test_asm_coarse_tables_and_colouring_host():
+    """the coarse vertices, their adjacency and the distance-2 colouring the Galerkin probing relies
+    on (no vertex sees two vertices of one colour), on boxes and on an element-scrambled mesh"""
+    from pynama_b200.domain.box_mesh import BoxMesh
+    hc = _hc()
+    hc.hc_asm_coarse_tables.restype = ctypes.c_longlong
+    rng = np.random.default_rng(13)
+    for nelem, ngl, scramble in (([4, 3], 3, False), ([3, 3, 3], 3, False), ([5, 4, 3], 4, True), ([7, 6], 5, True)):
+        m = BoxMesh(nelem, [0.0] * len(nelem), [1.0] * len(nelem), ngl)
+        en = np.ascontiguousarray(m.elem_nodes, dtype=np.int32)
+        if scramble:                                     # element order of an unstructured mesh
+            en = np.ascontiguousarray(en[rng.permutation(len(en))])
+        dim, nel, nn = m.dim, len(en), en.shape[1]
+        ncorner = 2 ** dim
+        vert_node = np.zeros(m.nnodes, np.int32)
+        elem_verts = np.zeros(nel * ncorner, np.int32)
+        color = np.zeros(m.nnodes, np.int32)
+        adj_ptr = np.zeros(m.nnodes + 1, np.int64)
+        adj = np.zeros(m.nnodes * 125, np.int32)
+        info = np.zeros(1, np.int32)
+        phi = np.zeros(nn * ncorner)
+        vp = lambda a: a.ctypes.data_as(ctypes.c_void_p)          # noqa: E731
+        nv = hc.hc_asm_coarse_tables(dim, ngl, nel, m.nnodes, vp(en), vp(vert_node), vp(elem_verts), vp(color),
+                                     vp(adj_ptr), vp(adj), vp(info), vp(phi))
+        assert nv == np.prod(np.array(nelem) + 1)
+        vert_node, color, adj_ptr = vert_node[:nv], color[:nv], adj_ptr[:nv + 1]
+        assert np.all(np.diff(vert_node) > 0)
+        phi = phi.reshape(nn, ncorner)
+        np.testing.assert_allclose(phi.sum(1), 1.0, atol=1e-13)      # partition of unity
+        assert ((phi == 1.0).sum(0) == 1).all()                      # each corner function is 1 at its own node
+        # P reproduces the coordinates (multilinear interpolation from the corners is exact on boxes)
+        ev = elem_verts.reshape(nel, ncorner)
+        for e in (0, nel // 2, nel - 1):
+            np.testing.assert_allclose(phi @ m.coords[vert_node[ev[e]]], m.coords[en[e]], atol=1e-13)
+        nbrs = [set(adj[adj_ptr[v]:adj_ptr[v + 1]].tolist()) for v in range(nv)]
+        for v in range(nv):
+            assert v in nbrs[v] and all(v in nbrs[w] for w in nbrs[v])          # symmetric, reflexive
+            cols = color[sorted(nbrs[v])]
+            assert len(set(cols.tolist())) == len(cols)                          # the probing property
+        assert info[0] == color.max() + 1 and info[0] <= 5 ** dim
+
+
+def test_asm_chebyshev_coefficients_host():
+    """k steps with the coefficients reproduce the Chebyshev polynomial: on a diagonal matrix with
+    spectrum inside [lmin, lmax] the error polynomial stays below 2 / (T_k(sigma)) everywhere"""
+    hc = _hc()
+    lmin, lmax, k = 0.1, 1.1, 5
+    c1, c2 = np.zeros(k + 1), np.zeros(k + 1)
+    hc.hc_asm_cheb_coefficients(k, ctypes.c_double(lmin), ctypes.c_double(lmax), c1.ctypes.data_as(ctypes.c_void_p),
+                                c2.ctypes.data_as(ctypes.c_void_p))
+    lam = np.linspace(lmin, lmax, 101)
+    b = np.ones_like(lam)
+    x, r, d = np.zeros_like(lam), b.copy(), c2[0] * b
+    for s in range(1, k + 1):
+        x += d
+        r -= lam * d
+        d = c1[s] * d + c2[s] * r
+    theta, delta = 0.5 * (lmax + lmin), 0.5 * (lmax - lmin)
+    bound = 1.0 / np.cosh(k * np.arccosh(theta / delta))
+    assert np.abs(1.0 - lam * x).max() <= bound * (1 + 1e-10)        # residual polynomial r_k = T_k(..)/T_k(sigma)
+    assert np.allclose(r, 1.0 - lam * x)
