@@ -165,8 +165,9 @@ def main():
     rtol = 1e-10
     mesh = BoxMesh([nel] * 3, [0, 0, 0], [1, 1, 1], ngl)
     t0 = time.perf_counter()
+    lean = os.environ.get("STUDY_LEAN") == "1"      # large meshes: no LU anywhere, three rows, cold solves only
     prob = timestep.OracleProblem(3, ngl, mesh.corner_xyz, mesh.elem_nodes, mesh.coords, mesh.getBordersNodes(),
-                                  rho=0.5, mu=0.01, solver="direct")
+                                  rho=0.5, mu=0.01, solver="cg" if lean else "direct", pc="jacobi")
     K = prob.K
     d = 3
     # the right-hand side of the first solve of a run (kle_solver.py:33-37), zero initial guess
@@ -178,6 +179,26 @@ def main():
     print(f"# {nel}^3 elements, ngl={ngl}: {K.shape[0]} dofs, nnz {K.nnz}, set-up {time.perf_counter() - t0:.1f} s")
     bj = node_block_jacobi(K, d)
     rows = [("bjacobi", bj)]
+    if lean:
+        swb, ncls = element_schwarz(K, mesh.elem_nodes, d, True)
+        print(f"# schwarz-w: {ncls} distinct element blocks", flush=True)
+        rows.append(("schwarz-w", swb))
+        keepv = np.ones(K.shape[0])
+        keepv[prob.bdofs] = 0.0
+        Pk = (sp.diags(keepv) @ q1_prolongation(mesh, d, nel)).tocsr()
+        nzc = np.flatnonzero(np.asarray(abs(Pk).sum(0)).ravel() > 0)
+        Pk = Pk[:, nzc].tocsr()
+        Ac = (Pk.T @ K @ Pk).tocsr()
+        dinv = 1.0 / Ac.diagonal()
+        lmax = 1.1 * spl.eigsh(spl.LinearOperator(Ac.shape, matvec=lambda v: dinv * (Ac @ v)), k=1, which="LM",
+                               return_eigenvectors=False, tol=1e-3)[0]
+        ch = chebyshev_inverse(Ac, lambda v: dinv * v, 5, lmax)
+        rows.append(("schwarz-w+coarse~cheb5", lambda r: swb(r) + Pk @ ch(Pk.T @ r)))
+        print(f"{'preconditioner':26s} {'its cold':>9s} {'true rel. residual':>20s} {'s':>7s}", flush=True)
+        for name, M in rows:
+            its, info, res, secs = run_cg(K, b, M, rtol)
+            print(f"{name:26s} {its:9d} {res:20.2e} {secs:7.1f}" + ("" if info == 0 else f"  (info {info})"), flush=True)
+        return
     for weighted in (False, True):
         sw, ncls = element_schwarz(K, mesh.elem_nodes, d, weighted)
         name = "schwarz-w" if weighted else "schwarz"
