@@ -280,3 +280,23 @@ def test_emulated_coarse_level_matches_numpy(dim, nelem, ngl):
         r2 = rng.standard_normal(K.shape[0])
         y2, _, _, _, _ = run_emulated(mesh, K, B, r2, grid=1, coarse_steps=steps)
         assert abs(r2 @ z2 - r @ y2) < 1e-11 * abs(r2 @ z2)
+
+
+def test_oracle_asm_is_the_same_preconditioner_and_the_same_time_step():
+    """oracle/timestep.py's pc="asm" is the checker of the GPU tests: it must be the operator the
+    emulated kernels apply, and a time step through it must land on the direct-solve fields"""
+    mesh = BoxMesh([3, 3, 3], [0.0] * 3, [1.0] * 3, 3)
+    args = (3, 3, mesh.corner_xyz, mesh.elem_nodes, mesh.coords, mesh.getBordersNodes())
+    direct = timestep.OracleProblem(*args, rho=0.5, mu=0.01, solver="direct")
+    asm = timestep.OracleProblem(*args, rho=0.5, mu=0.01, solver="cg", pc="asm", rtol=1e-12)
+    bj = timestep.OracleProblem(*args, rho=0.5, mu=0.01, solver="cg", pc="bjacobi", rtol=1e-12)
+    r = np.random.default_rng(6).standard_normal(asm.K.shape[0])
+    z, _, _, _, _ = run_emulated(mesh, asm.K, 3, r, grid=2)
+    zo = asm._M.matvec(r)
+    assert np.abs(z - zo).max() < 1e-11 * np.abs(zo).max()
+    for p in (direct, asm, bj):
+        p.step(0.0, 2e-3)
+    for name in ("vort", "vel"):
+        want = getattr(direct, name)
+        assert np.abs(getattr(asm, name) - want).max() < 1e-9 * np.abs(want).max()
+    assert asm.iterations < 0.75 * bj.iterations, (asm.iterations, bj.iterations)
