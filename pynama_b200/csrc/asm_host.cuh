@@ -53,6 +53,50 @@ inline int64_t asm_group_by_hash(int64_t nel, const uint64_t* h /* [nel][2] */, 
   return (int64_t)rep->size();
 }
 
+// Row-partitioned runs: classes from the block hashes of the COMPLETE elements (all rows local),
+// the others by their signature (asm_signature_kernel).  hash/sig: [nel][2].  Returns the number of
+// classes, -1 when two complete elements agree in the signature but not in the block (the signature
+// does not determine the block on this mesh), -2 - e when incomplete element e has no complete twin.
+inline int64_t asm_group_partitioned(int64_t nel, const uint8_t* complete, const uint64_t* hash, const uint64_t* sig,
+                                     std::vector<int32_t>* cls, std::vector<int32_t>* rep) {
+  std::vector<int32_t> ids;
+  std::vector<uint64_t> hc;
+  for (int64_t e = 0; e < nel; ++e)
+    if (complete[e]) {
+      ids.push_back((int32_t)e);
+      hc.push_back(hash[2 * e]);
+      hc.push_back(hash[2 * e + 1]);
+    }
+  std::vector<int32_t> cc, rc;
+  const int64_t nclass = asm_group_by_hash((int64_t)ids.size(), hc.data(), &cc, &rc);
+  cls->assign((size_t)nel, -1);
+  rep->assign((size_t)nclass, 0);
+  for (int64_t k = 0; k < nclass; ++k) (*rep)[(size_t)k] = ids[(size_t)rc[(size_t)k]];
+  struct Key {
+    uint64_t a, b;
+    bool operator==(const Key& o) const { return a == o.a && b == o.b; }
+  };
+  struct KeyHash {
+    size_t operator()(const Key& k) const { return (size_t)(k.a ^ (k.b * 0x9E3779B97F4A7C15ull)); }
+  };
+  std::unordered_map<Key, int32_t, KeyHash> by_sig;
+  for (size_t i = 0; i < ids.size(); ++i) {
+    const int64_t e = ids[i];
+    (*cls)[(size_t)e] = cc[i];
+    const Key k{sig[2 * e], sig[2 * e + 1]};
+    auto it = by_sig.find(k);
+    if (it == by_sig.end()) by_sig.emplace(k, cc[i]);
+    else if (it->second != cc[i]) return -1;
+  }
+  for (int64_t e = 0; e < nel; ++e)
+    if (!complete[e]) {
+      auto it = by_sig.find(Key{sig[2 * e], sig[2 * e + 1]});
+      if (it == by_sig.end()) return -2 - e;
+      (*cls)[(size_t)e] = it->second;
+    }
+  return nclass;
+}
+
 // In-place inverse of the dense n x n matrix a (row-major) by Gauss-Jordan elimination with
 // partial pivoting.  Returns 0, or -1 when a pivot vanishes (singular to working precision).
 inline int asm_dense_inverse(int n, double* a) {

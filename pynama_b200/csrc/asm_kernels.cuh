@@ -83,12 +83,43 @@ asm_blocks_kernel(int64_t nlist, const int32_t* __restrict__ list, const int32_t
   }
 }
 
-__global__ void asm_weights_kernel(int64_t nnodes, const int64_t* __restrict__ n2e_ptr,
+// valence[n] = elements of the local mesh holding node n (a row-partitioned run then refreshes
+// the ghost entries from the owners, whose counts are complete)
+__global__ void asm_valence_kernel(int64_t nnodes, const int64_t* __restrict__ n2e_ptr,
+                                   double* __restrict__ valence) {
+  for (int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; n < nnodes;
+       n += (int64_t)gridDim.x * blockDim.x)
+    valence[n] = (double)(n2e_ptr[n + 1] - n2e_ptr[n]);
+}
+
+__global__ void asm_weights_kernel(int64_t nnodes, const double* __restrict__ valence,
                                    double* __restrict__ wnode) {
   for (int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; n < nnodes;
        n += (int64_t)gridDim.x * blockDim.x) {
-    const double m = (double)(n2e_ptr[n + 1] - n2e_ptr[n]);
+    const double m = valence[n];
     wnode[n] = m > 0.0 ? 1.0 / sqrt(m) : 0.0;
+  }
+}
+
+// Signature of an element on a mesh whose cells are all congruent: its assembled block is then
+// fixed by the dof classes and the global valences of its nodes (which neighbours exist, which
+// rows and columns the boundary conditions replaced).  Row-partitioned runs use it to give an
+// element whose block is incomplete here (ghost rows live on their owners) the inverse of a
+// complete local element with the same signature.  One thread per element.
+__global__ void asm_signature_kernel(int64_t nel, const int32_t* __restrict__ elem_nodes, int nn,
+                                     const uint8_t* __restrict__ nodecls, const double* __restrict__ valence,
+                                     unsigned long long* __restrict__ sig) {
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < nel; e += (int64_t)gridDim.x * blockDim.x) {
+    unsigned long long h0 = 0ull, h1 = 0ull;
+    for (int a = 0; a < nn; ++a) {
+      const int64_t n = elem_nodes[e * nn + a];
+      const unsigned long long key =
+          (unsigned long long)(nodecls ? nodecls[n] : 0) | ((unsigned long long)(long long)valence[n] << 8);
+      h0 += asm_hash_entry(key, (uint64_t)a, 0);
+      h1 += asm_hash_entry(key, (uint64_t)a, 1);
+    }
+    sig[2 * e] = h0;
+    sig[2 * e + 1] = h1;
   }
 }
 

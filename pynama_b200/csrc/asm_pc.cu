@@ -17,6 +17,7 @@
 #include "asm_pc.cuh"
 #include "asm_kernels.cuh"
 #include "spmv.cuh"
+#include "comm.cuh"
 
 namespace pyn {
 
@@ -28,12 +29,38 @@ static int asm_setup_impl(pyn_ctx* ctx, pyn_mat* A, AsmPc* pc) {
   pc->mesh = mesh;
   pc->B = B;
   pc->ld = ld;
-  // 1. hash every element block
-  DevBuf<unsigned long long> hash;
+  const bool dist = A->halo != nullptr && ctx->nranks > 1;
+  pc->halo = dist ? A->halo : nullptr;
+  pc->n_own = dist ? A->halo->n_own : mesh->nnodes;
+  // 0. valences (global ones: a partitioned run takes the ghost nodes' counts from their owners)
+  DevBuf<double> valence;
+  PYN_CHECK(valence.alloc(ctx, mesh->nnodes));
+  asm_valence_kernel<<<grid_for(ctx, mesh->nnodes, 256), 256, 0, ctx->stream>>>(mesh->nnodes, mesh->n2e_ptr.p,
+                                                                                valence.p);
+  PYN_LAUNCHED(ctx);
+  if (dist) PYN_CHECK(halo_exchange(A->halo, valence.p, 1));
+  // 1. hash the block of every complete element (all its rows are local)
+  std::vector<uint8_t> complete((size_t)nel, 1);
+  std::vector<int32_t> clist;
+  if (dist) {
+    std::vector<int32_t> en((size_t)(nel * nn));
+    PYN_CHECK(mesh->elem_nodes.download(en.data(), nel * nn));
+    for (int64_t e = 0; e < nel; ++e)
+      for (int a = 0; a < nn; ++a)
+        if (en[(size_t)(e * nn + a)] >= pc->n_own) complete[(size_t)e] = 0;
+  }
+  for (int64_t e = 0; e < nel; ++e)
+    if (complete[(size_t)e]) clist.push_back((int32_t)e);
+  pc->ncomplete = (int64_t)clist.size();
+  PYN_REQUIRE(pc->ncomplete > 0, "pc asm: no element of this rank has all its rows here");
+  DevBuf<int32_t> dlist;
+  PYN_CHECK(dlist.alloc(ctx, pc->ncomplete));
+  PYN_CHECK(dlist.upload(clist.data(), pc->ncomplete));
+  DevBuf<unsigned long long> hash, sig;
   PYN_CHECK(hash.alloc(ctx, 2 * nel));
   PYN_CHECK(hash.zero());
-  const int grid = grid_for(ctx, nel * nn * 32, 256);
-  asm_blocks_kernel<B, 0><<<grid, 256, 0, ctx->stream>>>(nel, nullptr, mesh->elem_nodes.p, nn, A->rowptr.p,
+  const int grid = grid_for(ctx, pc->ncomplete * nn * 32, 256);
+  asm_blocks_kernel<B, 0><<<grid, 256, 0, ctx->stream>>>(pc->ncomplete, dlist.p, mesh->elem_nodes.p, nn, A->rowptr.p,
                                                          A->colidx.p, A->val.p, hash.p, nullptr);
   PYN_LAUNCHED(ctx);
   std::vector<unsigned long long> hh((size_t)(2 * nel));
@@ -41,7 +68,25 @@ static int asm_setup_impl(pyn_ctx* ctx, pyn_mat* A, AsmPc* pc) {
   // 2. classes of equal blocks, their representatives
   std::vector<int32_t> cls, rep;
   static_assert(sizeof(unsigned long long) == sizeof(uint64_t), "hash word");
-  pc->nclass = asm_group_by_hash(nel, reinterpret_cast<const uint64_t*>(hh.data()), &cls, &rep);
+  if (pc->ncomplete == nel) {
+    pc->nclass = asm_group_by_hash(nel, reinterpret_cast<const uint64_t*>(hh.data()), &cls, &rep);
+  } else {
+    // elements with ghost nodes: class of a complete element with the same signature
+    PYN_REQUIRE(mesh->nclass == 1, "pc asm on a row-partitioned operator needs a mesh of congruent cells "
+                                   "(one congruence class; this mesh has %lld); use bjacobi", (long long)mesh->nclass);
+    PYN_CHECK(sig.alloc(ctx, 2 * nel));
+    asm_signature_kernel<<<grid_for(ctx, nel, 256), 256, 0, ctx->stream>>>(
+        nel, mesh->elem_nodes.p, nn, mesh->has_cls ? mesh->nodecls.p : nullptr, valence.p, sig.p);
+    PYN_LAUNCHED(ctx);
+    std::vector<unsigned long long> ss((size_t)(2 * nel));
+    PYN_CHECK(sig.download(ss.data(), 2 * nel));
+    pc->nclass = asm_group_partitioned(nel, complete.data(), reinterpret_cast<const uint64_t*>(hh.data()),
+                                       reinterpret_cast<const uint64_t*>(ss.data()), &cls, &rep);
+    PYN_REQUIRE(pc->nclass != -1, "pc asm: element signatures do not determine the element blocks on this mesh");
+    PYN_REQUIRE(pc->nclass >= 0, "pc asm: element %lld touches another rank's rows and no element of this rank "
+                                 "with all rows local has the same signature; use fewer ranks or bjacobi",
+                (long long)(-2 - pc->nclass));
+  }
   const int64_t inv_bytes = pc->nclass * (int64_t)ld * ld * (int64_t)sizeof(double);
   PYN_REQUIRE(inv_bytes <= kAsmMaxInverseBytes,
               "pc asm: %lld distinct element blocks of %d^2 (%lld MB of inverses): the elements of this mesh "
@@ -72,7 +117,7 @@ static int asm_setup_impl(pyn_ctx* ctx, pyn_mat* A, AsmPc* pc) {
   PYN_CHECK(pc->tile_class.upload(tile_class.data(), pc->ntiles));
   // 5. weights, element-local result buffer
   PYN_CHECK(pc->wnode.alloc(ctx, mesh->nnodes));
-  asm_weights_kernel<<<grid_for(ctx, mesh->nnodes, 256), 256, 0, ctx->stream>>>(mesh->nnodes, mesh->n2e_ptr.p,
+  asm_weights_kernel<<<grid_for(ctx, mesh->nnodes, 256), 256, 0, ctx->stream>>>(mesh->nnodes, valence.p,
                                                                                 pc->wnode.p);
   PYN_LAUNCHED(ctx);
   PYN_CHECK(pc->ybuf.alloc(ctx, nel * ld));
@@ -185,9 +230,10 @@ static int asm_coarse_setup(pyn_ctx* ctx, pyn_mat* A, AsmPc* pc) {
 int asm_setup(pyn_ctx* ctx, pyn_mat* A, int coarse_steps, AsmPc** out) {
   *out = nullptr;
   PYN_REQUIRE(A->mesh && !A->free_pattern, "pc asm needs an operator assembled from a mesh");
+  const bool dist = A->halo && ctx->nranks > 1;
   PYN_REQUIRE(A->br == A->bc && A->nbrows == A->mesh->nnodes, "pc asm: operator is not square over the mesh nodes");
-  if (A->halo && ctx->nranks > 1) {
-    set_error("pc asm is not available on row-partitioned operators yet (single GPU only); use bjacobi");
+  if (dist && coarse_steps > 0) {
+    set_error("pc asm: the coarse level (-pc_asm_coarse) is not available on row-partitioned operators yet");
     return PYN_E_UNSUPPORTED;
   }
   AsmPc* pc = new AsmPc();
@@ -212,8 +258,9 @@ int asm_setup(pyn_ctx* ctx, pyn_mat* A, int coarse_steps, AsmPc** out) {
 }
 
 template <int B>
-static int asm_apply_impl(pyn_ctx* ctx, AsmPc* pc, const double* r, double* z, double* dots, const double* done) {
+static int asm_apply_impl(pyn_ctx* ctx, AsmPc* pc, double* r, double* z, double* dots, const double* done) {
   pyn_mesh* mesh = pc->mesh;
+  if (pc->halo) PYN_CHECK(halo_exchange(pc->halo, r, B));     // the elements of the halo layer read ghost entries
   const int64_t cap = (int64_t)ctx->num_sms * 2;
   const int gridm = (int)(pc->ntiles < cap ? pc->ntiles : cap);
   asm_mult_kernel<B><<<gridm > 0 ? gridm : 1, 256, pc->smem, ctx->stream>>>(
@@ -235,14 +282,14 @@ static int asm_apply_impl(pyn_ctx* ctx, AsmPc* pc, const double* r, double* z, d
     }
     xc = pc->xc.p;
   }
-  asm_sum_kernel<B><<<grid_for(ctx, mesh->nnodes, 256), 256, 0, ctx->stream>>>(
-      mesh->nnodes, mesh->n2e_ptr.p, mesh->n2e.p, pc->ybuf.p, pc->ld, r, z, ctx->red_partials, ctx->red_ticket,
+  asm_sum_kernel<B><<<grid_for(ctx, pc->n_own, 256), 256, 0, ctx->stream>>>(
+      pc->n_own, mesh->n2e_ptr.p, mesh->n2e.p, pc->ybuf.p, pc->ld, r, z, ctx->red_partials, ctx->red_ticket,
       dots, done, asm_prolong_args<B>(pc, xc));
   PYN_LAUNCHED(ctx);
   return PYN_OK;
 }
 
-int asm_apply(pyn_ctx* ctx, AsmPc* pc, const double* r, double* z, double* dots, const double* done) {
+int asm_apply(pyn_ctx* ctx, AsmPc* pc, double* r, double* z, double* dots, const double* done) {
   if (pc->B == 3) return asm_apply_impl<3>(ctx, pc, r, z, dots, done);
   return asm_apply_impl<2>(ctx, pc, r, z, dots, done);
 }

@@ -16,6 +16,11 @@ struct AsmPc {
   DevBuf<int32_t> tile_elems;      // [ntiles][kAsmTile (asm_kernels.cuh)] elements of one class, -1 padded
   DevBuf<int32_t> tile_class;      // [ntiles]
   DevBuf<double> wnode;            // [nnodes]
+  // row-partitioned operator: the apply refreshes the ghost entries of r, multiplies over all local
+  // elements (block + halo layer) and sums into the owned nodes only -- no reverse exchange
+  pyn_halo* halo = nullptr;
+  int64_t n_own = 0;               // nodes summed into (all of them on one GPU)
+  int64_t ncomplete = 0;           // elements whose block could be read here (all rows local)
   DevBuf<double> ybuf;             // [nel][ld] element-local results of the last apply
   size_t smem = 0;
   // second level (coarse_steps > 0): Q1 space on the element corners, Galerkin operator
@@ -43,6 +48,8 @@ constexpr int64_t kAsmMaxInverseBytes = (int64_t)1 << 30;
 int asm_setup(pyn_ctx* ctx, pyn_mat* A, int coarse_steps, AsmPc** out);
 // z = M^-1 r.  dots != NULL: dots[0] = r.z, dots[1] = z.z (device).  done != NULL: a device flag;
 // when non-zero the apply is skipped (iterations launched after convergence).
-int asm_apply(pyn_ctx* ctx, AsmPc* pc, const double* r, double* z, double* dots, const double* done);
+// Row-partitioned: r's ghost entries are refreshed in place (they are copies of the owners' values
+// by definition), dots are this rank's partial sums.
+int asm_apply(pyn_ctx* ctx, AsmPc* pc, double* r, double* z, double* dots, const double* done);
 
 }  // namespace pyn

@@ -591,7 +591,8 @@ static int ksp_setup_pc(pyn_ksp* k) {
 template <int B>
 static int ksp_pc_dots(pyn_ksp* k, const double* r, double* z, int64_t nn, int gridn, double* out) {
   pyn_ctx* ctx = k->ctx;
-  if (k->pc == PYN_PC_ASM) return asm_apply(ctx, k->asmpc, r, z, out, nullptr);
+  // (asm refreshes r's ghost entries in place on a row-partitioned operator: copies of the owners' values)
+  if (k->pc == PYN_PC_ASM) return asm_apply(ctx, k->asmpc, const_cast<double*>(r), z, out, nullptr);
   pc_apply_dots_kernel<B><<<gridn, 256, 0, ctx->stream>>>(k->pc, k->pcd.p, r, z, nn, ctx->red_partials,
                                                           ctx->red_ticket, out);
   PYN_LAUNCHED(ctx);
@@ -602,7 +603,9 @@ template <int B>
 static int ksp_solve_cg(pyn_ksp* k, const double* b, double* x, int* its, int* reason, double* rnorm) {
   pyn_ctx* ctx = k->ctx;
   const int dist = k->A->halo != nullptr && ctx->nranks > 1;
-  const bool p2p = dist && p2p_enabled(ctx);     // fused peer-memory allreduce instead of NCCL
+  // fused peer-memory allreduce instead of NCCL; not under the Schwarz preconditioner, whose apply
+  // sits between the vector update and the reduction of r.z
+  const bool p2p = dist && p2p_enabled(ctx) && k->pc != PYN_PC_ASM;
   P2PRed red_off;
   memset(&red_off, 0, sizeof(red_off));
   red_off.nranks = 1;
@@ -695,13 +698,10 @@ static int ksp_solve_cg(pyn_ksp* k, const double* b, double* x, int* its, int* r
                                                           dist || asmpc ? 1 : 0, red);
       prof_end(ctx);
       PYN_LAUNCHED(ctx);
-      if (asmpc) {                    // z = M^-1 r, r.z and z.z into the partial slots, bookkeeping
-        PYN_CHECK(asm_apply(ctx, k->asmpc, k->r.p, k->z.p, S + S_LRZ, S + S_DONE));
-        cg_scalars_kernel<<<1, 1, 0, ctx->stream>>>(S, parity, k->maxit);
-        PYN_LAUNCHED(ctx);
-      }
-      if (dist && !p2p) {
-        PYN_CHECK(comm_allreduce_sum(ctx, S + S_LRZ, 2));
+      // z = M^-1 r with r.z and z.z (this rank's part) into the partial slots
+      if (asmpc) PYN_CHECK(asm_apply(ctx, k->asmpc, k->r.p, k->z.p, S + S_LRZ, S + S_DONE));
+      if (dist && !p2p) PYN_CHECK(comm_allreduce_sum(ctx, S + S_LRZ, 2));
+      if (asmpc || (dist && !p2p)) {
         cg_scalars_kernel<<<1, 1, 0, ctx->stream>>>(S, parity, k->maxit);
         PYN_LAUNCHED(ctx);
       }
@@ -813,7 +813,7 @@ struct KrylovOps {
     return pc(k->w.p, z);
   }
   int pc(const double* r, double* z) {
-    if (k->pc == PYN_PC_ASM) return asm_apply(ctx, k->asmpc, r, z, nullptr, nullptr);
+    if (k->pc == PYN_PC_ASM) return asm_apply(ctx, k->asmpc, const_cast<double*>(r), z, nullptr, nullptr);
     pc_apply_kernel<B><<<gridn, 256, 0, ctx->stream>>>(k->pc, k->pcd.p, r, z, nn);
     PYN_LAUNCHED(ctx);
     return PYN_OK;
@@ -1027,10 +1027,6 @@ int pyn_ksp_create(pyn_ctx* ctx, pyn_mat* a, int type, int pc, pyn_ksp** out) {
   if (pc == PYN_PC_ASM) {
     PYN_REQUIRE(a->mesh && !a->free_pattern && (a->br == 2 || a->br == 3),
                 "pc asm needs a 2-D or 3-D operator assembled from a mesh");
-    if (a->halo && ctx->nranks > 1) {
-      set_error("pc asm is not available on row-partitioned operators yet (single GPU only); use bjacobi");
-      return PYN_E_UNSUPPORTED;
-    }
   }
   if (type != PYN_KSP_CG && type != PYN_KSP_GMRES && type != PYN_KSP_BCGS) {
     set_error("KSP type %d is not available (cg, gmres, bcgs)", type);
