@@ -55,8 +55,10 @@ inline int64_t asm_group_by_hash(int64_t nel, const uint64_t* h /* [nel][2] */, 
 
 // Row-partitioned runs: classes from the block hashes of the COMPLETE elements (all rows local),
 // the others by their signature (asm_signature_kernel).  hash/sig: [nel][2].  Returns the number of
-// classes, -1 when two complete elements agree in the signature but not in the block (the signature
-// does not determine the block on this mesh), -2 - e when incomplete element e has no complete twin.
+// classes, or -2 - e when incomplete element e has no complete twin.  Complete elements with one
+// signature may still fall into several classes (blocks that differ in the last bits, or a mesh on
+// which the signature says too little): the lowest such element lends its inverse, which keeps the
+// preconditioner symmetric positive definite whatever the blocks are.
 inline int64_t asm_group_partitioned(int64_t nel, const uint8_t* complete, const uint64_t* hash, const uint64_t* sig,
                                      std::vector<int32_t>* cls, std::vector<int32_t>* rep) {
   std::vector<int32_t> ids;
@@ -86,7 +88,6 @@ inline int64_t asm_group_partitioned(int64_t nel, const uint8_t* complete, const
     const Key k{sig[2 * e], sig[2 * e + 1]};
     auto it = by_sig.find(k);
     if (it == by_sig.end()) by_sig.emplace(k, cc[i]);
-    else if (it->second != cc[i]) return -1;
   }
   for (int64_t e = 0; e < nel; ++e)
     if (!complete[e]) {

@@ -82,7 +82,6 @@ static int asm_setup_impl(pyn_ctx* ctx, pyn_mat* A, AsmPc* pc) {
     PYN_CHECK(sig.download(ss.data(), 2 * nel));
     pc->nclass = asm_group_partitioned(nel, complete.data(), reinterpret_cast<const uint64_t*>(hh.data()),
                                        reinterpret_cast<const uint64_t*>(ss.data()), &cls, &rep);
-    PYN_REQUIRE(pc->nclass != -1, "pc asm: element signatures do not determine the element blocks on this mesh");
     PYN_REQUIRE(pc->nclass >= 0, "pc asm: element %lld touches another rank's rows and no element of this rank "
                                  "with all rows local has the same signature; use fewer ranks or bjacobi",
                 (long long)(-2 - pc->nclass));

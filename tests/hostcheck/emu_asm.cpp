@@ -15,15 +15,40 @@ template <int B>
 int run(int nn, long long nel, long long nnodes, const int32_t* elem_nodes, const int64_t* rowptr,
         const int32_t* colidx, const double* val, const int64_t* n2e_ptr, const int2* n2e, const double* r,
         int grid, int napply, double* z, double* dots, long long* nclass_out, int32_t* cls_out, double* inv_out,
-        int dim, int ngl, int coarse_steps, long long* coarse_info, double* ac_dense) {
+        int dim, int ngl, int coarse_steps, long long* coarse_info, double* ac_dense, long long n_own,
+        const double* valence_global, const uint8_t* nodecls) {
   const int ld = nn * B;
   // set-up, as asm_setup_impl
+  std::vector<double> valence((size_t)nnodes, -1.0);
+  cuda_emu::launch(grid, 256, 0, [&]() { asm_valence_kernel(nnodes, n2e_ptr, valence.data()); });
+  if (valence_global)                           // stands for halo_exchange(valence): ghost counts from the owners
+    for (long long n = n_own; n < nnodes; ++n) valence[(size_t)n] = valence_global[n];
+  std::vector<uint8_t> complete((size_t)nel, 1);
+  std::vector<int32_t> clist;
+  for (long long e = 0; e < nel; ++e) {
+    for (int a = 0; a < nn; ++a)
+      if (elem_nodes[e * nn + a] >= n_own) complete[(size_t)e] = 0;
+    if (complete[(size_t)e]) clist.push_back((int32_t)e);
+  }
+  if (clist.empty()) return -8;
   std::vector<unsigned long long> hash((size_t)(2 * nel), 0ull);
   cuda_emu::launch(grid, 256, 0, [&]() {
-    asm_blocks_kernel<B, 0>(nel, nullptr, elem_nodes, nn, rowptr, colidx, val, hash.data(), nullptr);
+    asm_blocks_kernel<B, 0>((int64_t)clist.size(), clist.data(), elem_nodes, nn, rowptr, colidx, val, hash.data(),
+                            nullptr);
   });
   std::vector<int32_t> cls, rep;
-  const int64_t nclass = asm_group_by_hash(nel, reinterpret_cast<const uint64_t*>(hash.data()), &cls, &rep);
+  int64_t nclass;
+  if ((long long)clist.size() == nel) {
+    nclass = asm_group_by_hash(nel, reinterpret_cast<const uint64_t*>(hash.data()), &cls, &rep);
+  } else {
+    std::vector<unsigned long long> sig((size_t)(2 * nel), 0ull);
+    cuda_emu::launch(grid, 256, 0, [&]() {
+      asm_signature_kernel(nel, elem_nodes, nn, nodecls, valence.data(), sig.data());
+    });
+    nclass = asm_group_partitioned(nel, complete.data(), reinterpret_cast<const uint64_t*>(hash.data()),
+                                   reinterpret_cast<const uint64_t*>(sig.data()), &cls, &rep);
+    if (nclass < 0) return -10;
+  }
   *nclass_out = nclass;
   for (long long e = 0; e < nel; ++e) cls_out[e] = cls[(size_t)e];
   std::vector<double> inv((size_t)(nclass * (int64_t)ld * ld), -777.0);
@@ -39,7 +64,7 @@ int run(int nn, long long nel, long long nnodes, const int32_t* elem_nodes, cons
   std::vector<int32_t> tile_elems, tile_class;
   const int64_t ntiles = asm_make_tiles(nel, cls.data(), nclass, kAsmTile, &tile_elems, &tile_class);
   std::vector<double> wnode((size_t)nnodes, -1.0);
-  cuda_emu::launch(grid, 256, 0, [&]() { asm_weights_kernel(nnodes, n2e_ptr, wnode.data()); });
+  cuda_emu::launch(grid, 256, 0, [&]() { asm_weights_kernel(nnodes, valence.data(), wnode.data()); });
   std::vector<double> ybuf((size_t)(nel * ld), -777.0);
   const size_t smem = sizeof(double) * ((size_t)ld * kAsmTile + (size_t)kAsmKC * kAsmRP);
   // second level, as asm_coarse_setup (the product with K: plain loops over the row-plane BSR)
@@ -136,23 +161,23 @@ int run(int nn, long long nel, long long nnodes, const int32_t* elem_nodes, cons
       cp.xc = xc.data();
     }
     cuda_emu::launch(grid, 256, 0, [&]() {
-      asm_sum_kernel<B>(nnodes, n2e_ptr, n2e, ybuf.data(), ld, r, z, partials.data(), &ticket, dots, &done0, cp);
+      asm_sum_kernel<B>(n_own, n2e_ptr, n2e, ybuf.data(), ld, r, z, partials.data(), &ticket, dots, &done0, cp);
     });
     if (ticket != 0) return -3;                 // the last CTA re-arms the ticket
   }
   // a raised `done` flag must leave z and the dots alone
   const double done1 = 1.0;
-  std::vector<double> zkeep(z, z + nnodes * B);
+  std::vector<double> zkeep(z, z + n_own * B);
   double dkeep[2] = {dots[0], dots[1]};
   cuda_emu::launch(grid, 256, smem, [&]() {
     asm_mult_kernel<B>(ntiles, tile_elems.data(), tile_class.data(), elem_nodes, nn, inv.data(), wnode.data(), z,
                        ybuf.data(), &done1);
   });
   cuda_emu::launch(grid, 256, 0, [&]() {
-    asm_sum_kernel<B>(nnodes, n2e_ptr, n2e, ybuf.data(), ld, r, z, partials.data(), &ticket, dots, &done1,
+    asm_sum_kernel<B>(n_own, n2e_ptr, n2e, ybuf.data(), ld, r, z, partials.data(), &ticket, dots, &done1,
                       AsmProlong{nullptr, nullptr, nullptr, nullptr, 0});
   });
-  for (long long i = 0; i < nnodes * B; ++i)
+  for (long long i = 0; i < n_own * B; ++i)
     if (z[i] != zkeep[(size_t)i]) return -4;
   if (dots[0] != dkeep[0] || dots[1] != dkeep[1]) return -4;
   return 0;
@@ -162,23 +187,27 @@ int run(int nn, long long nel, long long nnodes, const int32_t* elem_nodes, cons
 
 extern "C" {
 // n2e: (element, local index) pairs, int32 x 2 per entry.  inv_out: NULL or [nclass][ld][ld].
+// n_own < nnodes: one rank of a row-partitioned run (nodes [n_own, nnodes) are ghosts whose rows are not
+// here; valence_global[nnodes] gives their global valences, nodecls[nnodes] the packed dof classes; r holds
+// refreshed ghost entries; z and the dots cover the owned nodes).
 // coarse_steps > 0: two-level; coarse_info[2] = {coarse vertices, colours}; ac_dense: NULL or the
 // probed coarse operator as a dense [nv*B][nv*B] (zero-initialised by the caller).
 // Returns 0, or < 0 on a failed internal check.
 int emu_asm_apply(int B, int nn, long long nel, long long nnodes, const int* elem_nodes, const long long* rowptr,
                   const int* colidx, const double* val, const long long* n2e_ptr, const int* n2e, const double* r,
                   int grid, int napply, double* z, double* dots, long long* nclass_out, int* cls_out,
-                  double* inv_out, int dim, int ngl, int coarse_steps, long long* coarse_info, double* ac_dense) {
+                  double* inv_out, int dim, int ngl, int coarse_steps, long long* coarse_info, double* ac_dense,
+                  long long n_own, const double* valence_global, const unsigned char* nodecls) {
   static_assert(sizeof(long long) == sizeof(int64_t) && sizeof(int2) == 2 * sizeof(int), "ABI");
   const int64_t* rp = reinterpret_cast<const int64_t*>(rowptr);
   const int64_t* np = reinterpret_cast<const int64_t*>(n2e_ptr);
   const int2* ne = reinterpret_cast<const int2*>(n2e);
   if (B == 3)
     return run<3>(nn, nel, nnodes, elem_nodes, rp, colidx, val, np, ne, r, grid, napply, z, dots, nclass_out, cls_out,
-                  inv_out, dim, ngl, coarse_steps, coarse_info, ac_dense);
+                  inv_out, dim, ngl, coarse_steps, coarse_info, ac_dense, n_own, valence_global, nodecls);
   if (B == 2)
     return run<2>(nn, nel, nnodes, elem_nodes, rp, colidx, val, np, ne, r, grid, napply, z, dots, nclass_out, cls_out,
-                  inv_out, dim, ngl, coarse_steps, coarse_info, ac_dense);
+                  inv_out, dim, ngl, coarse_steps, coarse_info, ac_dense, n_own, valence_global, nodecls);
   return -1;
 }
 }
