@@ -268,8 +268,9 @@ int pyn_vec_device_ptr(pyn_vec* v, void** ptr);
 #define PYN_PC_BJACOBI 2 /* node-block (br x br) Jacobi */
 /* -pc_type asm: additive Schwarz with one subdomain per spectral element,
  * sum_e R_e^T W inv(R_e K R_e^T) W R_e with W = 1/sqrt(elements sharing the node); elements with
- * bitwise equal blocks share one inverse.  Operators assembled from a mesh, one GPU, 2-D or 3-D;
- * refused (error) when the distinct inverses would exceed 1 GiB.  CG drops the single-reduction
+ * bitwise equal blocks share one inverse.  Operators assembled from a mesh, 2-D or 3-D; row-partitioned
+ * operators on meshes of congruent cells (one level); refused (error) when the distinct inverses
+ * would exceed 1 GiB.  CG drops the single-reduction
  * variant under this preconditioner. */
 #define PYN_PC_ASM 3
 int pyn_ksp_create(pyn_ctx* ctx, pyn_mat* a, int type, int pc, pyn_ksp** out);

@@ -201,3 +201,21 @@ def test_time_steps_with_asm_match_the_oracle(case, nelem, ngl):
         assert rel(fem.solverKLE.getSolution().getArray(), orc.vel) < 1e-8
     finally:
         o.setValue("pc_type", "bjacobi")
+
+
+@pytest.mark.parametrize("nproc,ksp", [(2, "cg"), (2, "gmres"), (4, "cg"), (8, "cg")])
+def test_partitioned_run_with_asm(nproc, ksp):
+    """row-partitioned operator: ghost refresh of r, all local elements, owned nodes summed, blocks of
+    elements with ghost nodes borrowed by signature; fields after the steps against the oracle
+    (tests/dist_check.py).  Blocks are 3 elements thick so that every class has a complete twin."""
+    import subprocess
+    import sys
+    from tests.test_gpu_dist import SCRIPT, _ngpus
+    if _ngpus() < nproc:
+        pytest.skip(f"needs {nproc} GPUs")
+    env = dict(os.environ, DIST_OPTS="pc_type=asm", DIST_NELEM="6,6,6", DIST_KSP=ksp)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}",
+           "--master-addr", "127.0.0.1", "--master-port", str(29570 + nproc), SCRIPT]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=900, env=env)
+    assert r.returncode == 0, r.stdout[-3000:] + "\n" + r.stderr[-3000:]
+    assert "OK" in r.stdout

@@ -2,7 +2,10 @@
 # First GPU call of the next round: confirm -pc_type asm (written and CPU-emulated in round 1 after the
 # GPU minutes ran out) and measure it on the bench workload.  Run as
 #   gpurun --timeout 1500 -- 'bash tools/r2_first_gpu_call.sh'
-# Everything lands in gpurun_out/r2_asm/.
+# Everything lands in gpurun_out/r2_asm/.  Then, on 2 GPUs (gpurun --gpus 2): the same pytest line runs
+# test_partitioned_run_with_asm, and
+#   python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29611 \
+#       bench.py --gpus 2 --steps 3 --warmup 3 --pc asm
 set -u
 out=gpurun_out/r2_asm
 mkdir -p "$out"
