@@ -334,7 +334,8 @@ def test_emulated_partitioned_apply_matches_the_global_one(dim, nelem, ngl, size
         pack |= (cls[:, i].astype(np.uint8) & 3) << (2 * i)
     K = K.tocsr()
     total_rz = 0.0
-    for rank in range(size):
+    ranks = range(size) if size <= 4 else (0, 3, size - 1)       # (8 ranks: a corner, a mixed and the last block)
+    for rank in ranks:
         part = Partition(mesh, rank, size)
         l2g = part.l2g
         gd = (l2g[:, None] * B + np.arange(B)[None, :]).ravel()            # local dof -> global dof
@@ -349,7 +350,8 @@ def test_emulated_partitioned_apply_matches_the_global_one(dim, nelem, ngl, size
         # inverse is the twin's, not the element's own: equal to rounding times the block's condition)
         assert np.abs(z[:part.n_own * B] - zref[own]).max() < 1e-9 * np.abs(zref).max(), rank
         total_rz += dots[0]
-    assert abs(total_rz - r @ zref) < 1e-9 * abs(r @ zref)                  # what the allreduce sums
+    if len(ranks) == size:
+        assert abs(total_rz - r @ zref) < 1e-9 * abs(r @ zref)              # what the allreduce sums
 
 
 def test_emulated_partitioned_setup_refuses_blocks_without_a_twin():
