@@ -21,6 +21,22 @@
 
 namespace pyn {
 
+// Row-partitioned set-up: a rank that has to refuse (no twin for an incomplete element, too many
+// classes) must not leave the others waiting in the next collective -- all ranks fail together.
+static int asm_all_ranks_ok(pyn_ctx* ctx, bool dist, bool ok_here) {
+  if (!dist) return ok_here ? PYN_OK : PYN_E_UNSUPPORTED;
+  DevBuf<double> flag;
+  PYN_CHECK(flag.alloc(ctx, 1));
+  const double mine = ok_here ? 0.0 : 1.0;
+  PYN_CHECK(flag.upload(&mine, 1));
+  PYN_CHECK(comm_allreduce_sum(ctx, flag.p, 1));
+  double all = 0.0;
+  PYN_CHECK(flag.download(&all, 1));
+  if (all == 0.0) return PYN_OK;
+  if (ok_here) set_error("pc asm: the set-up was refused on another rank (%d of %d ranks)", (int)all, ctx->nranks);
+  return PYN_E_UNSUPPORTED;
+}
+
 template <int B>
 static int asm_setup_impl(pyn_ctx* ctx, pyn_mat* A, AsmPc* pc) {
   pyn_mesh* mesh = A->mesh;
@@ -52,9 +68,8 @@ static int asm_setup_impl(pyn_ctx* ctx, pyn_mat* A, AsmPc* pc) {
   for (int64_t e = 0; e < nel; ++e)
     if (complete[(size_t)e]) clist.push_back((int32_t)e);
   pc->ncomplete = (int64_t)clist.size();
-  PYN_REQUIRE(pc->ncomplete > 0, "pc asm: no element of this rank has all its rows here");
   DevBuf<int32_t> dlist;
-  PYN_CHECK(dlist.alloc(ctx, pc->ncomplete));
+  PYN_CHECK(dlist.alloc(ctx, pc->ncomplete > 0 ? pc->ncomplete : 1));
   PYN_CHECK(dlist.upload(clist.data(), pc->ncomplete));
   DevBuf<unsigned long long> hash, sig;
   PYN_CHECK(hash.alloc(ctx, 2 * nel));
@@ -68,12 +83,18 @@ static int asm_setup_impl(pyn_ctx* ctx, pyn_mat* A, AsmPc* pc) {
   // 2. classes of equal blocks, their representatives
   std::vector<int32_t> cls, rep;
   static_assert(sizeof(unsigned long long) == sizeof(uint64_t), "hash word");
-  if (pc->ncomplete == nel) {
+  bool ok = true;
+  if (pc->ncomplete == 0) {
+    set_error("pc asm: no element of this rank has all its rows here");
+    ok = false;
+  } else if (pc->ncomplete == nel) {
     pc->nclass = asm_group_by_hash(nel, reinterpret_cast<const uint64_t*>(hh.data()), &cls, &rep);
+  } else if (mesh->nclass != 1) {
+    set_error("pc asm on a row-partitioned operator needs a mesh of congruent cells (one congruence class; this "
+              "mesh has %lld); use bjacobi", (long long)mesh->nclass);
+    ok = false;
   } else {
     // elements with ghost nodes: class of a complete element with the same signature
-    PYN_REQUIRE(mesh->nclass == 1, "pc asm on a row-partitioned operator needs a mesh of congruent cells "
-                                   "(one congruence class; this mesh has %lld); use bjacobi", (long long)mesh->nclass);
     PYN_CHECK(sig.alloc(ctx, 2 * nel));
     asm_signature_kernel<<<grid_for(ctx, nel, 256), 256, 0, ctx->stream>>>(
         nel, mesh->elem_nodes.p, nn, mesh->has_cls ? mesh->nodecls.p : nullptr, valence.p, sig.p);
@@ -82,15 +103,21 @@ static int asm_setup_impl(pyn_ctx* ctx, pyn_mat* A, AsmPc* pc) {
     PYN_CHECK(sig.download(ss.data(), 2 * nel));
     pc->nclass = asm_group_partitioned(nel, complete.data(), reinterpret_cast<const uint64_t*>(hh.data()),
                                        reinterpret_cast<const uint64_t*>(ss.data()), &cls, &rep);
-    PYN_REQUIRE(pc->nclass >= 0, "pc asm: element %lld touches another rank's rows and no element of this rank "
-                                 "with all rows local has the same signature; use fewer ranks or bjacobi",
+    if (pc->nclass < 0) {
+      set_error("pc asm: element %lld touches another rank's rows and no element of this rank with all rows local "
+                "has the same signature (blocks of elements too thin); use fewer ranks or bjacobi",
                 (long long)(-2 - pc->nclass));
+      ok = false;
+    }
   }
-  const int64_t inv_bytes = pc->nclass * (int64_t)ld * ld * (int64_t)sizeof(double);
-  PYN_REQUIRE(inv_bytes <= kAsmMaxInverseBytes,
-              "pc asm: %lld distinct element blocks of %d^2 (%lld MB of inverses): the elements of this mesh "
+  const int64_t inv_bytes = ok ? pc->nclass * (int64_t)ld * ld * (int64_t)sizeof(double) : 0;
+  if (ok && inv_bytes > kAsmMaxInverseBytes) {
+    set_error("pc asm: %lld distinct element blocks of %d^2 (%lld MB of inverses): the elements of this mesh "
               "are not congruent enough for the element-block Schwarz preconditioner; use bjacobi",
               (long long)pc->nclass, ld, (long long)(inv_bytes >> 20));
+    ok = false;
+  }
+  PYN_CHECK(asm_all_ranks_ok(ctx, dist, ok));
   // 3. dense blocks of the representatives -> host -> inverse -> device
   DevBuf<int32_t> drep;
   PYN_CHECK(drep.alloc(ctx, pc->nclass));
