@@ -463,6 +463,15 @@ def read_traffic():
 # which is not installed) timed on the host cores.  Checker code, used here only as the
 # reported baseline / the --impl reference arm.
 # ---------------------------------------------------------------------------------------------
+def _oracle_pc(args):
+    """the oracle's name of the preconditioner this run uses (-pc_asm_coarse k > 0: two-level)"""
+    if args.pc == "none":
+        return "jacobi"
+    if args.pc == "asm" and any(kv.startswith("pc_asm_coarse=") and kv.split("=")[1] not in ("0", "") for kv in args.opt):
+        return "asm+coarse"
+    return args.pc
+
+
 def cpu_timestep(args, steps, warmup):
     """one bounded sample: the same RK5BS time step on a (cpu_nelem)^3, ngl mesh with scipy CG +
     the same preconditioner and tolerance; returns (DOF/s, ms_per_step, description)"""
@@ -472,7 +481,7 @@ def cpu_timestep(args, steps, warmup):
     mesh = BoxMesh([n] * 3, [0, 0, 0], [1, 1, 1], args.ngl)
     prob = timestep.OracleProblem(3, args.ngl, mesh.corner_xyz, mesh.elem_nodes, mesh.coords,
                                   mesh.getBordersNodes(), rho=0.5, mu=0.01, solver="cg", rtol=args.rtol,
-                                  pc=args.pc if args.pc != "none" else "jacobi", fischer=args.fischer)
+                                  pc=_oracle_pc(args), fischer=args.fischer)
     ndof = mesh.nnodes * 3
     t, k0 = 0.0, None
     for _ in range(max(warmup, 1)):

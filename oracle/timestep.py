@@ -88,6 +88,7 @@ class OracleProblem:
         self.bdofs = (self.bnd[:, None] * dim + np.arange(dim)[None, :]).ravel()
         cls[self.bdofs] = 1
         self.bwdofs = self.bnd if dim == 2 else self.bdofs
+        self.ngl = ngl
         tab = sem.SpectralTables(ngl, dim)
         self.mats = assembly.assemble_kle(tab, corner_xyz, elem_nodes, nnodes, cls, "FS", reuse=reuse)
         self.ops = assembly.assemble_ops(tab, corner_xyz, elem_nodes, nnodes, reuse=reuse)
@@ -111,7 +112,7 @@ class OracleProblem:
         if self.pc == "jacobi":
             dinv = 1.0 / self.K.diagonal()
             self._M = spl.LinearOperator((n, n), matvec=lambda r: dinv * r)
-        elif self.pc == "asm":
+        elif self.pc in ("asm", "asm+coarse"):
             # PETSc PCASM with one subdomain per spectral element, symmetrically weighted by
             # 1/sqrt(elements sharing the dof):  sum_e R_e^T W inv(R_e K R_e^T) W R_e
             en = self.elem_nodes
@@ -125,6 +126,8 @@ class OracleProblem:
                 out = np.zeros_like(r)
                 np.add.at(out, dofs.ravel(), z.ravel())
                 return out
+            if self.pc == "asm+coarse":
+                apply = self._with_coarse_level(apply)
             self._M = spl.LinearOperator((n, n), matvec=apply)
         else:                       # node-block Jacobi
             import scipy.sparse as sp
@@ -137,6 +140,63 @@ class OracleProblem:
             blk[rows[sel]] = B.data[sel]
             inv = np.linalg.inv(blk)
             self._M = spl.LinearOperator((n, n), matvec=lambda r: np.einsum("nij,nj->ni", inv, r.reshape(nb, d)).ravel())
+
+    def _with_coarse_level(self, one_level, steps=5):
+        """-pc_asm_coarse <steps>: additive Q1 correction on the element corners.  P = the multilinear
+        corner functions at the GLL nodes (rows of constrained dofs left out), Ac = P^T K P, solved by
+        `steps` Chebyshev steps with point Jacobi on [0.1, 1.1] lambda_max(D^-1 Ac)"""
+        import scipy.sparse as sp
+        d, ngl = self.dim, self.ngl
+        en = self.elem_nodes
+        nel, nn = en.shape
+        x1 = sem.gauss_lobatto(ngl)[0]
+        t = sem.local_order(ngl, d)                                  # tensor index of every local node
+        tc = sem.local_order(2, d)                                   # ... of every corner, in {0, 1}
+        lin = np.stack([(1.0 - x1) / 2.0, (1.0 + x1) / 2.0], 1)      # [gll point][corner side]
+        phi = np.ones((nn, len(tc)))
+        for c in range(len(tc)):
+            for k in range(d):
+                phi[:, c] *= lin[t[:, k], tc[c, k]]
+        phi[np.abs(phi) < 1e-14] = 0.0
+        corner_local = [int(np.flatnonzero(np.all(t == tc[c] * (ngl - 1), axis=1))[0]) for c in range(len(tc))]
+        vnodes = np.unique(en[:, corner_local])
+        vid = np.full(en.max() + 1, -1)
+        vid[vnodes] = np.arange(len(vnodes))
+        first = {}
+        for e in range(nel):                                          # a node interpolates through its first element
+            for a in range(nn):
+                first.setdefault(int(en[e, a]), (e, a))
+        rows, cols, vals = [], [], []
+        for node, (e, a) in first.items():
+            for c in range(len(tc)):
+                if phi[a, c] != 0.0:
+                    rows.append(node), cols.append(vid[en[e, corner_local[c]]]), vals.append(phi[a, c])
+        P = sp.csr_matrix((vals, (rows, cols)), shape=(en.max() + 1, len(vnodes)))
+        K = self.K.tocsr()
+        off = K - sp.diags(K.diagonal())
+        keep = (np.asarray(abs(off).sum(1)).ravel() > 0).astype(float)
+        P = (sp.diags(keep) @ sp.kron(P, sp.identity(d))).tocsr()
+        Ac = (P.T @ K @ P).tocsr()
+        dg = Ac.diagonal()
+        dinv = np.where(dg > 1e-12 * dg.max(), 1.0 / np.where(dg == 0, 1.0, dg), 0.0)
+        lmax = 1.1 * spl.eigsh(spl.LinearOperator(Ac.shape, matvec=lambda v: dinv * (Ac @ v)), k=1, which="LM",
+                               return_eigenvectors=False, tol=1e-4)[0]
+        theta, delta = 0.55 * lmax, 0.45 * lmax
+
+        def coarse(b):
+            x = np.zeros_like(b)
+            r = b.copy()
+            sigma = theta / delta
+            rho = 1.0 / sigma
+            dv = dinv * r / theta
+            for _ in range(steps):
+                x = x + dv
+                r = r - Ac @ dv
+                rho_new = 1.0 / (2.0 * sigma - rho)
+                dv = rho_new * rho * dv + 2.0 * rho_new / delta * (dinv * r)
+                rho = rho_new
+            return x
+        return lambda r: one_level(r) + P @ coarse(P.T @ r)
 
     # ---- kle_solver.py:33-37 ---------------------------------------------------------------------
     def solve_kle(self, vort):

@@ -309,6 +309,12 @@ def test_oracle_asm_is_the_same_preconditioner_and_the_same_time_step():
     z, _, _, _, _ = run_emulated(mesh, asm.K, 3, r, grid=2)
     zo = asm._M.matvec(r)
     assert np.abs(z - zo).max() < 1e-11 * np.abs(zo).max()
+    # the two-level statement (pc="asm+coarse" = -pc_asm_coarse 5): same operator as the emulated kernels up
+    # to the power iteration's estimate of lambda_max (a few per cent of the coarse part)
+    two = timestep.OracleProblem(*args, rho=0.5, mu=0.01, solver="cg", pc="asm+coarse", rtol=1e-12)
+    z2 = run_emulated(mesh, asm.K, 3, r, grid=1, coarse_steps=5)[0]
+    zo2 = two._M.matvec(r)
+    assert np.abs((z2 - z) - (zo2 - zo)).max() < 0.05 * np.abs(zo2 - zo).max()
     for p in (direct, asm, bj):
         p.step(0.0, 2e-3)
     for name in ("vort", "vel"):
