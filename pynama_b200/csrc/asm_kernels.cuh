@@ -21,7 +21,8 @@ constexpr int kAsmRP = kAsmRG * kAsmRM;   // rows per panel
 constexpr int kAsmEM = 4;          // elements per thread (kAsmTile / 4 thread columns)
 static_assert(kAsmTile == 4 * kAsmEM, "thread layout: 4 element groups x 64 row groups");
 
-// MODE 0: hash the block of every element of the list into hash[e][2]
+// MODE 0: hash the block of every element of the list into hash[e][2] (quantum > 0: of the values
+//         rounded to multiples of it)
 // MODE 1: write the dense block of list element li to dense[li][ld][ld]
 // One warp per (list element, local row node).
 template <int B, int MODE>
@@ -29,7 +30,7 @@ __global__ void __launch_bounds__(256)
 asm_blocks_kernel(int64_t nlist, const int32_t* __restrict__ list, const int32_t* __restrict__ elem_nodes,
                   int nn, const int64_t* __restrict__ rowptr, const int32_t* __restrict__ colidx,
                   const double* __restrict__ val, unsigned long long* __restrict__ hash,
-                  double* __restrict__ dense) {
+                  double* __restrict__ dense, double quantum) {
   constexpr int BB = B * B;
   const int ld = nn * B;
   const int lane = threadIdx.x & 31;
@@ -60,7 +61,13 @@ asm_blocks_kernel(int64_t nlist, const int32_t* __restrict__ list, const int32_t
         const int64_t pos = (int64_t)(a * B + i) * ld + (b * B + j);
         if (MODE == 0) {
           if (v != 0.0) {
-            const unsigned long long bits = (unsigned long long)__double_as_longlong(v);
+            // quantum > 0: values are compared as multiples of it (blocks equal up to rounding share a
+            // class; what rounds to zero is a structural zero)
+            unsigned long long bits = (unsigned long long)__double_as_longlong(v);
+            if (quantum > 0.0) {
+              bits = (unsigned long long)llrint(v / quantum);
+              if (bits == 0ull) continue;
+            }
             h0 += asm_hash_entry(bits, (uint64_t)pos, 0);
             h1 += asm_hash_entry(bits, (uint64_t)pos, 1);
           }
@@ -81,6 +88,21 @@ asm_blocks_kernel(int64_t nlist, const int32_t* __restrict__ list, const int32_t
       }
     }
   }
+}
+
+// *out = bit pattern of max |val[i]| (non-negative doubles order like their bit patterns)
+__global__ void asm_absmax_kernel(int64_t n, const double* __restrict__ val, unsigned long long* out) {
+  double m = 0.0;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const double a = fabs(val[i]);
+    if (a > m) m = a;                       // NaNs never win
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const double t = __shfl_xor_sync(0xffffffffu, m, o);
+    if (t > m) m = t;
+  }
+  if ((threadIdx.x & 31) == 0) atomicMax(out, (unsigned long long)__double_as_longlong(m));
 }
 
 // valence[n] = elements of the local mesh holding node n (a row-partitioned run then refreshes

@@ -73,13 +73,43 @@ static int asm_setup_impl(pyn_ctx* ctx, pyn_mat* A, AsmPc* pc) {
   PYN_CHECK(dlist.upload(clist.data(), pc->ncomplete));
   DevBuf<unsigned long long> hash, sig;
   PYN_CHECK(hash.alloc(ctx, 2 * nel));
-  PYN_CHECK(hash.zero());
   const int grid = grid_for(ctx, pc->ncomplete * nn * 32, 256);
-  asm_blocks_kernel<B, 0><<<grid, 256, 0, ctx->stream>>>(pc->ncomplete, dlist.p, mesh->elem_nodes.p, nn, A->rowptr.p,
-                                                         A->colidx.p, A->val.p, hash.p, nullptr);
-  PYN_LAUNCHED(ctx);
+  // exact first; if that leaves more classes than the inverse store may hold, once more with the values
+  // rounded to multiples of 1e-7 of the largest entry of K, so that blocks equal up to rounding share one
+  // inverse (any symmetric positive definite inverse of a nearby block serves a preconditioner)
   std::vector<unsigned long long> hh((size_t)(2 * nel));
-  PYN_CHECK(hash.download(hh.data(), 2 * nel));
+  for (int attempt = 0; attempt < 2; ++attempt) {
+    double quantum = 0.0;
+    if (attempt == 1) {
+      DevBuf<unsigned long long> mx;
+      PYN_CHECK(mx.alloc(ctx, 1));
+      PYN_CHECK(mx.zero());
+      asm_absmax_kernel<<<grid_for(ctx, A->val.n, 256), 256, 0, ctx->stream>>>(A->val.n, A->val.p, mx.p);
+      PYN_LAUNCHED(ctx);
+      unsigned long long mbits = 0ull;
+      PYN_CHECK(mx.download(&mbits, 1));
+      double amax;
+      memcpy(&amax, &mbits, sizeof(double));
+      quantum = kAsmHashQuantum * amax;
+      if (!(quantum > 0.0)) break;
+    }
+    PYN_CHECK(hash.zero());
+    asm_blocks_kernel<B, 0><<<grid, 256, 0, ctx->stream>>>(pc->ncomplete, dlist.p, mesh->elem_nodes.p, nn,
+                                                           A->rowptr.p, A->colidx.p, A->val.p, hash.p, nullptr,
+                                                           quantum);
+    PYN_LAUNCHED(ctx);
+    PYN_CHECK(hash.download(hh.data(), 2 * nel));
+    pc->hash_quantum = quantum;
+    if (pc->ncomplete == 0) break;
+    std::vector<uint64_t> hc;
+    for (int32_t e : clist) {
+      hc.push_back(hh[(size_t)(2 * e)]);
+      hc.push_back(hh[(size_t)(2 * e + 1)]);
+    }
+    std::vector<int32_t> c0, r0;
+    const int64_t n0 = asm_group_by_hash((int64_t)clist.size(), hc.data(), &c0, &r0);
+    if (n0 * (int64_t)ld * ld * (int64_t)sizeof(double) <= kAsmMaxInverseBytes) break;
+  }
   // 2. classes of equal blocks, their representatives
   std::vector<int32_t> cls, rep;
   static_assert(sizeof(unsigned long long) == sizeof(uint64_t), "hash word");
@@ -124,7 +154,7 @@ static int asm_setup_impl(pyn_ctx* ctx, pyn_mat* A, AsmPc* pc) {
   PYN_CHECK(drep.upload(rep.data(), pc->nclass));
   PYN_CHECK(pc->inv.alloc(ctx, pc->nclass * (int64_t)ld * ld));
   asm_blocks_kernel<B, 1><<<grid_for(ctx, pc->nclass * nn * 32, 256), 256, 0, ctx->stream>>>(
-      pc->nclass, drep.p, mesh->elem_nodes.p, nn, A->rowptr.p, A->colidx.p, A->val.p, nullptr, pc->inv.p);
+      pc->nclass, drep.p, mesh->elem_nodes.p, nn, A->rowptr.p, A->colidx.p, A->val.p, nullptr, pc->inv.p, 0.0);
   PYN_LAUNCHED(ctx);
   std::vector<double> blocks((size_t)(pc->nclass * (int64_t)ld * ld));
   PYN_CHECK(pc->inv.download(blocks.data(), (int64_t)blocks.size()));

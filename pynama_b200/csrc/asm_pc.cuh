@@ -21,6 +21,7 @@ struct AsmPc {
   pyn_halo* halo = nullptr;
   int64_t n_own = 0;               // nodes summed into (all of them on one GPU)
   int64_t ncomplete = 0;           // elements whose block could be read here (all rows local)
+  double hash_quantum = 0.0;       // values were grouped as multiples of this (0: bitwise equal blocks)
   DevBuf<double> ybuf;             // [nel][ld] element-local results of the last apply
   size_t smem = 0;
   // second level (coarse_steps > 0): Q1 space on the element corners, Galerkin operator
@@ -43,6 +44,7 @@ struct AsmPc {
 // more distinct element blocks than this (bytes of inverses) is refused: the apply would read
 // more than the SpMV it is meant to save
 constexpr int64_t kAsmMaxInverseBytes = (int64_t)1 << 30;
+constexpr double kAsmHashQuantum = 1e-7;   // second grouping attempt: values as multiples of this x max |K|
 
 // coarse_steps: 0 = one level; k > 0 = plus the coarse correction with k Chebyshev steps
 int asm_setup(pyn_ctx* ctx, pyn_mat* A, int coarse_steps, AsmPc** out);

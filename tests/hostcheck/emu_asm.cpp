@@ -16,7 +16,7 @@ int run(int nn, long long nel, long long nnodes, const int32_t* elem_nodes, cons
         const int32_t* colidx, const double* val, const int64_t* n2e_ptr, const int2* n2e, const double* r,
         int grid, int napply, double* z, double* dots, long long* nclass_out, int32_t* cls_out, double* inv_out,
         int dim, int ngl, int coarse_steps, long long* coarse_info, double* ac_dense, long long n_own,
-        const double* valence_global, const uint8_t* nodecls) {
+        const double* valence_global, const uint8_t* nodecls, double quantum_rel) {
   const int ld = nn * B;
   // set-up, as asm_setup_impl
   std::vector<double> valence((size_t)nnodes, -1.0);
@@ -31,10 +31,19 @@ int run(int nn, long long nel, long long nnodes, const int32_t* elem_nodes, cons
     if (complete[(size_t)e]) clist.push_back((int32_t)e);
   }
   if (clist.empty()) return -8;
+  double quantum = 0.0;
+  if (quantum_rel > 0.0) {                      // the set-up's second grouping attempt
+    unsigned long long mbits = 0ull;
+    const int64_t nval = rowptr[nnodes] * B * B;
+    cuda_emu::launch(grid, 256, 0, [&]() { asm_absmax_kernel(nval, val, &mbits); });
+    double amax;
+    memcpy(&amax, &mbits, sizeof(double));
+    quantum = quantum_rel * amax;
+  }
   std::vector<unsigned long long> hash((size_t)(2 * nel), 0ull);
   cuda_emu::launch(grid, 256, 0, [&]() {
     asm_blocks_kernel<B, 0>((int64_t)clist.size(), clist.data(), elem_nodes, nn, rowptr, colidx, val, hash.data(),
-                            nullptr);
+                            nullptr, quantum);
   });
   std::vector<int32_t> cls, rep;
   int64_t nclass;
@@ -53,7 +62,7 @@ int run(int nn, long long nel, long long nnodes, const int32_t* elem_nodes, cons
   for (long long e = 0; e < nel; ++e) cls_out[e] = cls[(size_t)e];
   std::vector<double> inv((size_t)(nclass * (int64_t)ld * ld), -777.0);
   cuda_emu::launch(grid, 256, 0, [&]() {
-    asm_blocks_kernel<B, 1>(nclass, rep.data(), elem_nodes, nn, rowptr, colidx, val, nullptr, inv.data());
+    asm_blocks_kernel<B, 1>(nclass, rep.data(), elem_nodes, nn, rowptr, colidx, val, nullptr, inv.data(), 0.0);
   });
   for (int64_t c = 0; c < nclass; ++c) {
     double* a = inv.data() + c * (int64_t)ld * ld;
@@ -197,17 +206,17 @@ int emu_asm_apply(int B, int nn, long long nel, long long nnodes, const int* ele
                   const int* colidx, const double* val, const long long* n2e_ptr, const int* n2e, const double* r,
                   int grid, int napply, double* z, double* dots, long long* nclass_out, int* cls_out,
                   double* inv_out, int dim, int ngl, int coarse_steps, long long* coarse_info, double* ac_dense,
-                  long long n_own, const double* valence_global, const unsigned char* nodecls) {
+                  long long n_own, const double* valence_global, const unsigned char* nodecls, double quantum_rel) {
   static_assert(sizeof(long long) == sizeof(int64_t) && sizeof(int2) == 2 * sizeof(int), "ABI");
   const int64_t* rp = reinterpret_cast<const int64_t*>(rowptr);
   const int64_t* np = reinterpret_cast<const int64_t*>(n2e_ptr);
   const int2* ne = reinterpret_cast<const int2*>(n2e);
   if (B == 3)
     return run<3>(nn, nel, nnodes, elem_nodes, rp, colidx, val, np, ne, r, grid, napply, z, dots, nclass_out, cls_out,
-                  inv_out, dim, ngl, coarse_steps, coarse_info, ac_dense, n_own, valence_global, nodecls);
+                  inv_out, dim, ngl, coarse_steps, coarse_info, ac_dense, n_own, valence_global, nodecls, quantum_rel);
   if (B == 2)
     return run<2>(nn, nel, nnodes, elem_nodes, rp, colidx, val, np, ne, r, grid, napply, z, dots, nclass_out, cls_out,
-                  inv_out, dim, ngl, coarse_steps, coarse_info, ac_dense, n_own, valence_global, nodecls);
+                  inv_out, dim, ngl, coarse_steps, coarse_info, ac_dense, n_own, valence_global, nodecls, quantum_rel);
   return -1;
 }
 }
