@@ -9,8 +9,12 @@
 set -u
 out=gpurun_out/r2_asm
 mkdir -p "$out"
+# memory errors first, on the smallest case (these kernels have never touched a GPU)
+PYN_TEST_ASM=1 timeout 600 compute-sanitizer --tool memcheck --error-exitcode 9 \
+  python -m pytest tests/test_gpu_asm.py -x -q -k "reproducible" > "$out/memcheck.log" 2>&1
+echo "memcheck rc=$?" | tee "$out/rc.txt"
 PYN_TEST_ASM=1 timeout 900 python -m pytest tests/test_gpu_asm.py -x -q > "$out/pytest_asm.log" 2>&1
-echo "pytest_asm rc=$?" | tee "$out/rc.txt"
+echo "pytest_asm rc=$?" | tee -a "$out/rc.txt"
 for cfg in "bjacobi" "asm" "asm --opt pc_asm_coarse=5"; do
   tag=$(echo "$cfg" | tr -c 'a-z0-9' '_')
   timeout 600 python bench.py --steps 3 --warmup 3 --pc $cfg --no-asm-warm > "$out/bench_$tag.json" 2> "$out/bench_$tag.err"
