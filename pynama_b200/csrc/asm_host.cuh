@@ -140,13 +140,30 @@ inline int asm_dense_inverse(int n, double* a) {
   return 0;
 }
 
-// a <- (a + a^T)/2: the preconditioner must be exactly symmetric for CG
-inline void asm_symmetrise(int n, double* a) {
+// a <- (a + a^T)/2 when a is symmetric up to rounding (the preconditioner must be exactly symmetric
+// for CG); a visibly unsymmetric inverse (an unsymmetric operator under GMRES / BiCGStab) is left
+// alone.  Returns whether it symmetrised.
+inline bool asm_symmetrise(int n, double* a) {
+  double amax = 0.0, dmax = 0.0;
+  for (int i = 0; i < n; ++i)
+    for (int j = 0; j < n; ++j) {
+      amax = std::max(amax, fabs(a[(int64_t)i * n + j]));
+      if (j > i) dmax = std::max(dmax, fabs(a[(int64_t)i * n + j] - a[(int64_t)j * n + i]));
+    }
+  if (dmax > 1e-8 * amax) return false;
   for (int i = 0; i < n; ++i)
     for (int j = i + 1; j < n; ++j) {
       const double v = 0.5 * (a[(int64_t)i * n + j] + a[(int64_t)j * n + i]);
       a[(int64_t)i * n + j] = a[(int64_t)j * n + i] = v;
     }
+  return true;
+}
+
+// The product kernel reads row k of the stored matrix for column k of the inverse: an inverse that
+// was not symmetrised is stored transposed.
+inline void asm_transpose(int n, double* a) {
+  for (int i = 0; i < n; ++i)
+    for (int j = i + 1; j < n; ++j) std::swap(a[(int64_t)i * n + j], a[(int64_t)j * n + i]);
 }
 
 // Tiles of `te` elements of one class each (the last tile of a class padded with -1), classes

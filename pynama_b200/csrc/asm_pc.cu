@@ -161,7 +161,7 @@ static int asm_setup_impl(pyn_ctx* ctx, pyn_mat* A, AsmPc* pc) {
   for (int64_t c = 0; c < pc->nclass; ++c) {
     double* a = blocks.data() + c * (int64_t)ld * ld;
     PYN_REQUIRE(asm_dense_inverse(ld, a) == 0, "pc asm: the block of element %d is singular", (int)rep[(size_t)c]);
-    asm_symmetrise(ld, a);
+    if (!asm_symmetrise(ld, a)) asm_transpose(ld, a);
   }
   PYN_CHECK(pc->inv.upload(blocks.data(), (int64_t)blocks.size()));
   // 4. tiles of elements of one class

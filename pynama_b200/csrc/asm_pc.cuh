@@ -12,7 +12,7 @@ struct AsmPc {
   pyn_mesh* mesh = nullptr;
   int B = 0, ld = 0;               // dofs per node, dofs per element (nn * B)
   int64_t nclass = 0, ntiles = 0;
-  DevBuf<double> inv;              // [nclass][ld][ld], symmetric
+  DevBuf<double> inv;              // [nclass][ld][ld], symmetric (or the transposed inverse of an unsymmetric block)
   DevBuf<int32_t> tile_elems;      // [ntiles][kAsmTile (asm_kernels.cuh)] elements of one class, -1 padded
   DevBuf<int32_t> tile_class;      // [ntiles]
   DevBuf<double> wnode;            // [nnodes]

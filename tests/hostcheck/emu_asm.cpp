@@ -67,7 +67,7 @@ int run(int nn, long long nel, long long nnodes, const int32_t* elem_nodes, cons
   for (int64_t c = 0; c < nclass; ++c) {
     double* a = inv.data() + c * (int64_t)ld * ld;
     if (asm_dense_inverse(ld, a) != 0) return -2;
-    asm_symmetrise(ld, a);
+    if (!asm_symmetrise(ld, a)) asm_transpose(ld, a);
   }
   if (inv_out) memcpy(inv_out, inv.data(), sizeof(double) * inv.size());
   std::vector<int32_t> tile_elems, tile_class;

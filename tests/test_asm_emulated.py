@@ -393,3 +393,16 @@ def test_emulated_rounded_grouping_merges_blocks_equal_up_to_rounding():
     for c in range(n1):
         assert len({tuple(p) for p in pos[cls == c]}) == 1              # one position class per hash class
     assert np.abs(z1 - z0).max() < 1e-9 * np.abs(z0).max()
+
+
+def test_emulated_apply_on_an_unsymmetric_operator():
+    """GMRES / BiCGStab may hand the preconditioner an unsymmetric operator: the inverses are then
+    not symmetrised and are stored transposed (the product kernel reads row k for column k)"""
+    mesh, K = kle_operator(2, [4, 3], 4)
+    rng = np.random.default_rng(51)
+    K2 = (K @ sp.diags(rng.uniform(0.5, 2.0, K.shape[0]))).tocsr()
+    r = rng.standard_normal(K.shape[0])
+    z, _, _, _, inv = run_emulated(mesh, K2, 2, r, grid=2, want_inv=True)
+    zref = element_schwarz(K2, mesh.elem_nodes, 2, weighted=True)[0](r)
+    assert np.abs(z - zref).max() < 1e-10 * np.abs(zref).max()
+    assert not np.allclose(inv[0], inv[0].T)
