@@ -173,3 +173,38 @@ def assemble_ops(tab, corner_xyz, elem_nodes, nnodes, reuse=True):
         out[name] = m
     out["W"] = W
     return out
+
+
+def elements_of_nodes(elem_nodes, nodes):
+    """ascending list of the elements touching any of `nodes`"""
+    en = np.asarray(elem_nodes)
+    return np.flatnonzero(np.isin(en, np.asarray(nodes)).any(axis=1))
+
+
+def assemble_rows(tab, corner_xyz, elem_nodes, nnodes, cls, nodes, mode="FS", ops=True, reuse=True):
+    """The rows of the sampled `nodes` of every matrix, for meshes too large to assemble whole on
+    the CPU: the cell loops of mat_fs.py:150-201 / mat_ns.py:47-145 restricted to the cells that
+    touch a sampled node, in the same ascending cell order -- those rows receive exactly the
+    contributions (and the summation order) of the full loop.  Returns (dict name -> csr holding
+    only the sampled rows, all other rows empty; 'W' -> lumped mass at the nodes) and the cells used."""
+    nodes = np.unique(np.asarray(nodes, dtype=np.int64))
+    els = elements_of_nodes(elem_nodes, nodes)
+    cx = np.asarray(corner_xyz).reshape(len(elem_nodes), -1, tab.dim)[els]
+    en = np.asarray(elem_nodes)[els]
+    out = dict(assemble_kle(tab, cx, en, nnodes, cls, mode, reuse=reuse))
+    if ops:
+        with np.errstate(divide="ignore", invalid="ignore"):      # nodes no sampled cell touches: W = 0
+            out.update(assemble_ops(tab, cx, en, nnodes, reuse=reuse))
+
+    def keep_rows(m, br):
+        rows = (nodes[:, None] * br + np.arange(br)[None, :]).ravel()
+        sel = np.zeros(m.shape[0], bool)
+        sel[rows] = True
+        m = m.tocsr()
+        lens = np.diff(m.indptr)
+        mask = np.repeat(sel, lens)
+        ip = np.concatenate([[0], np.cumsum(np.where(sel, lens, 0))])
+        return sp.csr_matrix((m.data[mask], m.indices[mask], ip), shape=m.shape)
+    br = {"Curl": tab.dim_w, "SrT": tab.dim_s}
+    res = {k: (m[nodes] if k == "W" else keep_rows(m, br.get(k, tab.dim))) for k, m in out.items()}
+    return res, els

@@ -94,6 +94,10 @@ int pyn_tune(const char* key, int value) {
     g_ksp_check_every = value;
     return PYN_OK;
   }
+  if (strcmp(key, "force_idx64") == 0) {          // tests: take the 64-bit index instantiations on small meshes
+    g_force_idx64 = value != 0;
+    return PYN_OK;
+  }
   set_error("pyn_tune: unknown key '%s'", key);
   return PYN_E_INVALID;
 }

@@ -701,7 +701,7 @@ static int assemble_kle_fused_impl(pyn_mesh* mesh, const MatSpec* sp, pyn_mat** 
   // two half passes K|Krhs and Rw|Rd: 0.82 ms)
   const int grid = grid_for(ctx, g.nrows * 32, 256, 2);   // one resident wave
   // 32-bit contribution / record indices when they fit
-  const bool idx32 = g.ncontrib < (int64_t)0x7fffffff &&
+  const bool idx32 = !g_force_idx64 && g.ncontrib < (int64_t)0x7fffffff &&
                      mesh->nclass * npairs * kle_record_stride(d) < (int64_t)0x7fffffff;
 #define NKLE_ARGS                                                                                   \
   <<<grid, 256, 0, ctx->stream>>>(g.nrows, g.rowptr.p, g.colidx.p, g.cptr.p, src, sp[0].ebs, npairs, \

@@ -21,6 +21,7 @@
 
 namespace pyn {
 int g_ksp_check_every = 8;
+bool g_force_idx64 = false;
 
 // device scalar block
 enum {
@@ -96,6 +97,9 @@ __device__ __forceinline__ void cg_bookkeeping(double* S, double rz_new, double 
   S[S_RNORM] = rn;
   if (!(rn == rn) || !(pw == pw) || pw == 0.0) {       // NaN / breakdown
     S[S_REASON] = -9.0;
+    S[S_DONE] = 1.0;
+  } else if (pw < 0.0) {                                 // p.Ap < 0: KSP_DIVERGED_INDEFINITE_MAT
+    S[S_REASON] = -10.0;
     S[S_DONE] = 1.0;
   } else if (rn <= S[S_TTOL]) {
     S[S_REASON] = S[S_REASON] == 0.0 ? 2.0 : S[S_REASON];
@@ -292,6 +296,8 @@ cg_sr_update_kernel(int pc, const double* __restrict__ pcd, double* __restrict__
     stop = 1; reason = -3.0;
   } else if (!(denom == denom) || denom == 0.0) {
     stop = 1; reason = -9.0;
+  } else if (denom < 0.0) {                  // p.Kp < 0: KSP_DIVERGED_INDEFINITE_MAT
+    stop = 1; reason = -10.0;
   }
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     S[S_ZZ] = uu;

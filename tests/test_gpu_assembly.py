@@ -170,3 +170,29 @@ def test_fused_kle_pass_equals_per_matrix_pass(mode, nelem, ngl, perturb, monkey
         a, b = fused[name].getValuesCSR(), per[name].getValuesCSR()
         for x, y in zip(a, b):
             assert np.array_equal(x, y), name
+
+
+@pytest.mark.parametrize("mode,nelem,ngl,perturb", [("FS", [3, 3, 2], 3, 0.15), ("NS", [2, 2, 2], 4, 0.0),
+                                                     ("NS", [4, 3], 4, 0.1)])
+def test_64bit_index_path_equals_32bit_and_oracle(mode, nelem, ngl, perturb):
+    """BASELINE.json configs[2] (32^3, ngl=5: 4.09e9 scalar non-zeros in K) is the only mesh large
+    enough to take the 64-bit instantiation of the numeric kernel by itself; pyn_tune("force_idx64")
+    makes a small mesh take it, and the result must be the oracle's and bit-identical to the 32-bit one"""
+    from pynama_b200 import _lib
+    mesh, dm, tab = _setup(nelem, ngl, perturb)
+    cls = ns_classes(mesh, None) if mode == "NS" else fs_classes(mesh)
+    dm.set_dof_class(cls)
+    a = dm.assemble_kle(mode)
+    _lib.call("pyn_tune", b"force_idx64", 1)
+    try:
+        b = dm.assemble_kle(mode)
+    finally:
+        _lib.call("pyn_tune", b"force_idx64", 0)
+    want = assembly.assemble_kle(tab, mesh.corner_xyz, mesh.elem_nodes, mesh.nnodes, cls, mode)
+    for name in want:
+        if mode == "FS" and name == "Rd":
+            continue
+        ga, gb = a[name].getValuesCSR(), b[name].getValuesCSR()
+        for x, y in zip(ga, gb):
+            assert np.array_equal(x, y), name
+        assert_same_csr(csr_of(b[name]), want[name], name=name)

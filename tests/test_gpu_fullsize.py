@@ -134,3 +134,79 @@ def test_solve_round_trip(full, opts):
     assert np.abs(x.getArray() - xs).max() <= 1e-7
     r = (K * x).getArray() - b.getArray()
     assert np.linalg.norm(r) <= 1e-9 * np.linalg.norm(b.getArray())
+
+
+# ---- oracle parity at the full size: a sample of rows ------------------------------------------
+def _sample_nodes(mesh):
+    """48 row nodes of the 16^3 / ngl=4 GLL grid covering every kind of row: box corners, box edges,
+    box faces, element vertices (valence 8), element edges (4), element faces (2), element interiors
+    (1), nodes on the planes where the 2/4/8-rank partitions cut (element index 8), first and last row"""
+    g = mesh.grid
+    p = NGL - 1
+    nid = lambda i, j, k: int(i + g[0] * (j + g[1] * k))
+    last = int(g[0] - 1)
+    mid = 8 * p                       # the partition planes of parallel.py (element 8 of 16)
+    picks = [(0, 0, 0), (last, last, last), (last, 0, 0), (0, last, last),          # box corners
+             (5, 0, 0), (0, 7, last), (last, last, 10), (mid, 0, 0),                 # box edges
+             (4, 5, 0), (last, 7, 11), (6, last, mid), (mid, mid, 0),                # box faces
+             (3, 3, 3), (mid, mid, mid), (3 * p, 9 * p, 15 * p), (p, 15 * p, p),     # element vertices
+             (mid, mid, mid + 1), (3, 6, 9 + 1), (12 + 2, 9, 3), (mid, mid - 1, mid),  # element edges
+             (mid, 10, 11), (4, mid + 1, 2 * p), (7, 8, 3 * p), (mid + 1, mid + 2, mid),  # element faces
+             (1, 1, 1), (mid + 1, mid + 2, mid + 1), (46, 47, 46), (22, 23, 26),      # element interiors
+             (mid, 5, 7), (11, mid, 13), (20, 22, mid), (mid, mid, 4), (mid - 1, mid, mid)]  # partition planes
+    rng = np.random.default_rng(20240229)
+    nodes = [nid(*q) for q in picks] + rng.integers(0, mesh.nnodes, 15).tolist()
+    return np.unique(np.asarray(nodes, dtype=np.int64))
+
+
+def _rows(m, nodes, br):
+    rows = (np.asarray(nodes)[:, None] * br + np.arange(br)[None, :]).ravel()
+    return m.tocsr()[rows]
+
+
+def _check_rows(got_mat, want, nodes, br, name, rtol=1e-12):
+    from tests.util import csr_of
+    g = _rows(csr_of(got_mat), nodes, br)
+    w = _rows(want, nodes, br)
+    w.sort_indices()
+    assert np.array_equal(g.indptr, w.indptr), f"{name}: row lengths differ"
+    assert np.array_equal(g.indices, w.indices), f"{name}: column indices differ"
+    scale = np.abs(w.data).max() if w.nnz else 1.0
+    err = np.abs(g.data - w.data).max() if w.nnz else 0.0
+    assert err <= rtol * scale, f"{name}: max |diff| {err:.3e} vs scale {scale:.3e}"
+    return g.nnz
+
+
+@pytest.mark.parametrize("perturb", [0.0, 0.15])
+def test_sampled_rows_against_the_oracle(perturb):
+    """configs[1] (16^3 elements, ngl = 4), affine and perturbed: the rows of 48 sampled nodes of K,
+    Krhs, Rw, Curl, SrT, DivSrT and the lumped mass against the oracle's restatement of the cell
+    loops (mat_fs.py:150-201, spectral.py:92-228) restricted to the cells touching those nodes:
+    pattern bit-exact (explicit zeros included), values <= 1e-12 of the largest entry"""
+    from oracle import assembly, sem
+    from pynama_b200.device_mesh import DeviceMesh
+    from pynama_b200.domain.box_mesh import BoxMesh
+    mesh = BoxMesh([NEL] * 3, [0.0] * 3, [1.0] * 3, NGL, perturb=perturb)
+    dm = DeviceMesh(3, NGL, mesh.corner_xyz, mesh.elem_nodes, mesh.nnodes)
+    assert dm.congruence()[1] == (1 if perturb == 0.0 else mesh.nel)
+    cls = np.zeros(mesh.nnodes * 3, np.uint8)
+    b = mesh.getBordersNodes()
+    for d in range(3):
+        cls[b * 3 + d] = 1
+    dm.set_dof_class(cls)
+    nodes = _sample_nodes(mesh)
+    want, els = assembly.assemble_rows(sem.SpectralTables(NGL, 3), mesh.corner_xyz, mesh.elem_nodes,
+                                       mesh.nnodes, cls, nodes, "FS")
+    assert len(els) > 80
+    mats = dm.assemble_kle("FS")
+    total = 0
+    for name in ("K", "Krhs", "Rw"):
+        total += _check_rows(mats[name], want[name], nodes, 3, name)
+        mats[name].destroy()
+    curl, srt, div, w = dm.assemble_ops(compact=True)           # the storage the bench runs on
+    total += _check_rows(curl, want["Curl"], nodes, 3, "Curl")
+    total += _check_rows(srt, want["SrT"], nodes, 6, "SrT")
+    total += _check_rows(div, want["DivSrT"], nodes, 3, "DivSrT")
+    assert np.abs(w.getArray()[nodes] - want["W"]).max() <= 1e-13 * want["W"].max()
+    assert total > 100000
+    dm.destroy()

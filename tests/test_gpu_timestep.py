@@ -80,3 +80,56 @@ def test_no_slip_cavity_fields_after_n_steps(case, nelem, ngl):
     assert _rel(fem.solverKLE.getSolution().getArray(), orc.vel) < TOL
     assert _rel(fem.solverKLE.getFreeSlipSolution().getArray(), orc.velfs) < TOL
     assert _rel(fem.vort.getArray(), orc.vort) < TOL
+
+
+_ORACLE_8 = {}
+
+
+def _oracle_8cube(mesh, rho, mu):
+    """oracle fields after 3 steps of dt = 1e-3 on the 8^3 / ngl=4 mesh, computed once per session
+    (about 90 s of scipy CG to a 1e-13 residual)"""
+    if not _ORACLE_8:
+        orc = timestep.OracleProblem(3, 4, mesh.corner_xyz, mesh.elem_nodes, mesh.coords, mesh.getBordersNodes(),
+                                     rho=rho, mu=mu, solver="cg", rtol=1e-13, pc="bjacobi")
+        t, k0 = 0.0, None
+        for _ in range(3):
+            t, k0 = orc.step(t, 1e-3, k0)
+        _ORACLE_8.update(vel=orc.vel.copy(), vort=orc.vort.copy(), t=t)
+    return _ORACLE_8
+
+
+@pytest.mark.parametrize("extra", [{}, {"ksp_cg_single_reduction": 1}, {"kle_matfree": 1}],
+                         ids=["bench-options", "single-reduction", "matrix-free"])
+def test_bench_options_fields_at_8cube(extra):
+    """The options bench.py times (cg + bjacobi, rtol 1e-10, -ksp_fischer_guess 1,16, dt 1e-3; and the
+    multi-GPU default -ksp_cg_single_reduction, and -kle_matfree) on the 8^3-element, ngl=4 mesh
+    (46 875 dofs: the largest the oracle steps in about a minute): velocity and vorticity after 3 RK5BS
+    steps against the oracle run to a 1e-13 residual (base_problem.py:111-136, kle_solver.py:33-37)."""
+    from pynama_b200.cases.base_problem import BaseProblem
+    from pynama_b200.petsc import Options
+    from pynama_b200.run_case import loadCase
+    o = _options()
+    o.setValue("ksp_rtol", 1e-10)
+    o.setValue("ksp_fischer_guess", "1,16")
+    o.setValue("ts_dt", 1e-3)
+    for k, v in extra.items():
+        o.setValue(k, v)
+    try:
+        cfg = loadCase("taylor-green3d")
+        fem = BaseProblem(cfg, case="taylor-green3d", nelem=[8, 8, 8], ngl=4)
+        fem.setUp()
+        fem.setUpSolver()
+        fem.ts._post = None
+        fem.ts.setSolution(fem.vort)
+        mesh = fem.dom.getMesh()
+        for _ in range(3):
+            fem.ts.step()
+        orc = _oracle_8cube(mesh, fem.rho, fem.mu)
+        assert abs(fem.ts.getTime() - orc["t"]) < 1e-15
+        ev = _rel(fem.solverKLE.getSolution().getArray(), orc["vel"])
+        ew = _rel(fem.vort.getArray(), orc["vort"])
+        print(f"bench-option parity at 8^3: vel {ev:.3e} vort {ew:.3e} its {fem.kspIterations}")
+        assert ev < TOL and ew < TOL
+    finally:
+        for k in list(extra) + ["ksp_fischer_guess"]:
+            Options().delValue(k)
