@@ -541,8 +541,14 @@ class Vec:
 
     def norm(self, norm_type=None):
         if norm_type not in (None, 2, Vec.NormType.NORM_2):
-            a = np.abs(self.getArray())
-            return float(a.sum()) if norm_type == 1 else float(a.max(initial=0.0))
+            a = np.abs(self.getArray())                      # owned entries
+            if norm_type == 1:
+                v, op = float(a.sum()), "sum"
+            else:
+                v, op = float(a.max(initial=0.0)), "max"
+            if self._layout is not None and COMM_WORLD.size > 1:
+                v = float(Context.get().allreduce([v], op)[0])
+            return v
         out = c_dbl()
         call("pyn_vec_norm2", self._h, ctypes.byref(out))
         return out.value
@@ -897,10 +903,18 @@ class KSP:
         if self._mat is None:
             raise PynamaError("KSP.setUp: no operator set")
         ktype, pctype, rtol = self._type, self._pc.getType(), self.rtol
+        self._direct_mapped = False
         if pctype in ("lu", "cholesky") or ktype == "preonly":
-            self._log.warning("direct solve (-ksp_type %s -pc_type %s) requested: using cg + node-block "
-                              "Jacobi at rtol 1e-12 on the GPU instead", ktype, pctype)
-            ktype, pctype, rtol = "cg", "bjacobi", min(self.rtol, 1e-12)
+            # the reference default (kle_solver.py:58-60, makefile:7).  Only the KLE operator K is known
+            # to be symmetric positive definite; anything else (K + Kfs, the immersed-boundary H S) gets
+            # GMRES.  A direct solve cannot "fail to converge", so solve() raises if the mapped one does.
+            spd = getattr(self._mat, "_name", "") == "K"
+            mapped = "cg" if spd else "gmres"
+            self._log.warning("direct solve (-ksp_type %s -pc_type %s) requested on '%s': there is no sparse "
+                              "factorisation on the GPU path; using -ksp_type %s -pc_type bjacobi -ksp_rtol "
+                              "1e-12 instead", ktype, pctype, getattr(self._mat, "_name", "?"), mapped)
+            ktype, pctype, rtol = mapped, "bjacobi", min(self.rtol, 1e-12)
+            self._direct_mapped = True
         if ktype not in self._TYPES:
             raise PynamaError(f"unknown KSP type '{ktype}'")
         if pctype not in self._PCS:
@@ -927,8 +941,14 @@ class KSP:
              ctypes.byref(rn))
         self._its, self._reason, self._rnorm = its.value, reason.value, rn.value
         if reason.value < 0:
-            self._log.warning("KSP did not converge: reason %d after %d iterations, residual %.3e",
-                              reason.value, its.value, rn.value)
+            msg = "KSP did not converge: reason %d%s after %d iterations, residual %.3e" % (
+                reason.value, " (indefinite operator: p.Ap < 0 in CG)" if reason.value == -10 else "",
+                its.value, rn.value)
+            self.failures = getattr(self, "failures", 0) + 1           # sticky: callers may check
+            if getattr(self, "_direct_mapped", False):
+                raise PynamaError(msg + " -- the requested direct solve (-pc_type lu) was mapped to this "
+                                        "Krylov solve, which must converge")
+            self._log.warning(msg)
 
     def __call__(self, b, x=None):
         if x is None:

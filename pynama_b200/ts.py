@@ -41,6 +41,13 @@ TABLEAUX = {"5bs": {"A": _A, "b": _B, "be": _BE, "c": _C, "order": 5, "fsal": Tr
 # classical pairs PETSc also offers under the names TsSolver lists (ts_solver.py:4)
 TABLEAUX["3"] = {"A": [[], [1 / 2], [-1, 2]], "b": [1 / 6, 2 / 3, 1 / 6], "be": None,
                  "c": [0, 1 / 2, 1], "order": 3, "fsal": False}
+# Fehlberg 5(4), six stages (PETSc TSRK5F propagates the fifth-order solution)
+TABLEAUX["5f"] = {"A": [[], [1 / 4], [3 / 32, 9 / 32], [1932 / 2197, -7200 / 2197, 7296 / 2197],
+                        [439 / 216, -8, 3680 / 513, -845 / 4104],
+                        [-8 / 27, 2, -3544 / 2565, 1859 / 4104, -11 / 40]],
+                  "b": [16 / 135, 0, 6656 / 12825, 28561 / 56430, -9 / 50, 2 / 55],
+                  "be": [25 / 216, 0, 1408 / 2565, 2197 / 4104, -1 / 5, 0],
+                  "c": [0, 1 / 4, 3 / 8, 12 / 13, 1, 1 / 2], "order": 5, "fsal": False}
 
 
 class TS:
@@ -142,7 +149,12 @@ class TS:
         self._post = fn
 
     def setSolution(self, u):
+        """TSSetSolution.  The cases call it after changing the state between steps (the immersed-
+        boundary loops correct the velocity and recompute the vorticity, immersed_boundary.py:58-82),
+        so the stage carried over from the last step (FSAL) no longer belongs to the solution and is
+        evaluated again.  [PETSc's own rule for this is not in the reference tree: unpinned]"""
         self._u = u
+        self._fsal_valid = False
 
     def getSolution(self):
         return self._u
@@ -171,9 +183,16 @@ class TS:
 
     def _wlte(self, u_old, u_new, err):
         """weighted 2-norm of the local error estimate (TSErrorWeightedNorm, NORM_2)"""
-        a, b, e = u_old.getArray(), u_new.getArray(), err.getArray()
+        a, b, e = u_old.getArray(), u_new.getArray(), err.getArray()         # owned entries
         tol = self._atol + self._rtol * np.maximum(np.abs(a), np.abs(b))
-        return float(np.sqrt(np.mean((e / tol) ** 2))) if len(e) else 0.0
+        part = [float(np.sum((e / tol) ** 2)), float(len(e))]
+        if COMM_WORLD.size > 1:
+            # every rank must see the same norm, or the ranks accept / reject differently and the
+            # collectives of the next RHS evaluation no longer match; summed in rank order on the
+            # host, so the bits agree on all ranks
+            parts = COMM_WORLD.allgather(part)
+            part = [sum(q[0] for q in parts), sum(q[1] for q in parts)]
+        return float(np.sqrt(part[0] / part[1])) if part[1] > 0 else 0.0
 
     def step(self):
         """one accepted step of size <= dt (retries with a smaller step on rejection)"""

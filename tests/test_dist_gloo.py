@@ -17,3 +17,14 @@ def test_gloo_partitioned_host_logic(nproc, port):
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=900, env=env)
     assert r.returncode == 0, r.stdout[-2000:] + "\n" + r.stderr[-3000:]
     assert r.stdout.count("OK") == nproc
+
+
+def test_gloo_adaptive_time_step_is_the_same_on_all_ranks():
+    """the error norm of the adaptive controller is reduced over the ranks"""
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+           "--master-addr", "127.0.0.1", "--master-port", "29575",
+           os.path.join(ROOT, "tests", "gloo_ts_check.py")]
+    env = dict(os.environ, OMP_NUM_THREADS="1")
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env)
+    assert r.returncode == 0, r.stdout[-2000:] + "\n" + r.stderr[-3000:]
+    assert r.stdout.count("OK") == 2

@@ -163,3 +163,38 @@ def test_rejected_step_leaves_the_state_untouched(opts):
     assert ts.rejections >= 1 and ts.getStepNumber() == 1
     assert abs(u.a[0] - math.exp(-5.0 * ts.getTime())) < 1e-3
     assert calls[0] == 0.0
+
+
+def test_fehlberg_pair_is_listed_and_fifth_order(opts):
+    """TsSolver.rk_types names '5f' (ts_solver.py:4): the tableau exists and converges at order 5"""
+    opts("ts_adapt_type", "none")
+    opts("ts_rk_type", "5f")
+    errs = []
+    for n in (8, 16):
+        opts("ts_dt", 1.0 / n)
+        ts = make_ts(lambda ts_, t, u, f: np.copyto(f.a, -u.a * (1.0 + t)), 0.0, 1.0, 10000)
+        assert ts.getRKType() == "5f"
+        u = NpVec([1.0])
+        ts.solve(u)
+        errs.append(abs(u.a[0] - math.exp(-1.5)))
+    assert 4.5 < math.log2(errs[0] / errs[1]) < 6.5
+
+
+def test_set_solution_drops_the_carried_stage(opts):
+    """a state changed between steps (the immersed-boundary loops) must not reuse the
+    FSAL stage of the old state"""
+    opts("ts_adapt_type", "none")
+    opts("ts_dt", 0.1)
+    ts = make_ts(lambda ts_, t, u, f: np.copyto(f.a, -u.a), 0.0, 1.0, 100)
+    u = NpVec([1.0])
+    ts.setSolution(u)
+    ts.step()
+    n1 = ts.rhs_evals
+    ts.step()
+    assert ts.rhs_evals - n1 == 7            # FSAL: first stage carried over
+    u.a[:] = 5.0
+    ts.setSolution(u)
+    n2 = ts.rhs_evals
+    ts.step()
+    assert ts.rhs_evals - n2 == 8            # re-evaluated on the changed state
+    assert abs(u.a[0] - 5.0 * math.exp(-0.1)) < 1e-8
