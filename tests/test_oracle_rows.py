@@ -36,3 +36,19 @@ def test_sampled_rows_equal_full_assembly(nelem, ngl, mode, perturb):
         assert np.array_equal(a.indptr, b.indptr) and np.array_equal(a.indices, b.indices), name
         assert np.array_equal(a.data, b.data), name
         assert m.nnz == a.nnz, name                        # nothing outside the sampled rows
+
+
+@pytest.mark.parametrize("nelem,ngl,perturb", [([4, 3], 3, 0.0), ([3, 2, 4], 4, 0.15), ([2, 2, 2], 2, 0.1)])
+def test_oracle_box_mesh_equals_the_product_box_mesh(nelem, ngl, perturb):
+    """the CPU arm of bench.py builds its mesh from oracle/boxmesh.py (no product import there)"""
+    from oracle import boxmesh
+    from pynama_b200.domain.box_mesh import BoxMesh
+    dim = len(nelem)
+    a = BoxMesh(nelem, [0.0] * dim, [1.0, 2.0, 1.5][:dim], ngl, perturb=perturb)
+    b = boxmesh.box_mesh(nelem, [0.0] * dim, [1.0, 2.0, 1.5][:dim], ngl, perturb=perturb)
+    assert np.array_equal(a.corner_xyz, b.corner_xyz)
+    assert np.array_equal(a.elem_nodes, b.elem_nodes)
+    assert np.abs(a.coords - b.coords).max() <= 1e-14
+    assert np.array_equal(a.getBordersNodes(), b.border_nodes)
+    for s in a.sides:
+        assert np.array_equal(a.getBorderNodes(s), b.sides[s])
