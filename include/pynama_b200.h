@@ -301,6 +301,19 @@ int pyn_vtensv(pyn_vec* vel, pyn_vec* out, int dim);
 /* aux = 2 mu * aux - rho * vtensv(vel)   (base_problem.py:127-130 fused) */
 int pyn_stress_combine(pyn_vec* aux, pyn_vec* vel, double mu, double rho, int dim);
 
+/* ---- allocation-free entry point ---------------------------------------------------------*/
+/* No counterpart in the reference: added for callers that may
+ * not allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).
+ * out[0] = x . y over n entries; x, y, out are DEVICE pointers supplied by the caller; the work is
+ * queued on `stream` (a cudaStream_t; NULL = the context's stream) and the call does not wait for it.
+ * It is pyn_vec_dot's kernel with the reduction scratch (per-chunk partial sums + arrival ticket) in a
+ * file-scope device array of 131 328 bytes that every GPU loading the library holds until exit, so
+ * the call path has no cudaMalloc / cudaFree / allocating routine.  n > PYN_NOALLOC_MAX_N is refused
+ * (PYN_E_INVALID).  All calls on a device share that array: calls that overlap on the GPU race; calls
+ * ordered on one stream (or by events) are safe.  The current device must be the context's. */
+#define PYN_NOALLOC_MAX_N 268435456LL /* 16384 chunks x 16384 entries */
+int pyn_vec_dot_noalloc(pyn_ctx* ctx, const double* x, const double* y, int64_t n, double* out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
