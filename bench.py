@@ -47,7 +47,6 @@ def parse_args():
     ap.add_argument("--rtol", type=float, default=1e-10, help="KSP relative tolerance")
     ap.add_argument("--dt", type=float, default=1e-3, help="fixed time step (-ts_adapt_type none)")
     ap.add_argument("--pc", default="bjacobi", choices=["jacobi", "bjacobi", "none", "asm"])
-    ap.add_argument("--cpu-nelem", type=int, default=8, help="mesh of the bounded CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-matfree", action="store_true", help="skip the extra matrix-free (-kle_matfree 1) pass")
@@ -113,6 +112,11 @@ class ClockSampler:
             out = {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(smax)), "reasons": sorted(reasons),
                    "samples": len(sm)}
         return out
+
+
+def workload_name(args):
+    return (f"3-D Taylor-Green vortex, {args.nelem}^3 elements, ngl={args.ngl}, unit box "
+            "(BASELINE.json configs[1]); one RK5BS time step = 7 evalRHS")
 
 
 def case_config(nelem, ngl):
@@ -195,15 +199,21 @@ def run_b200(args, rank, world):
     vel = fem.solverKLE.getSolution()
     snap = {"vort": fem.vort.copy(), "vel": vel.copy(), "time": fem.ts.time, "step": fem.ts.step_number}
 
-    def prepare():
+    def prepare(warmup=None):
         snap["vort"].copy(fem.vort)
         snap["vel"].copy(vel)
         fem.ts.time, fem.ts.step_number, fem.ts._fsal_valid = snap["time"], snap["step"], False
         if args.fischer > 0:
             fem.solverKLE.solver.setUseFischerGuess(1, args.fischer)      # drops the basis
-        for _ in range(args.warmup):
+        for _ in range(args.warmup if warmup is None else warmup):
             one_step()
         ctx.sync()
+
+    # checksum: norms of the fields CHECK_STEPS steps after the initial condition -- the same number at
+    # every N (SCALE shows the N-rank runs computed the same fields) and in the CPU arm (cpu_baseline /
+    # --impl reference run the same steps on the same mesh)
+    prepare(CHECK_STEPS)
+    checksum = dict(field_checksum(fem.vort.getGlobalArray(), vel.getGlobalArray()), after_steps=CHECK_STEPS)
 
     restore = prepare
     prepare()
@@ -300,8 +310,7 @@ def run_b200(args, rank, world):
         "metric": METRIC, "value": ndof / (ms_per_step * 1e-3), "unit": UNIT, "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": f"3-D Taylor-Green vortex, {args.nelem}^3 elements, ngl={args.ngl}, unit box "
-                               "(BASELINE.json configs[1]); one RK5BS time step = 7 evalRHS",
+        "config": {"workload": workload_name(args),
                    "dofs": int(ndof), "nodes": int(ndof // 3), "ksp": f"cg+{args.pc}", "ksp_rtol": args.rtol,
                    "ksp_options": f"-ksp_type cg -pc_type {args.pc} -ksp_rtol {args.rtol:g}" +
                                   (f" -ksp_fischer_guess 1,{args.fischer}" if args.fischer > 0 else "") +
@@ -315,6 +324,7 @@ def run_b200(args, rank, world):
                     else "over NCCL") + f", {ctx.collectives()} collectives so far on rank 0",
                    "l2": "inputs larger than L2 (K = %.2f GB per SpMV)" % (spmv_bytes / 1e9)},
         "roofline": roofline,
+        "checksum": checksum,
         "kernel_time_ms_per_step": {"spmv_K_dot": ms_spmv / args.steps, "cg_update": ms_upd / args.steps,
                                     "cg_direction": ms_dir / args.steps, "spmv_other": ms_oth / args.steps},
         "assembly": assembly_report(asm, asm_kernels, fem, ndof, peak),
@@ -463,58 +473,88 @@ def read_traffic():
 # which is not installed) timed on the host cores.  Checker code, used here only as the
 # reported baseline / the --impl reference arm.
 # ---------------------------------------------------------------------------------------------
-def _oracle_pc(args):
-    """the oracle's name of the preconditioner this run uses (-pc_asm_coarse k > 0: two-level)"""
-    if args.pc == "none":
-        return "jacobi"
-    if args.pc == "asm" and any(kv.startswith("pc_asm_coarse=") and kv.split("=")[1] not in ("0", "") for kv in args.opt):
-        return "asm+coarse"
-    return args.pc
+CHECK_STEPS = 2          # the checksum is taken after this many steps from the initial condition
 
 
-def cpu_timestep(args, steps, warmup):
-    """one bounded sample: the same RK5BS time step on a (cpu_nelem)^3, ngl mesh with scipy CG +
-    the same preconditioner and tolerance; returns (DOF/s, ms_per_step, description)"""
-    from oracle import timestep
-    from pynama_b200.domain.box_mesh import BoxMesh
-    n = args.cpu_nelem
-    mesh = BoxMesh([n] * 3, [0, 0, 0], [1, 1, 1], args.ngl)
-    prob = timestep.OracleProblem(3, args.ngl, mesh.corner_xyz, mesh.elem_nodes, mesh.coords,
-                                  mesh.getBordersNodes(), rho=0.5, mu=0.01, solver="cg", rtol=args.rtol,
-                                  pc=_oracle_pc(args), fischer=args.fischer)
-    ndof = mesh.nnodes * 3
-    t, k0 = 0.0, None
-    for _ in range(max(warmup, 1)):
+def field_checksum(vort, vel):
+    """norms of the fields (numpy, whole vectors): compared between the GPU arm at every N and the CPU arm"""
+    return {"vort_l2": float(np.sqrt(vort @ vort)), "vel_l2": float(np.sqrt(vel @ vel)),
+            "vort_max": float(np.abs(vort).max())}
+
+
+def cpu_problem(args):
+    """the CPU restatement on the SAME mesh as the GPU arm: oracle/boxmesh.py tables, oracle/sem.py cell
+    matrices, oracle/ckle.c assembly + scalar-CSR products + CG on all host cores (oracle/cport.py).
+    No import of the product package."""
+    from oracle import boxmesh, cport
+    if args.pc not in ("jacobi", "bjacobi"):
+        raise SystemExit(f"the CPU arm has no '{args.pc}' preconditioner (jacobi, bjacobi); add --no-cpu-baseline")
+    t0 = time.perf_counter()
+    mesh = boxmesh.box_mesh([args.nelem] * 3, [0.0] * 3, [1.0] * 3, args.ngl)
+    prob = cport.CProblem(3, args.ngl, mesh.corner_xyz, mesh.elem_nodes, mesh.coords, mesh.border_nodes,
+                          rho=0.5, mu=0.01, rtol=args.rtol, pc=args.pc, fischer=args.fischer)
+    return prob, mesh.nnodes * 3, time.perf_counter() - t0, cport.threads()
+
+
+def cpu_run(args, steps, warmup, budget_s):
+    """W' <= warmup untimed and K' <= steps timed RK5BS steps of the full problem, cut short when the
+    wall-clock budget is spent (what ran is what is reported).  Returns a dict."""
+    prob, ndof, setup_s, cores = cpu_problem(args)
+    t_all = time.perf_counter()
+    t, k0, chk = 0.0, None, None
+    done_w = 0
+    for _ in range(warmup):
+        if done_w >= 1 and time.perf_counter() - t_all > 0.35 * budget_s:
+            break
         t, k0 = prob.step(t, args.dt, k0)
+        done_w += 1
+        if done_w == CHECK_STEPS:
+            chk = field_checksum(prob.vort, prob.vel)
     its0 = prob.iterations
     t0 = time.perf_counter()
+    done = 0
     for _ in range(steps):
+        if done >= 1 and time.perf_counter() - t_all > budget_s:
+            break
         t, k0 = prob.step(t, args.dt, k0)
+        done += 1
+        if done_w + done == CHECK_STEPS:
+            chk = field_checksum(prob.vort, prob.vel)
     wall = time.perf_counter() - t0
-    ms = wall / steps * 1e3
-    sample = (f"{steps} RK5BS step(s) of the same Taylor-Green problem on a {n}^3-element, ngl={args.ngl} box "
-              f"({ndof} dofs; the 16^3 mesh does not assemble in scipy within minutes), scipy CSR SpMV + "
-              f"scipy CG with {args.pc} to rtol {args.rtol:g}" +
-              (f" and the same Fischer guess (1,{args.fischer})" if args.fischer > 0 else "") +
-              f", {(prob.iterations - its0) / steps:.0f} CG its/step, "
-              f"{wall:.1f} s of CPU work")
-    return ndof / (ms * 1e-3), ms, sample
+    ms = wall / done * 1e3
+    its = (prob.iterations - its0) / done
+    sample = (f"{done} timed RK5BS step(s) after {done_w} warm-up step(s) of the SAME problem ({args.nelem}^3 elements, "
+              f"ngl={args.ngl}, {ndof} dofs): cell matrices from the numpy oracle, scatter-add assembly, scalar-CSR "
+              f"SpMV and CG + {args.pc} (rtol {args.rtol:g}" +
+              (f", Fischer guess 1,{args.fischer}" if args.fischer > 0 else "") +
+              f") in C + OpenMP on {cores} threads; {its:.0f} CG its/step, {wall:.1f} s timed, "
+              f"{setup_s:.1f} s set-up + assembly")
+    return {"value": ndof / (ms * 1e-3), "ms": ms, "sample": sample, "cores": cores, "steps": done,
+            "warmup": done_w, "its": its, "ndof": ndof, "setup_s": setup_s, "checksum": chk,
+            "K_nnz": int(prob.K.nnz)}
 
 
 def run_reference(args, rank, world):
+    """--impl reference: the reference's own implementation needs petsc4py + mpirun, which neither
+    machine has, so this arm times the CPU restatement of the path on all host
+    cores, on the same mesh, options and metric as the GPU arm."""
     if rank != 0:
         return None
-    steps, warmup = min(args.steps, 3), min(args.warmup, 1)
-    v, ms, sample = cpu_timestep(args, steps, warmup)
-    return {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": world,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
+    r = cpu_run(args, args.steps, args.warmup, budget_s=float(os.environ.get("PYN_CPU_BUDGET_S", "200")))
+    return {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": world,
+            "steps": r["steps"], "warmup": r["warmup"], "steps_requested": args.steps,
+            "warmup_requested": args.warmup, "ms_per_step": r["ms"], "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": f"3-D Taylor-Green vortex, {args.nelem}^3 elements, ngl={args.ngl}, unit box "
-                                   "(BASELINE.json configs[1]); one RK5BS time step = 7 evalRHS",
+            "config": {"workload": workload_name(args), "dofs": int(r["ndof"]), "ksp": f"cg+{args.pc}",
+                       "ksp_rtol": args.rtol, "dt": args.dt, "ksp_iterations_per_step": r["its"],
+                       "K_scalar_nnz": r["K_nnz"],
                        "note": "petsc4py/PETSc/mpirun are not installed: the reference's own modules cannot be "
-                               "imported; this arm times the CPU restatement (oracle/) of the same path"},
-            "cpu_baseline": {"value": v, "unit": UNIT, "cores": 1, "kind": "port", "sample": sample},
-            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                               "imported; this arm times the CPU restatement (oracle/) of the same path. steps / "
+                               "warmup are what actually ran inside the wall-clock budget"},
+            "checksum": dict(r["checksum"] or {}, after_steps=CHECK_STEPS),
+            "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port",
+                             "sample": r["sample"]},
+            "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
 
 
@@ -555,8 +595,14 @@ def main():
     else:
         out = run_b200(args, rank, world)
         if rank == 0 and world == 1 and not args.no_cpu_baseline:
-            v, ms, sample = cpu_timestep(args, 1, 1)
-            out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": 1, "kind": "port", "sample": sample}
+            r = cpu_run(args, 1, 1, budget_s=120.0)            # bounded sample: 1 warm-up + 1 timed step
+            out["cpu_baseline"] = {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port",
+                                   "sample": r["sample"]}
+            if r["checksum"] and out.get("checksum"):
+                g = out["checksum"]
+                out["cpu_baseline"]["checksum"] = r["checksum"]
+                out["cpu_baseline"]["checksum_rel_diff_vs_gpu"] = max(
+                    abs(g[k] - r["checksum"][k]) / abs(r["checksum"][k]) for k in r["checksum"])
     if rank == 0 and out is not None:
         print(json.dumps(out), flush=True)
     if world > 1:
