@@ -1,0 +1,185 @@
+"""B2: the reference's own callers run UNCHANGED on the drop-in layer.
+
+The reference's `src/cases/base_problem.py` and `src/solver/kle_solver.py` are imported as they are
+from $PYNAMA_REFERENCE (default /root/reference; skipped when absent -- the GPU box has no copy) with
+`petsc4py.PETSc` bound to `pynama_b200.petsc` and the package names they import (`domain`, `viewer`,
+`solver.ts_solver`, `matrices`, `functions`, `boundaries`) bound to the drop-in packages:
+
+* every method the two files call on Vec / Mat / KSP / PC / TS objects exists on the drop-in classes
+  (AST walk over the files, receivers recognised by name);
+* `BaseProblem.__init__`, `readMaterialData`, `setUpTimeSolver` run on the shim without a GPU;
+* with a GPU: `setUp`, `setUpSolver` (the reference's KleSolver/KspSolver on the drop-in KSP), one
+  `evalRHS` and one `ts.step()` give the fields of the repo's own mirror of the same case.
+"""
+import ast
+import importlib
+import importlib.util
+import os
+import sys
+import types
+
+import numpy as np
+import pytest
+
+REF = os.environ.get("PYNAMA_REFERENCE", "/root/reference")
+SRC = os.path.join(REF, "src")
+pytestmark = pytest.mark.skipif(not os.path.isfile(os.path.join(SRC, "cases", "base_problem.py")),
+                                reason="reference tree not present")
+
+ALIASES = {"domain": "pynama_b200.domain", "domain.domain": "pynama_b200.domain.domain",
+           "viewer": "pynama_b200.viewer", "viewer.paraviewer": "pynama_b200.viewer.paraviewer",
+           "matrices": "pynama_b200.matrices", "matrices.mat_fs": "pynama_b200.matrices.mat_fs",
+           "matrices.mat_ns": "pynama_b200.matrices.mat_ns", "functions": "pynama_b200.functions",
+           "boundaries": "pynama_b200.boundaries", "solver": None, "solver.ts_solver": "pynama_b200.solver.ts_solver"}
+
+
+def _load(name, path):
+    spec = importlib.util.spec_from_file_location(name, path)
+    mod = importlib.util.module_from_spec(spec)
+    sys.modules[name] = mod
+    spec.loader.exec_module(mod)
+    return mod
+
+
+@pytest.fixture(scope="module")
+def ref():
+    """the reference's base_problem / kle_solver modules, unmodified, on the shim"""
+    from pynama_b200 import petsc
+    saved = dict(sys.modules)
+    p4 = types.ModuleType("petsc4py")
+    p4.PETSc = petsc
+    p4.init = lambda *a, **k: None
+    petsc.TS = importlib.import_module("pynama_b200.ts").TS          # `from petsc4py.PETSc import TS`
+    sys.modules["petsc4py"] = p4
+    sys.modules["petsc4py.PETSc"] = petsc
+    m4 = types.ModuleType("mpi4py")
+    m4.MPI = None
+    sys.modules["mpi4py"] = m4
+    for alias, real in ALIASES.items():
+        if real is None:
+            pkg = types.ModuleType(alias)
+            pkg.__path__ = []
+            sys.modules[alias] = pkg
+        else:
+            sys.modules[alias] = importlib.import_module(real)
+    for fn in ("taylor_green", "taylor_green3d", "taylor_green_3d"):
+        sys.modules[f"functions.{fn}"] = importlib.import_module(f"pynama_b200.functions.{fn}")
+    common = types.ModuleType("common")
+    common.__path__ = []
+    sys.modules["common"] = common
+    _load("common.timer", os.path.join(SRC, "common", "timer.py"))             # the reference's own Timer
+    kle = _load("solver.kle_solver", os.path.join(SRC, "solver", "kle_solver.py"))
+    base = _load("ref_base_problem", os.path.join(SRC, "cases", "base_problem.py"))
+    yield types.SimpleNamespace(base=base, kle=kle)
+    for k in list(sys.modules):
+        if k not in saved:
+            del sys.modules[k]
+    sys.modules.update(saved)
+
+
+# receivers recognised by name in the two files -> drop-in class
+def _receiver_class(node):
+    """an (empty) instance of the drop-in class the receiver expression stands for, or None"""
+    from pynama_b200 import petsc
+    from pynama_b200.solver.ts_solver import TsSolver
+    src = ast.unparse(node)
+    vec = {"vel", "velFS", "vort", "rhs", "f", "proc", "self.vort", "self._Aux1", "self._VtensV", "self.__vel",
+           "self.__velFS", "vec", "exactVel", "exactVort", "exactConv", "exactDiff", "convective", "diffusive"}
+    if src in vec or src.startswith("self.operator.weig"):           # the lumped-mass Vecs (mat_fs.py:253-271)
+        return petsc.Vec()
+    if src.startswith("self.operator.") or src.startswith("self.mat.") and src.count(".") == 2 or src in ("K", "Kfs"):
+        return petsc.Mat()
+    if src in ("self.ts", "ts"):
+        return TsSolver()
+    if src in ("self.solver", "self.solverFS"):
+        return petsc.KSP()
+    if src == "pc":
+        return petsc.PC()
+    return None
+
+
+@pytest.mark.parametrize("rel", ["cases/base_problem.py", "solver/kle_solver.py", "solver/ts_solver.py"])
+def test_every_petsc_method_the_reference_calls_exists(rel):
+    from pynama_b200 import petsc
+    from pynama_b200.ts import TS
+    tree = ast.parse(open(os.path.join(SRC, rel)).read())
+    missing, seen = [], 0
+    defined_here = {n.name for n in ast.walk(tree) if isinstance(n, ast.FunctionDef)}     # e.g. KspSolver.createSolver
+    for node in ast.walk(tree):
+        if isinstance(node, ast.Attribute):
+            cls = _receiver_class(node.value)
+            if cls is not None and not node.attr.startswith("_") and node.attr not in defined_here:
+                seen += 1
+                if not hasattr(cls, node.attr):
+                    missing.append((type(cls).__name__, node.attr, node.lineno))
+    # methods the subclasses KspSolver(KSP) / TsSolver(TS) call on themselves
+    for node in ast.walk(tree):
+        if isinstance(node, ast.ClassDef) and node.bases and ast.unparse(node.bases[0]) in ("KSP", "TS"):
+            cls = petsc.KSP() if ast.unparse(node.bases[0]) == "KSP" else TS()
+            own = {n.name for n in node.body if isinstance(n, ast.FunctionDef)}
+            for sub in ast.walk(node):
+                if isinstance(sub, ast.Attribute) and ast.unparse(sub.value) == "self" and isinstance(sub.ctx, ast.Load):
+                    if sub.attr in own or sub.attr in ("logger", "comm", "rk_types"):
+                        continue
+                    seen += 1
+                    if not hasattr(cls, sub.attr):
+                        missing.append((type(cls).__name__, sub.attr, sub.lineno))
+    assert not missing, missing
+    assert seen >= (5 if rel.endswith("ts_solver.py") else 10)
+
+
+def _config(nelem=(3, 3, 3), ngl=3):
+    from pynama_b200.run_case import loadCase
+    cfg = loadCase("taylor-green3d")
+    cfg["domain"]["ngl"] = ngl
+    cfg["domain"]["box-mesh"]["nelem"] = list(nelem)
+    return cfg
+
+
+def test_reference_base_problem_constructs_on_the_shim(ref):
+    """__init__ -> readMaterialData -> setUpTimeSolver -> TsSolver(comm).setUpTimes / initSolver"""
+    from pynama_b200.solver.ts_solver import TsSolver
+    fem = ref.base.BaseProblem(_config(), case="taylor-green3d")
+    assert fem.rho == 0.5 and abs(fem.nu - fem.mu / fem.rho) < 1e-16
+    assert isinstance(fem.ts, TsSolver) and fem.ts.getType() == "rk" and fem.ts.getRKType() == "5bs"
+    assert fem.ts.getMaxTime() == _config()["time-solver"]["end-time"]
+    assert fem.comm.rank == 0
+    # the reference's KspSolver is a subclass of the drop-in KSP and skips its __init__ (kle_solver.py:51-52)
+    ksp = ref.kle.KspSolver()
+    assert ksp.logger is None and hasattr(ksp, "createSolver")
+
+
+@pytest.mark.gpu
+def test_reference_callers_run_unchanged_on_the_gpu(ref, tmp_path):
+    """setUp / setUpSolver / evalRHS / ts.step of the reference's BaseProblem + KleSolver, on the device
+    layer, against the repo's mirror of the same classes"""
+    from pynama_b200.cases.base_problem import BaseProblem as Mirror
+    from pynama_b200.petsc import Options
+    o = Options()
+    for k, v in (("ksp_type", "cg"), ("pc_type", "bjacobi"), ("ksp_rtol", 1e-13), ("ksp_max_it", 50000),
+                 ("ts_adapt_type", "none"), ("ts_dt", 2e-3)):
+        o.setValue(k, v)
+    o.delValue("ksp_fischer_guess")
+    cfg = _config()
+    cfg["save-dir"] = str(tmp_path)
+    fem = ref.base.BaseProblem(cfg, case="taylor-green3d")
+    fem.setUp()                                         # Domain, Paraviewer, createMesh
+    fem.setUpSolver()                                   # MatFS.build, KleSolver.setUp, initial conditions
+    assert type(fem.solverKLE).__module__ == "solver.kle_solver"          # the reference's class
+    mir = Mirror(_config(), case="taylor-green3d")
+    mir.setUp()
+    mir.setUpSolver()
+    f1, f2 = fem.vort.duplicate(), mir.vort.duplicate()
+    fem.evalRHS(fem.ts, 0.0, fem.vort, f1)
+    mir.evalRHS(mir.ts, 0.0, mir.vort, f2)
+    a, b = f1.getArray(), f2.getArray()
+    assert np.abs(a).max() > 0 and np.abs(a - b).max() <= 1e-9 * np.abs(b).max()
+    va, vb = fem.solverKLE.getSolution().getArray(), mir.solverKLE.getSolution().getArray()
+    assert np.abs(va - vb).max() <= 1e-10 * np.abs(vb).max()
+    # run_case.py:152-162: fem.ts.solve(fem.vort) -- two steps of it
+    for p in (fem, mir):
+        p.ts._post = None
+        p.ts.setMaxSteps(2)
+        p.ts.solve(p.vort)
+    assert fem.ts.getStepNumber() == 2
+    assert np.abs(fem.vort.getArray() - mir.vort.getArray()).max() <= 1e-9 * np.abs(mir.vort.getArray()).max()
