@@ -69,7 +69,9 @@ int pyn_prof_get(pyn_ctx* ctx, int cls, int64_t* count, double* total_ms);
 /* process-wide tuning knobs.  "ksp_check_every": Krylov iterations launched between two
  * polls of the device-side convergence flag (default 8).  "force_idx64": non-zero makes the
  * numeric assembly take its 64-bit index instantiation whatever the mesh size (the path that
- * meshes beyond 2^31 contributions / record offsets use; for parity tests on small meshes). */
+ * meshes beyond 2^31 contributions / record offsets use; for parity tests on small meshes).
+ * "asm_coarse_unfused": non-zero runs the coarse level of -pc_type asm as one restriction and
+ * steps+1 Chebyshev launches instead of the single cooperative launch (comparison / fallback). */
 int pyn_tune(const char* key, int value);
 /* page-locked host memory for the caller's staging buffers (cudaMallocHost) */
 int pyn_host_alloc(int64_t bytes, void** out);

@@ -94,6 +94,10 @@ int pyn_tune(const char* key, int value) {
     g_ksp_check_every = value;
     return PYN_OK;
   }
+  if (strcmp(key, "asm_coarse_unfused") == 0) {   // coarse level of pc asm as separate launches (comparison)
+    g_asm_coarse_unfused = value != 0;
+    return PYN_OK;
+  }
   if (strcmp(key, "force_idx64") == 0) {          // tests: take the 64-bit index instantiations on small meshes
     g_force_idx64 = value != 0;
     return PYN_OK;

@@ -14,12 +14,15 @@
 //                    L2), element-local results to ybuf
 //   asm_sum_kernel   per node: sum of the element-local results in ascending element order
 //                    (fixed order: run-to-run reproducible, no atomics), optionally r.z and z.z
+#include <cooperative_groups.h>
+
 #include "asm_pc.cuh"
 #include "asm_kernels.cuh"
 #include "spmv.cuh"
 #include "comm.cuh"
 
 namespace pyn {
+namespace cg = cooperative_groups;
 
 // Row-partitioned set-up: a rank that has to refuse (no twin for an incomplete element, too many
 // classes) must not leave the others waiting in the next collective -- all ranks fail together.
@@ -185,6 +188,110 @@ static int asm_setup_impl(pyn_ctx* ctx, pyn_mat* A, AsmPc* pc) {
   return PYN_OK;
 }
 
+// ---- fused coarse level ---------------------------------------------------------------------------
+// rc = P^T (keep r), then `steps` Chebyshev-Jacobi steps on Ac xc = rc, in one cooperative launch: one
+// warp per coarse vertex, lanes over the restriction list / over the blocks of the vertex' row of Ac
+// (27 on a box: one coalesced 1 944-byte run), fixed shuffle tree, grid.sync() between the steps.
+// Same arithmetic as asm_restrict_kernel + asm_cheb_kernel up to the order of the row sums; r2b
+// measured those at 18 + 6 x 23 us per apply (one THREAD per vertex walking its row).
+struct AsmCoarseArgs {
+  int64_t nv;
+  int steps;
+  const int64_t* rl_ptr;
+  const int32_t* rl_node;
+  const double* rl_w;
+  const double* keep;
+  const double* r;
+  const int64_t* ptr;
+  const int32_t* col;
+  const double* val;
+  const double* dinv;
+  const double* c1;
+  const double* c2;
+  double* rc;
+  double* xc;
+  double* d0;
+  double* d1;
+  const double* done;
+};
+
+template <int B>
+__global__ void __launch_bounds__(256)
+asm_coarse_fused_kernel(AsmCoarseArgs a) {
+  if (a.done && *a.done != 0.0) return;            // uniform over the grid: nobody reaches a barrier
+  cg::grid_group grid = cg::this_grid();
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  const double c2_0 = a.c2[0];
+  for (int64_t v = warp; v < a.nv; v += nwarps) {
+    double acc[B];
+#pragma unroll
+    for (int i = 0; i < B; ++i) acc[i] = 0.0;
+    for (int64_t k = a.rl_ptr[v] + lane; k < a.rl_ptr[v + 1]; k += 32) {
+      const int64_t n = a.rl_node[k];
+      const double w = a.rl_w[k];
+#pragma unroll
+      for (int i = 0; i < B; ++i) acc[i] += w * a.keep[n * B + i] * a.r[n * B + i];
+    }
+#pragma unroll
+    for (int i = 0; i < B; ++i)
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) acc[i] += __shfl_xor_sync(0xffffffffu, acc[i], o);
+    if (lane < B) {
+      double t = acc[0];
+#pragma unroll
+      for (int i = 1; i < B; ++i) t = lane == i ? acc[i] : t;
+      a.rc[v * B + lane] = t;
+      a.xc[v * B + lane] = 0.0;
+      a.d0[v * B + lane] = c2_0 * a.dinv[v * B + lane] * t;
+    }
+  }
+  double* dold = a.d0;
+  double* dnew = a.d1;
+  for (int s = 1; s <= a.steps; ++s) {
+    grid.sync();
+    const double c1 = a.c1[s], c2 = a.c2[s];
+    const bool last = s == a.steps;
+    for (int64_t v = warp; v < a.nv; v += nwarps) {
+      double ad[B];
+#pragma unroll
+      for (int i = 0; i < B; ++i) ad[i] = 0.0;
+      for (int64_t k = a.ptr[v] + lane; k < a.ptr[v + 1]; k += 32) {
+        const double* blk = a.val + k * B * B;
+        const double* d = dold + (int64_t)a.col[k] * B;
+        double dv[B];
+#pragma unroll
+        for (int j = 0; j < B; ++j) dv[j] = __ldcg(d + j);          // written by other SMs before the barrier
+#pragma unroll
+        for (int i = 0; i < B; ++i)
+#pragma unroll
+          for (int j = 0; j < B; ++j) ad[i] += blk[i * B + j] * dv[j];
+      }
+#pragma unroll
+      for (int i = 0; i < B; ++i)
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) ad[i] += __shfl_xor_sync(0xffffffffu, ad[i], o);
+      if (lane < B) {
+        double t = ad[0];
+#pragma unroll
+        for (int i = 1; i < B; ++i) t = lane == i ? ad[i] : t;
+        const int64_t q = v * B + lane;
+        const double dvv = __ldcg(dold + q);
+        a.xc[q] += dvv;
+        if (!last) {
+          const double rn = a.rc[q] - t;
+          a.rc[q] = rn;
+          dnew[q] = c1 * dvv + c2 * a.dinv[q] * rn;
+        }
+      }
+    }
+    double* tmp = dold;
+    dold = dnew;
+    dnew = tmp;
+  }
+}
+
 template <int B>
 static AsmProlong asm_prolong_args(const AsmPc* pc, const double* xc) {
   AsmProlong cp;
@@ -279,6 +386,44 @@ static int asm_coarse_setup(pyn_ctx* ctx, pyn_mat* A, AsmPc* pc) {
   PYN_CHECK(pc->ac_val.upload(val.data(), nnzb * B * B));
   PYN_CHECK(pc->ac_dinv.alloc(ctx, nv * B));
   PYN_CHECK(pc->ac_dinv.upload(dinv.data(), nv * B));
+  // restriction lists of the fused kernel: what asm_restrict_kernel visits (a fine node contributes
+  // through its first element only), vertex by vertex, elements then local nodes ascending
+  {
+    std::vector<int64_t> first((size_t)nnodes, -1);
+    for (int64_t k = nel * nn - 1; k >= 0; --k) first[(size_t)en[(size_t)k]] = k;     // lowest (e, a) wins
+    std::vector<int64_t> rl_ptr((size_t)nv + 1, 0);
+    std::vector<int32_t> rl_node;
+    std::vector<double> rl_w;
+    for (int64_t v = 0; v < nv; ++v) {
+      for (int64_t k = T.v2e_ptr[(size_t)v]; k < T.v2e_ptr[(size_t)v + 1]; ++k) {
+        const int64_t e = T.v2e[(size_t)(2 * k)];
+        const int c = T.v2e[(size_t)(2 * k + 1)];
+        for (int a = 0; a < nn; ++a) {
+          const double w = phi[(size_t)(a * ncorner + c)];
+          if (w == 0.0 || first[(size_t)en[(size_t)(e * nn + a)]] != e * nn + a) continue;
+          rl_node.push_back(en[(size_t)(e * nn + a)]);
+          rl_w.push_back(w);
+        }
+      }
+      rl_ptr[(size_t)v + 1] = (int64_t)rl_node.size();
+    }
+    PYN_CHECK(pc->rl_ptr.alloc(ctx, nv + 1));
+    PYN_CHECK(pc->rl_ptr.upload(rl_ptr.data(), nv + 1));
+    PYN_CHECK(pc->rl_node.alloc(ctx, (int64_t)rl_node.size() + 1));
+    PYN_CHECK(pc->rl_node.upload(rl_node.data(), (int64_t)rl_node.size()));
+    PYN_CHECK(pc->rl_w.alloc(ctx, (int64_t)rl_w.size() + 1));
+    PYN_CHECK(pc->rl_w.upload(rl_w.data(), (int64_t)rl_w.size()));
+    std::vector<double> cc;
+    cc.insert(cc.end(), pc->c1.begin(), pc->c1.end());
+    cc.insert(cc.end(), pc->c2.begin(), pc->c2.end());
+    PYN_CHECK(pc->cheb_c.alloc(ctx, (int64_t)cc.size()));
+    PYN_CHECK(pc->cheb_c.upload(cc.data(), (int64_t)cc.size()));
+    int per_sm = 0;
+    PYN_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, asm_coarse_fused_kernel<B>, 256, 0));
+    const int64_t want = (nv * 32 + 255) / 256;
+    const int64_t cap = (int64_t)per_sm * ctx->num_sms;
+    pc->coarse_grid = (int)std::max<int64_t>(1, std::min(want, cap));
+  }
   PYN_CUDA(cudaStreamSynchronize(ctx->stream));
   return PYN_OK;
 }
@@ -324,7 +469,33 @@ static int asm_apply_impl(pyn_ctx* ctx, AsmPc* pc, double* r, double* z, double*
       pc->ybuf.p, done);
   PYN_LAUNCHED(ctx);
   const double* xc = nullptr;
-  if (pc->coarse_steps > 0) {                  // xc ~ Ac^-1 P^T r by coarse_steps Chebyshev steps
+  const bool unfused = g_asm_coarse_unfused;     // pyn_tune("asm_coarse_unfused"): the seven-launch path (r2a)
+  if (pc->coarse_steps > 0 && !unfused) {     // restriction + all Chebyshev steps in ONE cooperative launch
+    AsmCoarseArgs ca;
+    ca.nv = pc->nv;
+    ca.steps = pc->coarse_steps;
+    ca.rl_ptr = pc->rl_ptr.p;
+    ca.rl_node = pc->rl_node.p;
+    ca.rl_w = pc->rl_w.p;
+    ca.keep = pc->keep.p;
+    ca.r = r;
+    ca.ptr = pc->ac_ptr.p;
+    ca.col = pc->ac_col.p;
+    ca.val = pc->ac_val.p;
+    ca.dinv = pc->ac_dinv.p;
+    ca.c1 = pc->cheb_c.p;
+    ca.c2 = pc->cheb_c.p + (pc->coarse_steps + 1);
+    ca.rc = pc->rc.p;
+    ca.xc = pc->xc.p;
+    ca.d0 = pc->d0.p;
+    ca.d1 = pc->d1.p;
+    ca.done = done;
+    void* args[] = {&ca};
+    PYN_CUDA(cudaLaunchCooperativeKernel((const void*)asm_coarse_fused_kernel<B>, dim3(pc->coarse_grid), dim3(256),
+                                         args, 0, ctx->stream));
+    PYN_LAUNCHED(ctx);
+    xc = pc->xc.p;
+  } else if (pc->coarse_steps > 0) {           // xc ~ Ac^-1 P^T r by coarse_steps Chebyshev steps
     PYN_CHECK(asm_restrict<B>(ctx, pc, r, pc->rc.p, done));
     const int gridc = grid_for(ctx, pc->nv, 256);
     double* dold = pc->d0.p;

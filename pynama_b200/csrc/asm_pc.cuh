@@ -38,6 +38,13 @@ struct AsmPc {
   DevBuf<int32_t> ac_col;
   DevBuf<double> ac_val, ac_dinv;
   DevBuf<double> rc, xc, d0, d1;
+  // restriction as explicit lists (fused coarse kernel): vertex v gathers w * keep * r over
+  // rl_node / rl_w [rl_ptr[v], rl_ptr[v+1]) -- the entries asm_restrict_kernel visits, in its order
+  DevBuf<int64_t> rl_ptr;
+  DevBuf<int32_t> rl_node;
+  DevBuf<double> rl_w;
+  DevBuf<double> cheb_c;           // [2][steps+1] Chebyshev coefficients c1, c2 on the device
+  int coarse_grid = 0;             // co-resident grid of the fused kernel (cooperative launch)
   std::vector<double> c1, c2;      // Chebyshev coefficients (asm_host.cuh)
 };
 

@@ -22,6 +22,7 @@
 namespace pyn {
 int g_ksp_check_every = 8;
 bool g_force_idx64 = false;
+bool g_asm_coarse_unfused = false;
 
 // device scalar block
 enum {

@@ -2,10 +2,8 @@
 the C ABI: same solutions as the direct solve of the oracle system, iteration counts of the
 oracle's CG with the same preconditioner, fewer iterations than node-block Jacobi.
 
-The preconditioner was written after this round's GPU minutes were spent: its kernels have run
-only under the CPU emulation (tests/test_asm_emulated.py).  Until a GPU run has confirmed them
-these tests are opt-in (PYN_TEST_ASM=1), so that an unconfirmed feature cannot take the GPU
-suite down; the product default (bjacobi) does not touch this code."""
+First run on a B200 in round 2 (gpurun_out r2a / r2b: all single-GPU cases green); since then part of
+the normal GPU suite.  The kernels are also exercised on CPU threads by tests/test_asm_emulated.py."""
 import os
 
 import numpy as np
@@ -15,9 +13,7 @@ import scipy.sparse.linalg as spl
 from oracle import assembly, sem, timestep
 from tests.util import fs_classes
 
-pytestmark = [pytest.mark.gpu,
-              pytest.mark.skipif(os.environ.get("PYN_TEST_ASM") != "1",
-                                 reason="pc asm not yet confirmed on a GPU: set PYN_TEST_ASM=1 to run")]
+pytestmark = pytest.mark.gpu
 
 
 def _setup(nelem, ngl, perturb=0.0):
@@ -142,6 +138,33 @@ def test_cg_two_level_asm_vs_direct(nelem, ngl, perturb):
         ksp.solve(Vec().createWithArray(b), x2)
         assert np.array_equal(x.getArray(), x2.getArray())
     assert its[5] <= its[0] + 3, its            # (small meshes: little for the coarse space to do)
+
+
+@pytest.mark.parametrize("nelem,ngl", [([4, 4, 4], 3), ([3, 4, 5], 4), ([7, 5], 4)])
+def test_fused_coarse_level_equals_the_separate_launches(nelem, ngl):
+    """one cooperative launch (restriction + all Chebyshev steps, a warp per coarse vertex) against the
+    seven-launch path it replaces: same iterates up to the order of the row sums"""
+    from pynama_b200 import _lib
+    from pynama_b200.petsc import Vec
+    mesh, dm, mats, want = _setup(nelem, ngl)
+    n = mesh.nnodes * len(nelem)
+    b = np.random.default_rng(21).uniform(-1, 1, n)
+    res = {}
+    for unfused in (1, 0):
+        _lib.call("pyn_tune", b"asm_coarse_unfused", unfused)
+        try:
+            ksp = _ksp(mats["K"], "cg", "asm", 1e-11, setASMCoarse=(5,))
+            x = Vec(n)
+            ksp.solve(Vec().createWithArray(b), x)
+            assert ksp.getConvergedReason() > 0
+            res[unfused] = (x.getArray(), ksp.getIterationNumber())
+            x2 = Vec(n)
+            ksp.solve(Vec().createWithArray(b), x2)
+            assert np.array_equal(x2.getArray(), res[unfused][0])            # reproducible
+        finally:
+            _lib.call("pyn_tune", b"asm_coarse_unfused", 0)
+    assert abs(res[0][1] - res[1][1]) <= 1
+    assert np.abs(res[0][0] - res[1][0]).max() <= 1e-8 * np.abs(res[1][0]).max()
 
 
 @pytest.mark.parametrize("ktype", ["gmres", "bcgs"])
