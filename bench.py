@@ -55,6 +55,8 @@ def parse_args():
                     help="-ksp_fischer_guess 1,<n>: initial guess from the last n solutions (0: off, PETSc default)")
     ap.add_argument("--opt", action="append", default=[], metavar="NAME=VALUE",
                     help="extra options-database entry, e.g. --opt ksp_cg_single_reduction=1 (repeatable)")
+    ap.add_argument("--tune", action="append", default=[], metavar="KEY=INT",
+                    help="pyn_tune(key, value) before the run, e.g. --tune halo_wait_at_start=1 (repeatable)")
     ap.add_argument("--check-every", type=int, default=0, help="KSP status poll interval (0: library default)")
     return ap.parse_args()
 
@@ -179,6 +181,9 @@ def run_b200(args, rank, world):
     ctx = Context.get()
     if args.check_every > 0:
         _lib.call("pyn_tune", b"ksp_check_every", args.check_every)
+    for kv in args.tune:
+        key, _, val = kv.partition("=")
+        _lib.call("pyn_tune", key.encode(), int(val or "1"))
     ctx.prof_enable(True)
     fem = build_problem(args)
     asm_kernels = {k: ctx.prof_get(k) for k in ("elem_kle", "numeric")}

@@ -71,7 +71,9 @@ int pyn_prof_get(pyn_ctx* ctx, int cls, int64_t* count, double* total_ms);
  * numeric assembly take its 64-bit index instantiation whatever the mesh size (the path that
  * meshes beyond 2^31 contributions / record offsets use; for parity tests on small meshes).
  * "asm_coarse_unfused": non-zero runs the coarse level of -pc_type asm as one restriction and
- * steps+1 Chebyshev launches instead of the single cooperative launch (comparison / fallback). */
+ * steps+1 Chebyshev launches instead of the single cooperative launch (comparison / fallback).
+ * "halo_wait_at_start": non-zero makes the fused-halo product wait for the ghost entries at CTA
+ * start (round 1) instead of interior rows first / wait before the first boundary row. */
 int pyn_tune(const char* key, int value);
 /* page-locked host memory for the caller's staging buffers (cudaMallocHost) */
 int pyn_host_alloc(int64_t bytes, void** out);

@@ -98,6 +98,10 @@ int pyn_tune(const char* key, int value) {
     g_asm_coarse_unfused = value != 0;
     return PYN_OK;
   }
+  if (strcmp(key, "halo_wait_at_start") == 0) {   // fused halo: wait for the ghosts at CTA start (round 1)
+    g_halo_wait_at_start = value != 0;
+    return PYN_OK;
+  }
   if (strcmp(key, "force_idx64") == 0) {          // tests: take the 64-bit index instantiations on small meshes
     g_force_idx64 = value != 0;
     return PYN_OK;

@@ -233,6 +233,7 @@ int pyn_mat_set_halo(pyn_mat* m, pyn_halo* h) {
               "pyn_mat_set_halo: layout has %lld local nodes, matrix is %lld x %lld", h ? (long long)h->n_loc : 0LL,
               (long long)m->nbrows, (long long)m->nbcols);
   m->halo = h;
+  if (h) PYN_CHECK(pyn::spmv_build_row_order(m));
   return PYN_OK;
 }
 int pyn_mat_set_matfree(pyn_mat* m, int on) {

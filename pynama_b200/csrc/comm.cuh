@@ -183,6 +183,20 @@ __device__ __forceinline__ bool halo_wait_cta(const HaloWait& h) {
   __syncthreads();
   return halo_ok_sm != 0;
 }
+// all lanes of a warp call; the lanes below nneigh spin on one flag each.  A timeout raises the flag
+// the host reads and lets the warp go on (the solve ends with reason -100).
+__device__ __forceinline__ void halo_wait_warp(const HaloWait& h) {
+  const int lane = threadIdx.x & 31;
+  for (int j = lane; j < h.nneigh; j += 32) {
+    long long spins = 0;
+    while (ld_acquire_sys(halo_flag(h.win, (int)(h.seq & 1ull), h.ranks[j])) < h.seq)
+      if (++spins > kSpinMax) {
+        *h.timeout_flag = 1;
+        break;
+      }
+  }
+  __syncwarp();
+}
 #endif
 }  // namespace pyn
 

@@ -59,6 +59,7 @@ constexpr int kNumSMs = 148;  // B200: 2 dies x 74 SMs
 extern int g_ksp_check_every;
 extern bool g_force_idx64;
 extern bool g_asm_coarse_unfused;
+extern bool g_halo_wait_at_start;
 
 }  // namespace pyn
 

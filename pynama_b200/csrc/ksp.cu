@@ -23,6 +23,7 @@ namespace pyn {
 int g_ksp_check_every = 8;
 bool g_force_idx64 = false;
 bool g_asm_coarse_unfused = false;
+bool g_halo_wait_at_start = false;
 
 // device scalar block
 enum {
@@ -547,6 +548,7 @@ struct pyn_ksp {
   double rtol = 1e-5, atol = 1e-50, dtol = 1e5;
   int maxit = 10000, restart = 30;
   int check_every = pyn::g_ksp_check_every;
+  int last_its = -1;              // iterations of the previous solve: sizes the first chunk of the next
   int B = 0;
   int64_t n = 0, nnodes = 0;
   DevBuf<double> pcd, r, z, p, w, S, tmp2;
@@ -671,7 +673,15 @@ static int ksp_solve_cg(pyn_ksp* k, const double* b, double* x, int* its, int* r
   // chunk c runs, so the GPU never idles on the host.
   int it = 0;
   for (int chunk = 0;; ++chunk) {
-    const int todo = (k->maxit - it) < k->check_every ? (k->maxit - it) : k->check_every;
+    // Successive KLE systems need about the same number of iterations, so the first chunk runs to
+    // just short of the previous count and the following ones are short: iterations launched after
+    // convergence return at once but still cost their launches (r2c: ~7 iterations per solve under
+    // the two-level preconditioner, up to 9 dead iterations of 7 launches each in chunks of 8).
+    // Every rank sees the same counts, so the launch sequences stay identical across ranks.
+    const int tail = std::max(1, std::min(k->check_every, asmpc ? 2 : 4));
+    const int first = k->last_its > 2 ? std::min(k->last_its - 1, 4 * k->check_every) : k->check_every;
+    const int want = chunk == 0 ? first : tail;
+    const int todo = (k->maxit - it) < want ? (k->maxit - it) : want;
     for (int j = 0; j < todo; ++j, ++it) {
       const int parity = it & 1;
       P2PRed red = p2p ? p2p_next(ctx) : red_off;
@@ -779,6 +789,7 @@ static int ksp_solve_cg(pyn_ksp* k, const double* b, double* x, int* its, int* r
   PYN_CUDA(cudaStreamSynchronize(ctx->stream));
   if (fischer && k->status_host[S_COUNT] != 0.0) k->fischer_n++;
   const double* st = k->status_host;
+  k->last_its = (int)st[S_ITS];
   if (its) *its = (int)st[S_ITS];
   if (reason) *reason = st[S_DONE] != 0.0 ? (int)st[S_REASON] : -3;
   if (rnorm) *rnorm = st[S_RNORM];

@@ -37,8 +37,10 @@ spmv_kernel(int64_t nbrows, const int64_t* __restrict__ rowptr, const int32_t* _
   if (fuse.skip && *fuse.skip != 0.0) return;
   const double* xg = nullptr;          // ghost section of x in the halo window (fused exchange)
   int64_t n_own = 0;
+  const int32_t* __restrict__ order = fuse.hw.win ? fuse.order : nullptr;
+  bool waited = order == nullptr;      // deferred, per warp, to the first boundary row
   if (fuse.hw.win) {
-    if (!halo_wait_cta(fuse.hw)) return;
+    if (!order && !halo_wait_cta(fuse.hw)) return;
     xg = halo_buf(fuse.hw.win, (int)(fuse.hw.seq & 1ull), fuse.hw.nghost, fuse.hw.max_bs);
     n_own = fuse.hw.n_own;
   }
@@ -49,17 +51,23 @@ spmv_kernel(int64_t nbrows, const int64_t* __restrict__ rowptr, const int32_t* _
   const int64_t grp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / G;
   const int64_t ngrp = ((int64_t)gridDim.x * blockDim.x) / G;
   const int64_t iters = (nbrows + ngrp - 1) / ngrp;
-  int64_t r = grp;
+  int64_t r = grp;                     // position in the walk; ra: the row itself
   bool live = r < nbrows;
-  int64_t p0 = live ? rowptr[r] : 0;
-  int nb = live ? (int)(rowptr[r + 1] - p0) : 0;
+  int64_t ra = live ? (order ? (int64_t)order[r] : r) : 0;
+  int64_t p0 = live ? rowptr[ra] : 0;
+  int nb = live ? (int)(rowptr[ra + 1] - p0) : 0;
   int32_t cnext = lane < nb ? colidx[p0 + lane] : 0;
   for (int64_t it = 0; it < iters; ++it) {
     // next row's extent, fetched early
     const int64_t rn = r + ngrp;
     const bool liven = rn < nbrows;
-    const int64_t p0n = liven ? rowptr[rn] : 0;
-    const int nbn = liven ? (int)(rowptr[rn + 1] - p0n) : 0;
+    const int64_t ran = liven ? (order ? (int64_t)order[rn] : rn) : 0;
+    const int64_t p0n = liven ? rowptr[ran] : 0;
+    const int nbn = liven ? (int)(rowptr[ran + 1] - p0n) : 0;
+    if (!waited && __any_sync(0xffffffffu, live && r >= fuse.n_int)) {
+      halo_wait_warp(fuse.hw);
+      waited = true;
+    }
     const double* __restrict__ v = val + p0 * BB;
     double acc[BR];
 #pragma unroll
@@ -89,19 +97,20 @@ spmv_kernel(int64_t nbrows, const int64_t* __restrict__ rowptr, const int32_t* _
     for (int i = 0; i < BR; ++i) {
       if (live && lane == i % G) {
         double out = alpha * acc[i];
-        if (beta != 0.0) out += beta * z[r * BR + i];
-        y[r * BR + i] = out;
+        if (beta != 0.0) out += beta * z[ra * BR + i];
+        y[ra * BR + i] = out;
         if (NDOT > 0) {
-          const double xr = x[r * BC + i];
+          const double xr = x[ra * BC + i];
           dotacc[0] += out * xr;
           if (NDOT == 3) {
-            dotacc[NV > 1 ? 1 : 0] += fuse.dot_r[r * BR + i] * xr;
+            dotacc[NV > 1 ? 1 : 0] += fuse.dot_r[ra * BR + i] * xr;
             dotacc[NV > 2 ? 2 : 0] += xr * xr;
           }
         }
       }
     }
     r = rn;
+    ra = ran;
     live = liven;
     p0 = p0n;
     nb = nbn;
@@ -124,6 +133,10 @@ static int spmv_launch(pyn_mat* m, double alpha, const double* x, double beta, c
     if (!fuse.hw.win) PYN_CHECK(halo_exchange(m->halo, const_cast<double*>(x), m->bc));
     nrows = m->halo->n_own;
     if (nrows == 0) return PYN_OK;
+  }
+  if (fuse.hw.win && m->n_interior >= 0 && !g_halo_wait_at_start) {
+    fuse.order = m->row_order.p;
+    fuse.n_int = m->n_interior;
   }
   if (m->mf) return matfree_apply(m, nrows, alpha, x, beta, z, y, dot, fuse);
   const double avg = m->nbrows ? (double)m->nblocks / (double)m->nbrows : 0.0;
@@ -161,6 +174,45 @@ static int spmv_launch(pyn_mat* m, double alpha, const double* x, double beta, c
 #undef LAUNCH
   prof_end(ctx);
   PYN_LAUNCHED(ctx);
+  return PYN_OK;
+}
+
+// flag[r] = 1 when row r holds a column >= n_own (one warp per row)
+__global__ void ghost_rows_kernel(int64_t nrows, int64_t n_own, const int64_t* __restrict__ rowptr,
+                                  const int32_t* __restrict__ colidx, uint8_t* __restrict__ flag) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  for (int64_t r = warp; r < nrows; r += nwarps) {
+    bool g = false;
+    for (int64_t k = rowptr[r] + lane; k < rowptr[r + 1]; k += 32) g |= colidx[k] >= n_own;
+    g = __any_sync(0xffffffffu, g);
+    if (lane == 0) flag[r] = g ? 1 : 0;
+  }
+}
+
+int spmv_build_row_order(pyn_mat* m) {
+  pyn_ctx* ctx = m->ctx;
+  m->n_interior = -1;
+  if (!m->halo || m->halo->n_own <= 0 || m->nblocks == 0) return PYN_OK;
+  const int64_t n_own = m->halo->n_own;
+  DevBuf<uint8_t> flag;
+  PYN_CHECK(flag.alloc(ctx, n_own));
+  ghost_rows_kernel<<<grid_for(ctx, n_own * 32, 256), 256, 0, ctx->stream>>>(n_own, n_own, m->rowptr.p,
+                                                                              m->colidx.p, flag.p);
+  PYN_LAUNCHED(ctx);
+  std::vector<uint8_t> f((size_t)n_own);
+  PYN_CHECK(flag.download(f.data(), n_own));
+  std::vector<int32_t> order;
+  order.reserve((size_t)n_own);
+  for (int64_t r = 0; r < n_own; ++r)
+    if (!f[(size_t)r]) order.push_back((int32_t)r);
+  const int64_t n_int = (int64_t)order.size();
+  for (int64_t r = 0; r < n_own; ++r)
+    if (f[(size_t)r]) order.push_back((int32_t)r);
+  PYN_CHECK(m->row_order.alloc(ctx, n_own));
+  PYN_CHECK(m->row_order.upload(order.data(), n_own));
+  m->n_interior = n_int;
   return PYN_OK;
 }
 
