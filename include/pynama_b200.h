@@ -73,7 +73,9 @@ int pyn_prof_get(pyn_ctx* ctx, int cls, int64_t* count, double* total_ms);
  * "asm_coarse_unfused": non-zero runs the coarse level of -pc_type asm as one restriction and
  * steps+1 Chebyshev launches instead of the single cooperative launch (comparison / fallback).
  * "halo_wait_at_start": non-zero makes the fused-halo product wait for the ghost entries at CTA
- * start (round 1) instead of interior rows first / wait before the first boundary row. */
+ * start (round 1) instead of interior rows first / wait before the first boundary row.
+ * "ksp_adaptive_chunks": 0 launches CG iterations in fixed chunks of ksp_check_every between status
+ * polls (round 1); default 1 sizes the first chunk from the previous solve's iteration count. */
 int pyn_tune(const char* key, int value);
 /* page-locked host memory for the caller's staging buffers (cudaMallocHost) */
 int pyn_host_alloc(int64_t bytes, void** out);

@@ -277,6 +277,12 @@ class OracleProblem:
 SIDE_AXIS = {"left": 0, "right": 0, "down": 1, "up": 1, "back": 2, "front": 2}   # boundary.py:151-162
 
 
+def side_axis(name):
+    """boundary.py:151-162 for the box names; borders beyond those (a body wall) name their normal axis
+    by a -x / -y / -z suffix"""
+    return SIDE_AXIS[name] if name in SIDE_AXIS else "xyz".index(name[-1])
+
+
 def ns_dof_classes(sides, side_nodes, nnodes, dim):
     """velocity dof classes of an all-no-slip box (0 free, 2 normal, 3 tangential).
 
@@ -286,7 +292,7 @@ def ns_dof_classes(sides, side_nodes, nnodes, dim):
     (mat_ns.py:59-62)."""
     tang, normal, remove = set(), set(), set()
     for s in sides:
-        ax = SIDE_AXIS[s]
+        ax = side_axis(s)
         nodes = np.asarray(side_nodes[s], dtype=np.int64)
         for d in range(dim):
             if d != ax:
@@ -343,7 +349,7 @@ class OracleProblemNS:
         v = self.velfs.reshape(-1, dim)                                                          # :121-122
         for s in self.sides:                    # setTangentialValuesToVec, boundary_conditions.py:262-277
             for d in range(dim):
-                if d != SIDE_AXIS[s]:
+                if d != side_axis(s):
                     v[self.side_nodes[s], d] = self.wall_vel[s][d]
         self.vort = self.ops["Curl"] @ self.velfs                                                # :123
         self.vel = self._lu.solve(m["Rw"] @ self.vort + m["Krhs"] @ self.vel)                    # :125

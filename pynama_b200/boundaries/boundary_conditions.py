@@ -26,11 +26,22 @@ from ..petsc import COMM_WORLD
 NORMAL_OF = {"left": 0, "right": 0, "up": 1, "down": 1, "front": 2, "back": 2}
 
 
+def normal_axis(name):
+    """normal direction of a side: the reference's table for the box names (boundary.py:151-152); a
+    border beyond those (the wall of a body) carries its normal axis as a suffix,
+    `<name>-x`, `<name>-y`, `<name>-z`"""
+    if name in NORMAL_OF:
+        return NORMAL_OF[name]
+    if len(name) > 2 and name[-2] == "-" and name[-1] in "xyz":
+        return "xyz".index(name[-1])
+    raise KeyError(f"border '{name}': not a box side and no -x/-y/-z suffix naming its normal axis")
+
+
 class Directions:
     dirs = NORMAL_OF
 
     def __init__(self, name, dim):
-        self._normal = self.dirs[name]
+        self._normal = normal_axis(name)
         self._tangs = [d for d in range(dim) if d != self._normal]
 
     def getNormal(self):
@@ -150,7 +161,7 @@ class BoundaryConditions:
         self._byType = {"free-slip": [], "no-slip": []}
         self._needsCoords = []
         self._borderNames = list(sides)
-        self._dim = 2 if len(sides) == 4 else 3
+        self._dim = 3 if ("front" in sides or "back" in sides) else 2      # (the reference: 2 if len(sides) == 4)
         self._plans = {}
         self._scatter = {}
         self._prefetched = {}

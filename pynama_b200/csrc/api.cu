@@ -102,6 +102,10 @@ int pyn_tune(const char* key, int value) {
     g_halo_wait_at_start = value != 0;
     return PYN_OK;
   }
+  if (strcmp(key, "ksp_adaptive_chunks") == 0) {  // 0: fixed chunks of ksp_check_every iterations (round 1)
+    g_ksp_adaptive_chunks = value != 0;
+    return PYN_OK;
+  }
   if (strcmp(key, "force_idx64") == 0) {          // tests: take the 64-bit index instantiations on small meshes
     g_force_idx64 = value != 0;
     return PYN_OK;

@@ -421,8 +421,9 @@ static int asm_coarse_setup(pyn_ctx* ctx, pyn_mat* A, AsmPc* pc) {
     int per_sm = 0;
     PYN_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, asm_coarse_fused_kernel<B>, 256, 0));
     const int64_t want = (nv * 32 + 255) / 256;
-    // one CTA per SM: grid.sync() costs grow with the CTA count (r2c: 614 CTAs, 52 us for 6 phases)
-    const int64_t cap = per_sm > 0 ? (int64_t)ctx->num_sms : 0;
+    // (r2d: one CTA per SM instead of the full co-resident grid made the apply ~90 us slower: a warp
+    // then walks four vertices one after the other; the barriers are the smaller cost)
+    const int64_t cap = (int64_t)per_sm * ctx->num_sms;
     pc->coarse_grid = (int)std::max<int64_t>(1, std::min(want, cap));
   }
   PYN_CUDA(cudaStreamSynchronize(ctx->stream));

@@ -60,6 +60,7 @@ extern int g_ksp_check_every;
 extern bool g_force_idx64;
 extern bool g_asm_coarse_unfused;
 extern bool g_halo_wait_at_start;
+extern bool g_ksp_adaptive_chunks;
 
 }  // namespace pyn
 

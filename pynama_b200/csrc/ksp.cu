@@ -24,6 +24,7 @@ int g_ksp_check_every = 8;
 bool g_force_idx64 = false;
 bool g_asm_coarse_unfused = false;
 bool g_halo_wait_at_start = false;
+bool g_ksp_adaptive_chunks = true;
 
 // device scalar block
 enum {
@@ -680,7 +681,7 @@ static int ksp_solve_cg(pyn_ksp* k, const double* b, double* x, int* its, int* r
     // Every rank sees the same counts, so the launch sequences stay identical across ranks.
     const int tail = std::max(1, std::min(k->check_every, asmpc ? 2 : 4));
     const int first = k->last_its > 2 ? std::min(k->last_its - 1, 4 * k->check_every) : k->check_every;
-    const int want = chunk == 0 ? first : tail;
+    const int want = !g_ksp_adaptive_chunks ? k->check_every : (chunk == 0 ? first : tail);
     const int todo = (k->maxit - it) < want ? (k->maxit - it) : want;
     for (int j = 0; j < todo; ++j, ++it) {
       const int parity = it & 1;

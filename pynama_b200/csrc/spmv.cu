@@ -26,7 +26,10 @@ namespace pyn {
 // producer warp (cp.async.bulk + mbarrier, 128 KB ring) was correct but 6x slower -- 16
 // consumer warps each holding a whole row (<= 24.7 KB) span more than the ring, so the
 // warps serialise (profiles/README.md, round 1).
-template <int BR, int BC, int G, int NDOT>
+// ORD: rows walked through fuse.order (row-partitioned matrices with the fused halo); a separate
+// instantiation, so that the one-GPU kernel keeps the exact code it was tuned with (r2d: the order
+// state in the common kernel cost 11 % at the 64-register cap)
+template <int BR, int BC, int G, int NDOT, bool ORD = false>
 __global__ void __launch_bounds__(256, 4)
 spmv_kernel(int64_t nbrows, const int64_t* __restrict__ rowptr, const int32_t* __restrict__ colidx,
              const double* __restrict__ val, const double* __restrict__ x, double alpha, double beta,
@@ -37,10 +40,10 @@ spmv_kernel(int64_t nbrows, const int64_t* __restrict__ rowptr, const int32_t* _
   if (fuse.skip && *fuse.skip != 0.0) return;
   const double* xg = nullptr;          // ghost section of x in the halo window (fused exchange)
   int64_t n_own = 0;
-  const int32_t* __restrict__ order = fuse.hw.win ? fuse.order : nullptr;
-  bool waited = order == nullptr;      // deferred, per warp, to the first boundary row
+  const int32_t* __restrict__ order = ORD ? fuse.order : nullptr;
+  bool waited = !ORD;                  // deferred, per warp, to the first boundary row
   if (fuse.hw.win) {
-    if (!order && !halo_wait_cta(fuse.hw)) return;
+    if (!ORD && !halo_wait_cta(fuse.hw)) return;
     xg = halo_buf(fuse.hw.win, (int)(fuse.hw.seq & 1ull), fuse.hw.nghost, fuse.hw.max_bs);
     n_own = fuse.hw.n_own;
   }
@@ -53,7 +56,7 @@ spmv_kernel(int64_t nbrows, const int64_t* __restrict__ rowptr, const int32_t* _
   const int64_t iters = (nbrows + ngrp - 1) / ngrp;
   int64_t r = grp;                     // position in the walk; ra: the row itself
   bool live = r < nbrows;
-  int64_t ra = live ? (order ? (int64_t)order[r] : r) : 0;
+  int64_t ra = live ? (ORD ? (int64_t)order[r] : r) : 0;
   int64_t p0 = live ? rowptr[ra] : 0;
   int nb = live ? (int)(rowptr[ra + 1] - p0) : 0;
   int32_t cnext = lane < nb ? colidx[p0 + lane] : 0;
@@ -61,12 +64,14 @@ spmv_kernel(int64_t nbrows, const int64_t* __restrict__ rowptr, const int32_t* _
     // next row's extent, fetched early
     const int64_t rn = r + ngrp;
     const bool liven = rn < nbrows;
-    const int64_t ran = liven ? (order ? (int64_t)order[rn] : rn) : 0;
+    const int64_t ran = liven ? (ORD ? (int64_t)order[rn] : rn) : 0;
     const int64_t p0n = liven ? rowptr[ran] : 0;
     const int nbn = liven ? (int)(rowptr[ran + 1] - p0n) : 0;
-    if (!waited && __any_sync(0xffffffffu, live && r >= fuse.n_int)) {
-      halo_wait_warp(fuse.hw);
-      waited = true;
+    if (ORD) {
+      if (!waited && __any_sync(0xffffffffu, live && r >= fuse.n_int)) {
+        halo_wait_warp(fuse.hw);
+        waited = true;
+      }
     }
     const double* __restrict__ v = val + p0 * BB;
     double acc[BR];
@@ -134,7 +139,7 @@ static int spmv_launch(pyn_mat* m, double alpha, const double* x, double beta, c
     nrows = m->halo->n_own;
     if (nrows == 0) return PYN_OK;
   }
-  if (fuse.hw.win && m->n_interior >= 0 && !g_halo_wait_at_start) {
+  if (dot && fuse.hw.win && m->n_interior >= 0 && !g_halo_wait_at_start) {
     fuse.order = m->row_order.p;
     fuse.n_int = m->n_interior;
   }
@@ -143,9 +148,15 @@ static int spmv_launch(pyn_mat* m, double alpha, const double* x, double beta, c
   const int G = avg > 24.0 ? 32 : (avg > 10.0 ? 16 : 8);
   // one wave: 4 resident CTAs per SM (__launch_bounds__(256, 4))
   const int grid = grid_for(ctx, nrows * G, 256, 4);
-#define LAUNCH(BR, BC, GG, DD)                                                                   \
-  spmv_kernel<BR, BC, GG, DD><<<grid, 256, 0, ctx->stream>>>(nrows, m->rowptr.p, m->colidx.p, \
-                                                             m->val.p, x, alpha, beta, z, y, fuse)
+#define LAUNCH(BR, BC, GG, DD)                                                                        \
+  do {                                                                                                \
+    if (DD > 0 && fuse.order)                                                                         \
+      spmv_kernel<BR, BC, GG, DD, (DD > 0)><<<grid, 256, 0, ctx->stream>>>(                           \
+          nrows, m->rowptr.p, m->colidx.p, m->val.p, x, alpha, beta, z, y, fuse);                     \
+    else                                                                                              \
+      spmv_kernel<BR, BC, GG, DD, false><<<grid, 256, 0, ctx->stream>>>(                              \
+          nrows, m->rowptr.p, m->colidx.p, m->val.p, x, alpha, beta, z, y, fuse);                     \
+  } while (0)
 #define CALL(BR, BC)                                     \
   do {                                                   \
     if (dot) {                                           \

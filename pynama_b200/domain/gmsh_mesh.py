@@ -177,6 +177,11 @@ class GmshMesh:
             for tag in msh["entity_physical"].get((ed, et), []) or [et]:
                 self._border_faces.setdefault(tag, []).extend(hit)
         self._phys_by_name = {nm.lower(): tag for (d, tag), nm in msh["physical_names"].items() if d == dim - 1}
+        # borders beyond the reference's six (four) box names: named physical groups of boundary faces,
+        # e.g. the wall of a body inside the channel (cylinder_mesh.py); in tag order after the box sides
+        extra = sorted((tag, nm) for (d, tag), nm in msh["physical_names"].items()
+                       if d == dim - 1 and nm.lower() not in self.sides and tag in self._border_faces)
+        self.sides = list(self.sides) + [nm.lower() for _, nm in extra]
 
     def _min_edge(self):
         c = self.corner_xyz

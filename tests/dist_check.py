@@ -38,8 +38,8 @@ def main():
         name, val = kv.split("=")
         o.setValue(name, val)
     case = os.environ.get("DIST_CASE", "taylor-green3d")
-    if case == "cavity":
-        return main_cavity(nelem, ngl, rank, size, ctx)
+    if case in ("cavity", "cylinder"):
+        return main_cavity(nelem, ngl, rank, size, ctx, case)
     cfg = bench.case_config(nelem[0], ngl)
     cfg["domain"]["box-mesh"]["nelem"] = nelem
     if os.environ.get("DIST_GMSH", "0") != "0":
@@ -109,14 +109,23 @@ def main():
     return 0 if nf == 0 else 1
 
 
-def main_cavity(nelem, ngl, rank, size, ctx):
+def main_cavity(nelem, ngl, rank, size, ctx, case="cavity"):
     """no-slip lid-driven cavity (MatNS, the two-solve branch of evalRHS) on the partitioned mesh
-    against OracleProblemNS on the global mesh"""
+    against OracleProblemNS on the global mesh.  case == "cylinder": BASELINE.json configs[3] on a
+    small channel (blocked-cell cylinder, unstructured file, 8 borders, RCB partition)"""
     from pynama_b200.cases.base_problem import BaseProblem
     from pynama_b200.run_case import loadCase
     Options().setValue("ksp_type", os.environ.get("DIST_KSP", "gmres"))
-    cfg = loadCase("cavity")
-    fem = BaseProblem(cfg, case="cavity", nelem=nelem, ngl=ngl)
+    cfg = loadCase(case)
+    kw = {"nelem": nelem}
+    if case == "cylinder":
+        import tempfile
+        from pynama_b200.domain.cylinder_mesh import write_cylinder_msh
+        path = os.path.join(tempfile.mkdtemp(prefix=f"pyn_cyl_{rank}_"), "cyl.msh")      # every rank its own identical copy
+        write_cylinder_msh(path, h=0.5, lower=(-2.0, -1.5, 0.0), upper=(3.0, 1.5, 1.0))
+        cfg["domain"]["gmsh-file"] = path
+        kw = {}
+    fem = BaseProblem(cfg, case=case, ngl=ngl, **kw)
     fem.setUp()
     fem.setUpSolver()
     fem.ts._post = None
@@ -144,7 +153,7 @@ def main_cavity(nelem, ngl, rank, size, ctx):
     check("cavity vorticity", fem.vort.getGlobalArray(), orc.vort, 1e-8)
     nf = ctx.allreduce([len(fails)], "max")[0]
     if rank == 0:
-        print(f"[dist_check] cavity, ranks {size}: {'OK' if nf == 0 else 'FAILED ' + str(fails)}", flush=True)
+        print(f"[dist_check] {case}, ranks {size}: {'OK' if nf == 0 else 'FAILED ' + str(fails)}", flush=True)
     return 0 if nf == 0 else 1
 
 

@@ -75,6 +75,23 @@ def test_no_slip_cavity_partitioned(nproc):
     _run(nproc, 29570 + nproc, env)
 
 
+@pytest.mark.parametrize("nproc", [1, 2, 4, 8])
+def test_cylinder_channel_partitioned(nproc):
+    """BASELINE.json configs[3] on a small channel: blocked-cell cylinder, unstructured Gmsh file with the
+    two extra wall borders (cylinder-x, cylinder-y), all sides no-slip, RCB partition; fields after two
+    RK5BS steps against OracleProblemNS on the global mesh"""
+    env = {"DIST_CASE": "cylinder", "DIST_NGL": "3"}
+    if nproc == 1:
+        r = subprocess.run([sys.executable, SCRIPT], capture_output=True, text=True, timeout=900,
+                           env=dict(os.environ, **env))
+        assert r.returncode == 0, r.stdout[-3000:] + "\n" + r.stderr[-3000:]
+        assert "OK" in r.stdout
+        return
+    if _ngpus() < nproc:
+        pytest.skip(f"needs {nproc} GPUs")
+    _run(nproc, 29580 + nproc, env)
+
+
 @pytest.mark.parametrize("nproc", [1, 2, 4])
 def test_unstructured_mesh_partitioned_by_rcb(nproc):
     """Gmsh input, recursive coordinate bisection over the ranks, same oracle comparison"""
