@@ -268,6 +268,17 @@ def run_b200(args, rank, world):
     live = max(min(its, n_spmv), 1)
     avg_ms = ms_spmv / live
     achieved = spmv_bytes / (avg_ms * 1e-3) / 1e9 if n_spmv else 0.0
+    per_rank = None
+    if world > 1:
+        # every rank multiplies its own rows: bytes = the blocks of the OWNED rows (pyn_mat_bytes), time =
+        # that rank's launches; the slowest rank is the one reported, the spread is printed beside it
+        lo = -float(ctx.allreduce([-achieved], "max")[0])
+        hi = float(ctx.allreduce([achieved], "max")[0])
+        per_rank = {"rank0": round(achieved, 1), "min": round(lo, 1), "max": round(hi, 1),
+                    "bytes_rank0": int(spmv_bytes),
+                    "bytes_max": int(ctx.allreduce([float(spmv_bytes)], "max")[0]),
+                    "avg_launch_us_max": round(float(ctx.allreduce([avg_ms * 1e3], "max")[0]), 2)}
+        achieved = lo
     roofline = {"bound": "hbm", "kernel": "spmv_kernel<3,3,32,DOT> on K (row-plane BSR)",
                 "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4),
                 "peak_source": peak_src, "bytes_per_launch": int(spmv_bytes), "launches": int(live),
@@ -279,6 +290,8 @@ def run_b200(args, rank, world):
                 "reference_equivalent_GBs": round((12 * nnz_ref + 16 * ndof + 8 * ndof) / (avg_ms * 1e-3) / 1e9, 1)
                 if n_spmv else 0.0,
                 "traffic": read_traffic() if world == 1 and args.nelem == 16 and args.ngl == 4 else None}
+    if per_rank:
+        roofline["over_ranks"] = per_rank
 
     e2e = None
     if not args.no_e2e:

@@ -192,8 +192,14 @@ int pyn_mat_bytes(pyn_mat* m, int64_t* stored_bytes, int64_t* spmv_bytes) {
   // column ids + row pointers + y written + x read once
   // (the padding blocks of the rows are stored and read but not credited)
   const int64_t nreal = m->free_pattern ? m->nblocks : m->nblocks_real;
-  if (spmv_bytes)
-    *spmv_bytes = nreal * (8 * bb + 4) + m->nbrows * (8 * m->br + 8) + m->nbcols * 8 * m->bc;
+  if (spmv_bytes) {
+    if (m->halo && m->own_blocks_real >= 0)
+      // row-partitioned: a product multiplies the owned rows only (the rows of ghost nodes are
+      // stored but never read), x is read over owned + ghost entries
+      *spmv_bytes = m->own_blocks_real * (8 * bb + 4) + m->halo->n_own * (8 * m->br + 8) + m->nbcols * 8 * m->bc;
+    else
+      *spmv_bytes = nreal * (8 * bb + 4) + m->nbrows * (8 * m->br + 8) + m->nbcols * 8 * m->bc;
+  }
   return PYN_OK;
 }
 

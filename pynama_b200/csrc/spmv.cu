@@ -189,16 +189,26 @@ static int spmv_launch(pyn_mat* m, double alpha, const double* x, double beta, c
 }
 
 // flag[r] = 1 when row r holds a column >= n_own (one warp per row)
+// *nreal += blocks of the rows that are not padding (padding repeats the row's last column)
 __global__ void ghost_rows_kernel(int64_t nrows, int64_t n_own, const int64_t* __restrict__ rowptr,
-                                  const int32_t* __restrict__ colidx, uint8_t* __restrict__ flag) {
+                                  const int32_t* __restrict__ colidx, uint8_t* __restrict__ flag,
+                                  unsigned long long* __restrict__ nreal) {
   const int lane = threadIdx.x & 31;
   const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
   for (int64_t r = warp; r < nrows; r += nwarps) {
     bool g = false;
-    for (int64_t k = rowptr[r] + lane; k < rowptr[r + 1]; k += 32) g |= colidx[k] >= n_own;
+    unsigned int real = 0;
+    for (int64_t k = rowptr[r] + lane; k < rowptr[r + 1]; k += 32) {
+      g |= colidx[k] >= n_own;
+      real += (k == rowptr[r] || colidx[k] != colidx[k - 1]) ? 1u : 0u;
+    }
     g = __any_sync(0xffffffffu, g);
-    if (lane == 0) flag[r] = g ? 1 : 0;
+    for (int o = 16; o > 0; o >>= 1) real += __shfl_xor_sync(0xffffffffu, real, o);
+    if (lane == 0) {
+      flag[r] = g ? 1 : 0;
+      atomicAdd(nreal, (unsigned long long)real);      // integer sum: order does not matter
+    }
   }
 }
 
@@ -208,10 +218,16 @@ int spmv_build_row_order(pyn_mat* m) {
   if (!m->halo || m->halo->n_own <= 0 || m->nblocks == 0) return PYN_OK;
   const int64_t n_own = m->halo->n_own;
   DevBuf<uint8_t> flag;
+  DevBuf<unsigned long long> nreal;
   PYN_CHECK(flag.alloc(ctx, n_own));
+  PYN_CHECK(nreal.alloc(ctx, 1));
+  PYN_CHECK(nreal.zero());
   ghost_rows_kernel<<<grid_for(ctx, n_own * 32, 256), 256, 0, ctx->stream>>>(n_own, n_own, m->rowptr.p,
-                                                                              m->colidx.p, flag.p);
+                                                                              m->colidx.p, flag.p, nreal.p);
   PYN_LAUNCHED(ctx);
+  unsigned long long nr = 0;
+  PYN_CHECK(nreal.download(&nr, 1));
+  m->own_blocks_real = (int64_t)nr;
   std::vector<uint8_t> f((size_t)n_own);
   PYN_CHECK(flag.download(f.data(), n_own));
   std::vector<int32_t> order;
