@@ -184,6 +184,7 @@ def run_b200(args, rank, world):
     for kv in args.tune:
         key, _, val = kv.partition("=")
         _lib.call("pyn_tune", key.encode(), int(val or "1"))
+    FP64_PEAK["TFLOPs"] = ctx.fp64_peak()          # DFMA chains, measured on this device before anything else runs
     ctx.prof_enable(True)
     fem = build_problem(args)
     asm_kernels = {k: ctx.prof_get(k) for k in ("elem_kle", "numeric")}
@@ -293,6 +294,17 @@ def run_b200(args, rank, world):
     if per_rank:
         roofline["over_ranks"] = per_rank
 
+    # the next kernels of the step, each against the roofline that bounds it
+    nloc = (K.getLocalSize()[0] if hasattr(K, "getLocalSize") else ndof)
+    upd_bytes = 8 * nloc * 8 + (nloc // 3) * 9 * 8        # x, r, z, p, w read / written (8 passes) + the 3x3 PC blocks
+    upd_us = ms_upd / max(n_upd, 1) * 1e3
+    other_rooflines = [
+        {"kernel": "cg_update_kernel (x, r, z update + node-block Jacobi + r.z, z.z + convergence test)",
+         "bound": "L2 / launch latency (vectors are L2-resident: 2.8 MB each)", "bytes_per_launch": int(upd_bytes),
+         "avg_launch_us": round(upd_us, 2), "achieved_GBs": round(upd_bytes / (upd_us * 1e-6) / 1e9, 1) if n_upd else None,
+         "frac_of_hbm_peak": round(upd_bytes / (upd_us * 1e-6) / 1e9 / peak, 4) if n_upd else None},
+    ]
+
     e2e = None
     if not args.no_e2e:
         e2e = run_e2e(args, fem, ctx, world, ndof, nvort, restore)
@@ -318,6 +330,13 @@ def run_b200(args, rank, world):
         matfree = {"option": "-kle_matfree 1", "value": ndof / (ms_mf * 1e-3), "unit": UNIT, "ms_per_step": ms_mf,
                    "ksp_iterations_per_step": its_mf,
                    "K_product_us": round(t_mf / max(n_mf, 1) * 1e3, 2),
+                   "roofline": {"bound": "fp64 pipe / latency", "flop_per_product": int(2 * 24000 * fem.dom.getDeviceMesh().nel),
+                                "flop_note": "~24 k FMA per element at ngl=4 (3 forward + 3 transposed sum-factorised "
+                                             "passes per rule + the point updates, DESIGN.md section 3)",
+                                "achieved_TFLOPs": round(2 * 24000 * fem.dom.getDeviceMesh().nel / (t_mf / max(n_mf, 1) * 1e-3) / 1e12, 2),
+                                "peak_TFLOPs": FP64_PEAK["TFLOPs"],
+                                "frac": round(2 * 24000 * fem.dom.getDeviceMesh().nel / (t_mf / max(n_mf, 1) * 1e-3) / 1e12
+                                              / FP64_PEAK["TFLOPs"], 4) if FP64_PEAK["TFLOPs"] else None},
                    "K_product": "mf_apply_kernel (sum-factorised, fp64 pipe) + mf_gather_kernel; "
                                 "vectors + 80 B of geometry per quadrature point per product"}
         if not args.no_e2e:
@@ -342,6 +361,9 @@ def run_b200(args, rank, world):
                     else "over NCCL") + f", {ctx.collectives()} collectives so far on rank 0",
                    "l2": "inputs larger than L2 (K = %.2f GB per SpMV)" % (spmv_bytes / 1e9)},
         "roofline": roofline,
+        "other_rooflines": other_rooflines,
+        "fp64_peak": {"TFLOPs": FP64_PEAK["TFLOPs"], "how": "pyn_fp64_peak: 16 independent DFMA chains per thread, "
+                      "8 CTAs of 256 threads per SM, best of 4 timed launches (2 flop per DFMA)"},
         "checksum": checksum,
         "kernel_time_ms_per_step": {"spmv_K_dot": ms_spmv / args.steps, "cg_update": ms_upd / args.steps,
                                     "cg_direction": ms_dir / args.steps, "spmv_other": ms_oth / args.steps},
@@ -379,6 +401,9 @@ def assembly_kernels(ctx, dm, mode, reps=3):
     return out
 
 
+FP64_PEAK = {"TFLOPs": None}
+
+
 def kernels_entry(k, peak, nel, ngl):
     n_el, ms_el = k["elem_kle"]
     n_nu, ms_nu = k["numeric"]
@@ -388,6 +413,8 @@ def kernels_entry(k, peak, nel, ngl):
     flop = 2.0 * nn * nn * (7 * ngl ** 3 + 15 * (ngl - 1) ** 3) * k["classes"]
     return {"congruence_classes": int(k["classes"]), "elements": int(nel),
             "elem_kle_ms": round(ms_el, 4), "elem_kle_TFLOPs": round(flop / (ms_el * 1e-3) / 1e12, 2) if ms_el else None,
+            "elem_kle_frac_of_measured_fp64_peak": round(flop / (ms_el * 1e-3) / 1e12 / FP64_PEAK["TFLOPs"], 4)
+            if ms_el and FP64_PEAK["TFLOPs"] else None,
             "numeric_ms": round(ms_nu, 4), "numeric_launches": n_nu, "numeric_value_bytes": k["value_bytes"],
             "numeric_GBs": round(k["value_bytes"] / (ms_nu * 1e-3) / 1e9, 1) if ms_nu else None,
             "numeric_frac_of_peak": round(k["value_bytes"] / (ms_nu * 1e-3) / 1e9 / peak, 4) if ms_nu else None}

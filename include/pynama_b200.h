@@ -307,6 +307,11 @@ int pyn_vtensv(pyn_vec* vel, pyn_vec* out, int dim);
 /* aux = 2 mu * aux - rho * vtensv(vel)   (base_problem.py:127-130 fused) */
 int pyn_stress_combine(pyn_vec* aux, pyn_vec* vel, double mu, double rho, int dim);
 
+/* measured fp64 FMA throughput of the device in TFLOP/s (2 flop per DFMA; 16 independent chains per
+ * thread, best of four timed launches): the denominator of the element kernels' roofline fraction.
+ * No counterpart in the reference (measurement support). */
+int pyn_fp64_peak(pyn_ctx* ctx, double* tflops);
+
 /* ---- allocation-free entry point ---------------------------------------------------------*/
 /* No counterpart in the reference: added for callers that may
  * not allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).

@@ -115,6 +115,7 @@ _PROTOS = {
     "pyn_vec_to_host_n": [vp, vp, c_i64],
     "pyn_vec_from_host_n": [vp, vp, c_i64],
     "pyn_vec_device_ptr": [vp, P(vp)],
+    "pyn_fp64_peak": [vp, P(c_dbl)],
     "pyn_vec_dot_noalloc": [vp, vp, vp, c_i64, vp, vp],
     "pyn_ksp_create": [vp, vp, c_int, c_int, P(vp)],
     "pyn_ksp_set_tolerances": [vp, c_dbl, c_dbl, c_int, c_int],

@@ -195,6 +195,12 @@ class Context:
         call("pyn_launch_count", self.handle, ctypes.byref(n))
         return n.value
 
+    def fp64_peak(self):
+        """measured DFMA throughput of this device, TFLOP/s (pyn_fp64_peak)"""
+        v = c_dbl()
+        call("pyn_fp64_peak", self.handle, ctypes.byref(v))
+        return v.value
+
     def flush_l2(self):
         call("pyn_flush_l2", self.handle)
 
