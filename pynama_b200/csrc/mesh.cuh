@@ -95,8 +95,7 @@ struct pyn_mat {
   // row-partitioned run: rows [0, halo->n_own) are this rank's; x gets its ghost entries
   // refreshed before every product (comm.cu)
   pyn_halo* halo = nullptr;
-  pyn::DevBuf<int32_t> row_order;  // [n_own] interior rows (no ghost column) first, then boundary rows
-  int64_t n_interior = -1;         // -1: not built
+  int64_t n_interior = -1;         // leading owned rows without a ghost column; -1: not counted
   int64_t own_blocks_real = -1;    // blocks (padding not counted) of the owned rows: what a product reads
   // products through the matrix-free element kernels instead of the stored blocks (matfree.cuh);
   // owned by the mesh

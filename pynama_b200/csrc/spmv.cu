@@ -26,9 +26,11 @@ namespace pyn {
 // producer warp (cp.async.bulk + mbarrier, 128 KB ring) was correct but 6x slower -- 16
 // consumer warps each holding a whole row (<= 24.7 KB) span more than the ring, so the
 // warps serialise (profiles/README.md, round 1).
-// ORD: rows walked through fuse.order (row-partitioned matrices with the fused halo); a separate
-// instantiation, so that the one-GPU kernel keeps the exact code it was tuned with (r2d: the order
-// state in the common kernel cost 11 % at the 64-register cap)
+// ORD: row-partitioned matrix with the fused halo whose first fuse.n_int rows read no ghost column
+// (pynama_b200/parallel.py numbers the owned nodes that way): a warp waits for the ghosts only when it
+// reaches its first row >= n_int.  A separate instantiation, so that the one-GPU kernel keeps the exact
+// code it was tuned with (r2d: extra state in the common kernel cost 11 % at the 64-register cap; r2f:
+// walking the rows through a permutation array instead cost 19 % -- one more dependent load per row).
 template <int BR, int BC, int G, int NDOT, bool ORD = false>
 __global__ void __launch_bounds__(256, 4)
 spmv_kernel(int64_t nbrows, const int64_t* __restrict__ rowptr, const int32_t* __restrict__ colidx,
@@ -40,7 +42,6 @@ spmv_kernel(int64_t nbrows, const int64_t* __restrict__ rowptr, const int32_t* _
   if (fuse.skip && *fuse.skip != 0.0) return;
   const double* xg = nullptr;          // ghost section of x in the halo window (fused exchange)
   int64_t n_own = 0;
-  const int32_t* __restrict__ order = ORD ? fuse.order : nullptr;
   bool waited = !ORD;                  // deferred, per warp, to the first boundary row
   if (fuse.hw.win) {
     if (!ORD && !halo_wait_cta(fuse.hw)) return;
@@ -54,19 +55,17 @@ spmv_kernel(int64_t nbrows, const int64_t* __restrict__ rowptr, const int32_t* _
   const int64_t grp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / G;
   const int64_t ngrp = ((int64_t)gridDim.x * blockDim.x) / G;
   const int64_t iters = (nbrows + ngrp - 1) / ngrp;
-  int64_t r = grp;                     // position in the walk; ra: the row itself
+  int64_t r = grp;
   bool live = r < nbrows;
-  int64_t ra = live ? (ORD ? (int64_t)order[r] : r) : 0;
-  int64_t p0 = live ? rowptr[ra] : 0;
-  int nb = live ? (int)(rowptr[ra + 1] - p0) : 0;
+  int64_t p0 = live ? rowptr[r] : 0;
+  int nb = live ? (int)(rowptr[r + 1] - p0) : 0;
   int32_t cnext = lane < nb ? colidx[p0 + lane] : 0;
   for (int64_t it = 0; it < iters; ++it) {
     // next row's extent, fetched early
     const int64_t rn = r + ngrp;
     const bool liven = rn < nbrows;
-    const int64_t ran = liven ? (ORD ? (int64_t)order[rn] : rn) : 0;
-    const int64_t p0n = liven ? rowptr[ran] : 0;
-    const int nbn = liven ? (int)(rowptr[ran + 1] - p0n) : 0;
+    const int64_t p0n = liven ? rowptr[rn] : 0;
+    const int nbn = liven ? (int)(rowptr[rn + 1] - p0n) : 0;
     if (ORD) {
       if (!waited && __any_sync(0xffffffffu, live && r >= fuse.n_int)) {
         halo_wait_warp(fuse.hw);
@@ -102,20 +101,19 @@ spmv_kernel(int64_t nbrows, const int64_t* __restrict__ rowptr, const int32_t* _
     for (int i = 0; i < BR; ++i) {
       if (live && lane == i % G) {
         double out = alpha * acc[i];
-        if (beta != 0.0) out += beta * z[ra * BR + i];
-        y[ra * BR + i] = out;
+        if (beta != 0.0) out += beta * z[r * BR + i];
+        y[r * BR + i] = out;
         if (NDOT > 0) {
-          const double xr = x[ra * BC + i];
+          const double xr = x[r * BC + i];
           dotacc[0] += out * xr;
           if (NDOT == 3) {
-            dotacc[NV > 1 ? 1 : 0] += fuse.dot_r[ra * BR + i] * xr;
+            dotacc[NV > 1 ? 1 : 0] += fuse.dot_r[r * BR + i] * xr;
             dotacc[NV > 2 ? 2 : 0] += xr * xr;
           }
         }
       }
     }
     r = rn;
-    ra = ran;
     live = liven;
     p0 = p0n;
     nb = nbn;
@@ -139,10 +137,7 @@ static int spmv_launch(pyn_mat* m, double alpha, const double* x, double beta, c
     nrows = m->halo->n_own;
     if (nrows == 0) return PYN_OK;
   }
-  if (dot && fuse.hw.win && m->n_interior >= 0 && !g_halo_wait_at_start) {
-    fuse.order = m->row_order.p;
-    fuse.n_int = m->n_interior;
-  }
+  if (dot && fuse.hw.win && m->n_interior > 0 && !g_halo_wait_at_start) fuse.n_int = m->n_interior;
   if (m->mf) return matfree_apply(m, nrows, alpha, x, beta, z, y, dot, fuse);
   const double avg = m->nbrows ? (double)m->nblocks / (double)m->nbrows : 0.0;
   const int G = avg > 24.0 ? 32 : (avg > 10.0 ? 16 : 8);
@@ -150,7 +145,7 @@ static int spmv_launch(pyn_mat* m, double alpha, const double* x, double beta, c
   const int grid = grid_for(ctx, nrows * G, 256, 4);
 #define LAUNCH(BR, BC, GG, DD)                                                                        \
   do {                                                                                                \
-    if (DD > 0 && fuse.order)                                                                         \
+    if (DD > 0 && fuse.n_int > 0)                                                                     \
       spmv_kernel<BR, BC, GG, DD, (DD > 0)><<<grid, 256, 0, ctx->stream>>>(                           \
           nrows, m->rowptr.p, m->colidx.p, m->val.p, x, alpha, beta, z, y, fuse);                     \
     else                                                                                              \
@@ -230,15 +225,11 @@ int spmv_build_row_order(pyn_mat* m) {
   m->own_blocks_real = (int64_t)nr;
   std::vector<uint8_t> f((size_t)n_own);
   PYN_CHECK(flag.download(f.data(), n_own));
-  std::vector<int32_t> order;
-  order.reserve((size_t)n_own);
-  for (int64_t r = 0; r < n_own; ++r)
-    if (!f[(size_t)r]) order.push_back((int32_t)r);
-  const int64_t n_int = (int64_t)order.size();
-  for (int64_t r = 0; r < n_own; ++r)
-    if (f[(size_t)r]) order.push_back((int32_t)r);
-  PYN_CHECK(m->row_order.alloc(ctx, n_own));
-  PYN_CHECK(m->row_order.upload(order.data(), n_own));
+  // the deferred wait needs the rows that read ghosts at the END of the owned rows (the numbering of
+  // pynama_b200/parallel.py); any other numbering keeps the wait at CTA start
+  int64_t n_int = 0;
+  while (n_int < n_own && !f[(size_t)n_int]) ++n_int;
+  // (rows after n_int need not all hold a ghost column: only the rows BEFORE n_int must be ghost-free)
   m->n_interior = n_int;
   return PYN_OK;
 }

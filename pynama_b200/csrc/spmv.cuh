@@ -18,10 +18,8 @@ struct SpmvFuse {
   // hw.win != NULL: the ghost entries of x were pushed into this rank's halo window by the
   // kernel that produced x; wait for them at CTA start and read ghost columns from the window
   HaloWait hw;
-  // with hw: rows are walked through `order` -- the n_int rows without a ghost column first, the
-  // rows that read ghosts last -- and a warp waits for the ghosts only when it reaches its first
-  // boundary row, so the arrival of the halo overlaps the interior part of the product
-  const int32_t* order;
+  // with hw and n_int > 0: the first n_int rows read no ghost column; a warp waits for the ghosts only
+  // when it reaches its first row >= n_int, so the arrival of the halo overlaps the interior rows
   int64_t n_int;
 };
 
@@ -33,8 +31,8 @@ int spmv_dot(pyn_mat* m, const double* x, double* y, double* dot_out, const doub
 // y = A x and out3 = {x.y, r.x, x.x} in one pass (single-reduction CG)
 int spmv_dot3(pyn_mat* m, const double* x, double* y, const double* r, double* out3, const double* skip,
               const P2PRed* red = nullptr);
-// row-partitioned matrix: classify the owned rows (interior: no column >= n_own) and keep the
-// interior-first permutation on the device
+// row-partitioned matrix: count the leading owned rows without a ghost column (n_interior) and the
+// blocks of the owned rows
 int spmv_build_row_order(pyn_mat* m);
 int diag_blocks(pyn_mat* m, double* dblk);   // [nbrows][b][b]
 int scale_rows(pyn_mat* m, const double* l);

@@ -100,10 +100,20 @@ class Partition:
         owner = np.full(mesh.nnodes, size, dtype=np.int64)
         np.minimum.at(owner, mesh.elem_nodes.ravel(), np.repeat(elem_rank, mesh.elem_nodes.shape[1]))
         self.node_owner = owner
-        self.owned = np.nonzero(owner == self.rank)[0]                      # ascending global id
+        owned = np.nonzero(owner == self.rank)[0]                           # ascending global id
         # elements touching an owned node
         touch = (owner[mesh.elem_nodes] == self.rank).any(axis=1)
         self.elems = np.nonzero(touch)[0]                                   # ascending global id
+        # owned nodes are numbered interior first, then the ones that share an element with a ghost node
+        # (the rows of a product that read ghost columns), each group by ascending global id: the
+        # device multiplies the interior rows while the ghost values are still on their way
+        en_loc = mesh.elem_nodes[self.elems]
+        with_ghost = (owner[en_loc] != self.rank).any(axis=1)
+        bnd = np.zeros(mesh.nnodes, dtype=bool)
+        bnd[np.unique(en_loc[with_ghost])] = True
+        is_bnd = bnd[owned]
+        self.owned = np.concatenate([owned[~is_bnd], owned[is_bnd]])
+        self.n_interior = int((~is_bnd).sum())
         loc_nodes = np.unique(mesh.elem_nodes[self.elems])
         ghost = loc_nodes[owner[loc_nodes] != self.rank]
         order = np.lexsort((ghost, owner[ghost]))                           # by owner, then global id

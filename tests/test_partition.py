@@ -73,7 +73,13 @@ def test_ownership_and_halo_tables(tmp_path, nelem, ngl, size):
     for p in parts:
         held[p.elems] += 1
         assert np.array_equal(p.l2g[p.elem_nodes], mesh.elem_nodes[p.elems])
-        assert np.all(np.diff(p.owned) > 0) and np.all(np.diff(p.elems) > 0)
+        # owned nodes: interior first, then the ones that share an element with a ghost, each ascending
+        ni = p.n_interior
+        assert np.all(np.diff(p.owned[:ni]) > 0) and np.all(np.diff(p.owned[ni:]) > 0) and np.all(np.diff(p.elems) > 0)
+        has_ghost = (p.elem_nodes >= p.n_own).any(axis=1)
+        touched = np.zeros(p.n_loc, bool)
+        touched[np.unique(p.elem_nodes[has_ghost])] = True
+        assert not touched[:ni].any() and touched[ni:p.n_own].all()           # rows [0, ni) read no ghost column
         assert np.all(p.g2l[p.l2g] == np.arange(p.n_loc))
         # all nodes coupled to an owned node are local (columns of owned rows)
         touch = (p.node_owner[mesh.elem_nodes] == p.rank).any(axis=1)
