@@ -72,8 +72,9 @@ int pyn_prof_get(pyn_ctx* ctx, int cls, int64_t* count, double* total_ms);
  * meshes beyond 2^31 contributions / record offsets use; for parity tests on small meshes).
  * "asm_coarse_unfused": non-zero runs the coarse level of -pc_type asm as one restriction and
  * steps+1 Chebyshev launches instead of the single cooperative launch (comparison / fallback).
- * "halo_wait_at_start": non-zero makes the fused-halo product wait for the ghost entries at CTA
- * start (round 1) instead of interior rows first / wait before the first boundary row.
+ * "halo_wait_at_start": 1 (default) makes the fused-halo product wait for the ghost entries at CTA
+ * start; 0 multiplies the interior rows first and lets each warp wait before its first boundary row
+ * (measured slower at 2 GPUs, profiles/README.md r2f/r2g; kept for experiments at higher rank counts).
  * "ksp_adaptive_chunks": 0 launches CG iterations in fixed chunks of ksp_check_every between status
  * polls (round 1); default 1 sizes the first chunk from the previous solve's iteration count. */
 int pyn_tune(const char* key, int value);
@@ -144,6 +145,12 @@ int pyn_mesh_graph_info(pyn_mesh* mesh, int64_t* npairs, int64_t* ncontrib, int*
 /* dof classes of the velocity dofs (nnodes*dim bytes): 0 free, 1 Dirichlet
  * (free-slip BC, mat_fs.py:158-172), 2 no-slip normal, 3 no-slip tangential
  * (mat_ns.py:59-75). */
+/* Row-partitioned runs: the element -> node table of the WHOLE mesh in global node ids (the same on
+ * every rank) and the global element of every local element.  Needed by the second level of
+ * -pc_type asm, whose coarse space (Q1 on the element corners of the whole mesh) is replicated on every
+ * rank.  Replaces nothing in the reference (PETSc would distribute the coarse problem of a PCMG). */
+int pyn_mesh_set_global_tables(pyn_mesh* mesh, int64_t n_global_nodes, int64_t nel_global,
+                               const int32_t* elem_nodes_global, const int64_t* elem_gid);
 int pyn_mesh_set_dof_class(pyn_mesh* mesh, const uint8_t* cls);
 /* Congruence classes of element shapes.  getElemKLEMatrices / getElemKLEOperators
  * (spectral.py:92-228) depend on an element only through its corner offsets, and the

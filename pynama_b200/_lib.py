@@ -70,6 +70,7 @@ _PROTOS = {
     "pyn_mesh_destroy": [vp],
     "pyn_mesh_graph_info": [vp, P(c_i64), P(c_i64), P(c_int)],
     "pyn_mesh_set_dof_class": [vp, vp],
+    "pyn_mesh_set_global_tables": [vp, c_i64, c_i64, vp, vp],
     "pyn_mesh_set_congruence": [vp, c_dbl, P(c_i64)],
     "pyn_mesh_get_congruence": [vp, P(c_dbl), P(c_i64)],
     "pyn_mesh_phase_ms": [vp, c_int, P(c_dbl)],

@@ -98,7 +98,7 @@ int pyn_tune(const char* key, int value) {
     g_asm_coarse_unfused = value != 0;
     return PYN_OK;
   }
-  if (strcmp(key, "halo_wait_at_start") == 0) {   // fused halo: wait for the ghosts at CTA start (round 1)
+  if (strcmp(key, "halo_wait_at_start") == 0) {   // fused halo: 1 wait at CTA start (default), 0 per warp before its first boundary row
     g_halo_wait_at_start = value != 0;
     return PYN_OK;
   }
@@ -332,6 +332,20 @@ int pyn_mesh_graph_info(pyn_mesh* mesh, int64_t* npairs, int64_t* ncontrib, int*
   if (npairs) *npairs = mesh->dense.nslots;
   if (ncontrib) *ncontrib = mesh->dense.ncontrib;
   if (max_row) *max_row = mesh->dense.max_row;
+  return PYN_OK;
+}
+
+int pyn_mesh_set_global_tables(pyn_mesh* mesh, int64_t n_global_nodes, int64_t nel_global,
+                               const int32_t* elem_nodes_global, const int64_t* elem_gid) {
+  PYN_REQUIRE(mesh && elem_nodes_global && elem_gid && nel_global >= mesh->nel && n_global_nodes > 0,
+              "pyn_mesh_set_global_tables: bad argument");
+  for (int64_t e = 0; e < mesh->nel; ++e)
+    PYN_REQUIRE(elem_gid[e] >= 0 && elem_gid[e] < nel_global, "pyn_mesh_set_global_tables: element id %lld of %lld",
+                (long long)elem_gid[e], (long long)nel_global);
+  mesh->g_elem_nodes.assign(elem_nodes_global, elem_nodes_global + nel_global * mesh->nn);
+  mesh->elem_gid.assign(elem_gid, elem_gid + mesh->nel);
+  mesh->g_nel = nel_global;
+  mesh->g_nnodes = n_global_nodes;
   return PYN_OK;
 }
 

@@ -197,6 +197,8 @@ static int asm_setup_impl(pyn_ctx* ctx, pyn_mat* A, AsmPc* pc) {
 struct AsmCoarseArgs {
   int64_t nv;
   int steps;
+  int mode;       // 0: restriction + Chebyshev; 1: restriction only (rc = this rank's part, summed over
+                  // the ranks before mode 2); 2: Chebyshev only, from rc
   const int64_t* rl_ptr;
   const int32_t* rl_node;
   const double* rl_w;
@@ -225,28 +227,36 @@ asm_coarse_fused_kernel(AsmCoarseArgs a) {
   const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
   const double c2_0 = a.c2[0];
   for (int64_t v = warp; v < a.nv; v += nwarps) {
-    double acc[B];
+    double t;
+    if (a.mode != 2) {
+      double acc[B];
 #pragma unroll
-    for (int i = 0; i < B; ++i) acc[i] = 0.0;
-    for (int64_t k = a.rl_ptr[v] + lane; k < a.rl_ptr[v + 1]; k += 32) {
-      const int64_t n = a.rl_node[k];
-      const double w = a.rl_w[k];
+      for (int i = 0; i < B; ++i) acc[i] = 0.0;
+      for (int64_t k = a.rl_ptr[v] + lane; k < a.rl_ptr[v + 1]; k += 32) {
+        const int64_t n = a.rl_node[k];
+        const double w = a.rl_w[k];
 #pragma unroll
-      for (int i = 0; i < B; ++i) acc[i] += w * a.keep[n * B + i] * a.r[n * B + i];
-    }
+        for (int i = 0; i < B; ++i) acc[i] += w * a.keep[n * B + i] * a.r[n * B + i];
+      }
 #pragma unroll
-    for (int i = 0; i < B; ++i)
+      for (int i = 0; i < B; ++i)
 #pragma unroll
-      for (int o = 16; o > 0; o >>= 1) acc[i] += __shfl_xor_sync(0xffffffffu, acc[i], o);
-    if (lane < B) {
-      double t = acc[0];
+        for (int o = 16; o > 0; o >>= 1) acc[i] += __shfl_xor_sync(0xffffffffu, acc[i], o);
+      t = acc[0];
 #pragma unroll
       for (int i = 1; i < B; ++i) t = lane == i ? acc[i] : t;
-      a.rc[v * B + lane] = t;
-      a.xc[v * B + lane] = 0.0;
-      a.d0[v * B + lane] = c2_0 * a.dinv[v * B + lane] * t;
+    } else {
+      t = lane < B ? a.rc[v * B + lane] : 0.0;
+    }
+    if (lane < B) {
+      if (a.mode != 2) a.rc[v * B + lane] = t;
+      if (a.mode != 1) {
+        a.xc[v * B + lane] = 0.0;
+        a.d0[v * B + lane] = c2_0 * a.dinv[v * B + lane] * t;
+      }
     }
   }
+  if (a.mode == 1) return;                         // uniform over the grid
   double* dold = a.d0;
   double* dnew = a.d1;
   for (int s = 1; s <= a.steps; ++s) {
@@ -292,6 +302,44 @@ asm_coarse_fused_kernel(AsmCoarseArgs a) {
   }
 }
 
+// mode / steps as in AsmCoarseArgs; r: the fine vector restricted (modes 0, 1)
+template <int B>
+static int asm_coarse_launch(pyn_ctx* ctx, AsmPc* pc, int mode, int steps, const double* r, const double* done) {
+  AsmCoarseArgs ca;
+  ca.nv = pc->nv;
+  ca.steps = steps;
+  ca.mode = mode;
+  ca.rl_ptr = pc->rl_ptr.p;
+  ca.rl_node = pc->rl_node.p;
+  ca.rl_w = pc->rl_w.p;
+  ca.keep = pc->keep.p;
+  ca.r = r;
+  ca.ptr = pc->ac_ptr.p;
+  ca.col = pc->ac_col.p;
+  ca.val = pc->ac_val.p;
+  ca.dinv = pc->ac_dinv.p;
+  ca.c1 = pc->cheb_c.p;
+  ca.c2 = pc->cheb_c.p + (pc->coarse_steps + 1);
+  ca.rc = pc->rc.p;
+  ca.xc = pc->xc.p;
+  ca.d0 = pc->d0.p;
+  ca.d1 = pc->d1.p;
+  ca.done = done;
+  void* args[] = {&ca};
+  PYN_CUDA(cudaLaunchCooperativeKernel((const void*)asm_coarse_fused_kernel<B>, dim3(pc->coarse_grid), dim3(256),
+                                       args, 0, ctx->stream));
+  PYN_LAUNCHED(ctx);
+  return PYN_OK;
+}
+
+// rc = P^T (keep r) over ALL ranks through the restriction lists (set-up probing; the apply fuses it)
+template <int B>
+static int asm_restrict_lists(pyn_ctx* ctx, AsmPc* pc, const double* r) {
+  PYN_CHECK(asm_coarse_launch<B>(ctx, pc, 1, 0, r, nullptr));
+  if (pc->halo) PYN_CHECK(comm_allreduce_sum(ctx, pc->rc.p, (int)(pc->nv * B)));
+  return PYN_OK;
+}
+
 template <int B>
 static AsmProlong asm_prolong_args(const AsmPc* pc, const double* xc) {
   AsmProlong cp;
@@ -327,20 +375,85 @@ static int asm_coarse_setup(pyn_ctx* ctx, pyn_mat* A, AsmPc* pc) {
   PYN_REQUIRE(asm_coarse_phi(mesh->htab, corner_local, &phi) == 0, "pc asm: element corner nodes not found");
   std::vector<int32_t> en((size_t)(nel * nn));
   PYN_CHECK(mesh->elem_nodes.download(en.data(), nel * nn));
+  const bool dist = pc->halo != nullptr;
+  PYN_REQUIRE(!dist || mesh->g_nel > 0,
+              "pc asm: the coarse level on a row-partitioned operator needs pyn_mesh_set_global_tables");
+  // the coarse space lives on the element corners of the WHOLE mesh: on several ranks the tables are
+  // built from the global element table, identically everywhere (vertex ids, adjacency, colours)
   AsmCoarseTables T;
-  asm_coarse_tables(nel, nnodes, nn, ncorner, en.data(), corner_local, &T);
+  if (dist)
+    asm_coarse_tables(mesh->g_nel, mesh->g_nnodes, nn, ncorner, mesh->g_elem_nodes.data(), corner_local, &T);
+  else
+    asm_coarse_tables(nel, nnodes, nn, ncorner, en.data(), corner_local, &T);
   const int64_t nv = pc->nv = T.nv;
   pc->ncolors = T.ncolors;
   PYN_CHECK(pc->phi.alloc(ctx, (int64_t)phi.size()));
   PYN_CHECK(pc->phi.upload(phi.data(), (int64_t)phi.size()));
+  std::vector<int32_t> ev_local((size_t)(nel * ncorner));              // coarse vertex of every local element corner
+  for (int64_t e = 0; e < nel; ++e) {
+    const int64_t ge = dist ? mesh->elem_gid[(size_t)e] : e;
+    for (int c = 0; c < ncorner; ++c) ev_local[(size_t)(e * ncorner + c)] = T.elem_verts[(size_t)(ge * ncorner + c)];
+  }
   PYN_CHECK(pc->elem_verts.alloc(ctx, nel * ncorner));
-  PYN_CHECK(pc->elem_verts.upload(T.elem_verts.data(), nel * ncorner));
-  PYN_CHECK(pc->v2e_ptr.alloc(ctx, nv + 1));
-  PYN_CHECK(pc->v2e_ptr.upload(T.v2e_ptr.data(), nv + 1));
+  PYN_CHECK(pc->elem_verts.upload(ev_local.data(), nel * ncorner));
   static_assert(sizeof(int2) == 2 * sizeof(int32_t), "int2 layout");
-  const int64_t nv2e = T.v2e_ptr[(size_t)nv];
-  PYN_CHECK(pc->v2e.alloc(ctx, nv2e));
-  PYN_CHECK(pc->v2e.upload(reinterpret_cast<const int2*>(T.v2e.data()), nv2e));
+  if (!dist) {                                  // (element, corner) lists of the separate-launch path
+    PYN_CHECK(pc->v2e_ptr.alloc(ctx, nv + 1));
+    PYN_CHECK(pc->v2e_ptr.upload(T.v2e_ptr.data(), nv + 1));
+    const int64_t nv2e = T.v2e_ptr[(size_t)nv];
+    PYN_CHECK(pc->v2e.alloc(ctx, nv2e));
+    PYN_CHECK(pc->v2e.upload(reinterpret_cast<const int2*>(T.v2e.data()), nv2e));
+  }
+  // restriction lists: an OWNED fine node contributes, through its first local element, to the
+  // vertices of that element with a non-zero corner function (the weights do not depend on the
+  // element: the mesh is conforming); local elements and local nodes ascending inside every list
+  {
+    std::vector<int64_t> first((size_t)nnodes, -1);
+    for (int64_t k = nel * nn - 1; k >= 0; --k) first[(size_t)en[(size_t)k]] = k;     // lowest (e, a) wins
+    std::vector<int64_t> rl_ptr((size_t)nv + 1, 0);
+    for (int pass = 0; pass < 2; ++pass) {
+      std::vector<int64_t> fill(rl_ptr.begin(), rl_ptr.end() - 1);
+      std::vector<int32_t> rl_node(pass ? (size_t)rl_ptr[(size_t)nv] + 1 : 1);
+      std::vector<double> rl_w(pass ? (size_t)rl_ptr[(size_t)nv] + 1 : 1);
+      for (int64_t e = 0; e < nel; ++e)
+        for (int a = 0; a < nn; ++a) {
+          const int64_t n = en[(size_t)(e * nn + a)];
+          if (n >= pc->n_own || first[(size_t)n] != e * nn + a) continue;
+          for (int c = 0; c < ncorner; ++c) {
+            const double w = phi[(size_t)(a * ncorner + c)];
+            if (w == 0.0) continue;
+            const int64_t v = ev_local[(size_t)(e * ncorner + c)];
+            if (!pass) {
+              rl_ptr[(size_t)v + 1]++;
+            } else {
+              rl_node[(size_t)fill[(size_t)v]] = (int32_t)n;
+              rl_w[(size_t)fill[(size_t)v]++] = w;
+            }
+          }
+        }
+      if (!pass) {
+        for (int64_t v = 0; v < nv; ++v) rl_ptr[(size_t)v + 1] += rl_ptr[(size_t)v];
+      } else {
+        PYN_CHECK(pc->rl_ptr.alloc(ctx, nv + 1));
+        PYN_CHECK(pc->rl_ptr.upload(rl_ptr.data(), nv + 1));
+        PYN_CHECK(pc->rl_node.alloc(ctx, (int64_t)rl_node.size()));
+        PYN_CHECK(pc->rl_node.upload(rl_node.data(), (int64_t)rl_node.size()));
+        PYN_CHECK(pc->rl_w.alloc(ctx, (int64_t)rl_w.size()));
+        PYN_CHECK(pc->rl_w.upload(rl_w.data(), (int64_t)rl_w.size()));
+      }
+    }
+    int per_sm = 0;
+    PYN_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, asm_coarse_fused_kernel<B>, 256, 0));
+    const int64_t want = (nv * 32 + 255) / 256;
+    // (r2d: one CTA per SM instead of the full co-resident grid made the apply ~90 us slower: a warp
+    // then walks four vertices one after the other; the barriers are the smaller cost)
+    const int64_t cap = (int64_t)per_sm * ctx->num_sms;
+    pc->coarse_grid = (int)std::max<int64_t>(1, std::min(want, cap));
+    // placeholders until the coefficients are known (the probing below restricts with steps = 0)
+    std::vector<double> cc0((size_t)(2 * (pc->coarse_steps + 1)), 0.0);
+    PYN_CHECK(pc->cheb_c.alloc(ctx, (int64_t)cc0.size()));
+    PYN_CHECK(pc->cheb_c.upload(cc0.data(), (int64_t)cc0.size()));
+  }
   PYN_CHECK(pc->keep.alloc(ctx, nnodes * B));
   asm_free_dofs_kernel<B><<<grid_for(ctx, nnodes * 32, 256), 256, 0, ctx->stream>>>(nnodes, A->rowptr.p, A->colidx.p,
                                                                                     A->val.p, pc->keep.p);
@@ -364,8 +477,8 @@ static int asm_coarse_setup(pyn_ctx* ctx, pyn_mat* A, AsmPc* pc) {
       asm_prolong_kernel<B><<<gridn, 256, 0, ctx->stream>>>(nnodes, mesh->n2e_ptr.p, mesh->n2e.p,
                                                             asm_prolong_args<B>(pc, pc->xc.p), xf.p);
       PYN_LAUNCHED(ctx);
-      PYN_CHECK(spmv(A, 1.0, xf.p, 0.0, nullptr, yf.p));
-      PYN_CHECK(asm_restrict<B>(ctx, pc, yf.p, pc->rc.p, nullptr));
+      PYN_CHECK(spmv(A, 1.0, xf.p, 0.0, nullptr, yf.p));          // (row-partitioned: refreshes the ghosts of xf)
+      PYN_CHECK(asm_restrict_lists<B>(ctx, pc, yf.p));
       PYN_CHECK(pc->rc.download(th.data(), nv * B));
       for (int64_t v = 0; v < nv; ++v)
         for (int64_t k = T.adj_ptr[(size_t)v]; k < T.adj_ptr[(size_t)v + 1]; ++k)
@@ -386,45 +499,11 @@ static int asm_coarse_setup(pyn_ctx* ctx, pyn_mat* A, AsmPc* pc) {
   PYN_CHECK(pc->ac_val.upload(val.data(), nnzb * B * B));
   PYN_CHECK(pc->ac_dinv.alloc(ctx, nv * B));
   PYN_CHECK(pc->ac_dinv.upload(dinv.data(), nv * B));
-  // restriction lists of the fused kernel: what asm_restrict_kernel visits (a fine node contributes
-  // through its first element only), vertex by vertex, elements then local nodes ascending
   {
-    std::vector<int64_t> first((size_t)nnodes, -1);
-    for (int64_t k = nel * nn - 1; k >= 0; --k) first[(size_t)en[(size_t)k]] = k;     // lowest (e, a) wins
-    std::vector<int64_t> rl_ptr((size_t)nv + 1, 0);
-    std::vector<int32_t> rl_node;
-    std::vector<double> rl_w;
-    for (int64_t v = 0; v < nv; ++v) {
-      for (int64_t k = T.v2e_ptr[(size_t)v]; k < T.v2e_ptr[(size_t)v + 1]; ++k) {
-        const int64_t e = T.v2e[(size_t)(2 * k)];
-        const int c = T.v2e[(size_t)(2 * k + 1)];
-        for (int a = 0; a < nn; ++a) {
-          const double w = phi[(size_t)(a * ncorner + c)];
-          if (w == 0.0 || first[(size_t)en[(size_t)(e * nn + a)]] != e * nn + a) continue;
-          rl_node.push_back(en[(size_t)(e * nn + a)]);
-          rl_w.push_back(w);
-        }
-      }
-      rl_ptr[(size_t)v + 1] = (int64_t)rl_node.size();
-    }
-    PYN_CHECK(pc->rl_ptr.alloc(ctx, nv + 1));
-    PYN_CHECK(pc->rl_ptr.upload(rl_ptr.data(), nv + 1));
-    PYN_CHECK(pc->rl_node.alloc(ctx, (int64_t)rl_node.size() + 1));
-    PYN_CHECK(pc->rl_node.upload(rl_node.data(), (int64_t)rl_node.size()));
-    PYN_CHECK(pc->rl_w.alloc(ctx, (int64_t)rl_w.size() + 1));
-    PYN_CHECK(pc->rl_w.upload(rl_w.data(), (int64_t)rl_w.size()));
     std::vector<double> cc;
     cc.insert(cc.end(), pc->c1.begin(), pc->c1.end());
     cc.insert(cc.end(), pc->c2.begin(), pc->c2.end());
-    PYN_CHECK(pc->cheb_c.alloc(ctx, (int64_t)cc.size()));
     PYN_CHECK(pc->cheb_c.upload(cc.data(), (int64_t)cc.size()));
-    int per_sm = 0;
-    PYN_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, asm_coarse_fused_kernel<B>, 256, 0));
-    const int64_t want = (nv * 32 + 255) / 256;
-    // (r2d: one CTA per SM instead of the full co-resident grid made the apply ~90 us slower: a warp
-    // then walks four vertices one after the other; the barriers are the smaller cost)
-    const int64_t cap = (int64_t)per_sm * ctx->num_sms;
-    pc->coarse_grid = (int)std::max<int64_t>(1, std::min(want, cap));
   }
   PYN_CUDA(cudaStreamSynchronize(ctx->stream));
   return PYN_OK;
@@ -435,10 +514,6 @@ int asm_setup(pyn_ctx* ctx, pyn_mat* A, int coarse_steps, AsmPc** out) {
   PYN_REQUIRE(A->mesh && !A->free_pattern, "pc asm needs an operator assembled from a mesh");
   const bool dist = A->halo && ctx->nranks > 1;
   PYN_REQUIRE(A->br == A->bc && A->nbrows == A->mesh->nnodes, "pc asm: operator is not square over the mesh nodes");
-  if (dist && coarse_steps > 0) {
-    set_error("pc asm: the coarse level (-pc_asm_coarse) is not available on row-partitioned operators yet");
-    return PYN_E_UNSUPPORTED;
-  }
   AsmPc* pc = new AsmPc();
   pc->coarse_steps = coarse_steps > 0 ? coarse_steps : 0;
   int rc;
@@ -472,30 +547,15 @@ static int asm_apply_impl(pyn_ctx* ctx, AsmPc* pc, double* r, double* z, double*
   PYN_LAUNCHED(ctx);
   const double* xc = nullptr;
   const bool unfused = g_asm_coarse_unfused;     // pyn_tune("asm_coarse_unfused"): the seven-launch path (r2a)
-  if (pc->coarse_steps > 0 && !unfused) {     // restriction + all Chebyshev steps in ONE cooperative launch
-    AsmCoarseArgs ca;
-    ca.nv = pc->nv;
-    ca.steps = pc->coarse_steps;
-    ca.rl_ptr = pc->rl_ptr.p;
-    ca.rl_node = pc->rl_node.p;
-    ca.rl_w = pc->rl_w.p;
-    ca.keep = pc->keep.p;
-    ca.r = r;
-    ca.ptr = pc->ac_ptr.p;
-    ca.col = pc->ac_col.p;
-    ca.val = pc->ac_val.p;
-    ca.dinv = pc->ac_dinv.p;
-    ca.c1 = pc->cheb_c.p;
-    ca.c2 = pc->cheb_c.p + (pc->coarse_steps + 1);
-    ca.rc = pc->rc.p;
-    ca.xc = pc->xc.p;
-    ca.d0 = pc->d0.p;
-    ca.d1 = pc->d1.p;
-    ca.done = done;
-    void* args[] = {&ca};
-    PYN_CUDA(cudaLaunchCooperativeKernel((const void*)asm_coarse_fused_kernel<B>, dim3(pc->coarse_grid), dim3(256),
-                                         args, 0, ctx->stream));
-    PYN_LAUNCHED(ctx);
+  if (pc->coarse_steps > 0 && pc->halo) {
+    // row-partitioned: the coarse problem is replicated.  This rank's part of P^T r, summed over the
+    // ranks (nv * B doubles), then every rank takes the same Chebyshev steps on the whole coarse problem
+    PYN_CHECK(asm_coarse_launch<B>(ctx, pc, 1, 0, r, done));
+    PYN_CHECK(comm_allreduce_sum(ctx, pc->rc.p, (int)(pc->nv * B)));
+    PYN_CHECK(asm_coarse_launch<B>(ctx, pc, 2, pc->coarse_steps, r, done));
+    xc = pc->xc.p;
+  } else if (pc->coarse_steps > 0 && !unfused) {     // restriction + all Chebyshev steps in ONE cooperative launch
+    PYN_CHECK(asm_coarse_launch<B>(ctx, pc, 0, pc->coarse_steps, r, done));
     xc = pc->xc.p;
   } else if (pc->coarse_steps > 0) {           // xc ~ Ac^-1 P^T r by coarse_steps Chebyshev steps
     PYN_CHECK(asm_restrict<B>(ctx, pc, r, pc->rc.p, done));

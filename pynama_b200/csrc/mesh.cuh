@@ -51,6 +51,12 @@ struct pyn_mesh {
   pyn::DevBuf<int32_t> elem_class;         // [nel] class of the element
   pyn::DevBuf<int32_t> class_rep;          // [nclass] lowest element of the class
   // node -> (element, local index), ascending element
+  // row-partitioned runs (pyn_mesh_set_global_tables): the element -> node table of the WHOLE mesh in
+  // global node ids (replicated on every rank) and the global ids of the local elements; the coarse
+  // level of pc asm builds identical global coarse tables on every rank from them
+  std::vector<int32_t> g_elem_nodes;       // [g_nel][nn]
+  std::vector<int64_t> elem_gid;           // [nel] global element of local element e
+  int64_t g_nel = 0, g_nnodes = 0;
   pyn::DevBuf<int64_t> n2e_ptr;            // [nnodes+1]
   pyn::DevBuf<int2> n2e;                   // [nel*nn]
   int max_valence = 0;

@@ -73,6 +73,15 @@ class DeviceMesh:
         call("pyn_mesh_get_congruence", self._h, ctypes.byref(t), ctypes.byref(n))
         return t.value, n.value
 
+    def set_global_tables(self, elem_nodes_global, n_global_nodes, elem_gid):
+        """row-partitioned runs: the whole mesh's element -> node table (global ids) and the global
+        element of every local element (second level of -pc_type asm: replicated coarse space)"""
+        en = np.ascontiguousarray(elem_nodes_global, dtype=np.int32).reshape(-1, self.nn)
+        gid = np.ascontiguousarray(elem_gid, dtype=np.int64).ravel()
+        if gid.size != self.nel:
+            raise ValueError("elem_gid must have one entry per local element")
+        call("pyn_mesh_set_global_tables", self._h, int(n_global_nodes), len(en), ptr(en), ptr(gid))
+
     def set_dof_class(self, cls):
         cls = np.ascontiguousarray(cls, dtype=np.uint8).ravel()
         if cls.size != self.nnodes * self.dim:

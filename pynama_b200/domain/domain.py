@@ -243,6 +243,10 @@ class Domain:
                                          layout=layout)
                 ldofs = (part.l2g[:, None] * m.dim + np.arange(m.dim)[None, :]).ravel()
                 cls = cls[ldofs]
+                from ..petsc import Options as _O
+                if _O().getString("pc_type", "") == "asm" and _O().getInt("pc_asm_coarse", 0) > 0:
+                    # the coarse level is replicated: every rank needs the global element table
+                    self._dmesh.set_global_tables(m.elem_nodes, m.nnodes, part.elems)
             else:
                 self._dmesh = DeviceMesh(m.dim, m.ngl, m.corner_xyz, m.elem_nodes, m.nnodes)
             from ..petsc import Options

@@ -228,6 +228,23 @@ def test_time_steps_with_asm_match_the_oracle(case, nelem, ngl):
         o.setValue("pc_type", "bjacobi")
 
 
+@pytest.mark.parametrize("nproc,coarse", [(2, 5), (4, 5), (8, 3)])
+def test_partitioned_run_with_two_level_asm(nproc, coarse):
+    """row-partitioned operator with the coarse level: global coarse tables on every rank (pyn_mesh_set_global_tables),
+    this rank's part of P^T r summed over the ranks, the Chebyshev steps replicated; same oracle comparison"""
+    import subprocess
+    import sys
+    from tests.test_gpu_dist import SCRIPT, _ngpus
+    if _ngpus() < nproc:
+        pytest.skip(f"needs {nproc} GPUs")
+    env = dict(os.environ, DIST_OPTS=f"pc_type=asm,pc_asm_coarse={coarse}", DIST_NELEM="6,6,6", DIST_KSP="cg")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}",
+           "--master-addr", "127.0.0.1", "--master-port", str(29590 + nproc), SCRIPT]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=900, env=env)
+    assert r.returncode == 0, r.stdout[-3000:] + "\n" + r.stderr[-3000:]
+    assert "OK" in r.stdout
+
+
 @pytest.mark.parametrize("nproc,ksp", [(2, "cg"), (2, "gmres"), (4, "cg"), (8, "cg")])
 def test_partitioned_run_with_asm(nproc, ksp):
     """row-partitioned operator: ghost refresh of r, all local elements, owned nodes summed, blocks of
