@@ -46,7 +46,10 @@ def parse_args():
     ap.add_argument("--ngl", type=int, default=4)
     ap.add_argument("--rtol", type=float, default=1e-10, help="KSP relative tolerance")
     ap.add_argument("--dt", type=float, default=1e-3, help="fixed time step (-ts_adapt_type none)")
-    ap.add_argument("--pc", default="bjacobi", choices=["jacobi", "bjacobi", "none", "asm"])
+    ap.add_argument("--pc", default="asm", choices=["jacobi", "bjacobi", "none", "asm"],
+                    help="asm: element-block additive Schwarz with a Q1 coarse level (--coarse Chebyshev steps)")
+    ap.add_argument("--coarse", type=int, default=5, help="-pc_asm_coarse (0: one-level Schwarz)")
+    ap.add_argument("--no-alt", action="store_true", help="skip the comparison pass with -pc_type bjacobi (round-1 default)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-matfree", action="store_true", help="skip the extra matrix-free (-kle_matfree 1) pass")
@@ -136,19 +139,22 @@ def case_config(nelem, ngl):
 # ---------------------------------------------------------------------------------------------
 # B200 arm
 # ---------------------------------------------------------------------------------------------
-def build_problem(args):
+def build_problem(args, pc=None):
     from pynama_b200.cases.base_problem import BaseProblem
     from pynama_b200.petsc import Options
+    pc = pc or args.pc
     o = Options()
     o.setValue("ksp_type", "cg")
-    o.setValue("pc_type", args.pc)
+    o.setValue("pc_type", pc)
+    o.setValue("pc_asm_coarse", args.coarse if pc == "asm" else 0)
     o.setValue("ksp_rtol", args.rtol)
     o.setValue("ksp_max_it", 50000)
     if args.fischer > 0:
         o.setValue("ksp_fischer_guess", f"1,{args.fischer}")
     o.setValue("ts_adapt_type", "none")
     o.setValue("ts_dt", args.dt)
-    if int(os.environ.get("WORLD_SIZE", "1")) > 1 and not any(kv.startswith("ksp_cg_single_reduction") for kv in args.opt):
+    if (int(os.environ.get("WORLD_SIZE", "1")) > 1 and pc != "asm"
+            and not any(kv.startswith("ksp_cg_single_reduction") for kv in args.opt)):
         # row-partitioned runs: CG with one synchronisation point per iteration (PETSc's
         # -ksp_cg_single_reduction); with the peer-memory back end the halo exchange is fused too
         args.opt.append("ksp_cg_single_reduction=1")
@@ -349,7 +355,8 @@ def run_b200(args, rank, world):
         "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": workload_name(args),
                    "dofs": int(ndof), "nodes": int(ndof // 3), "ksp": f"cg+{args.pc}", "ksp_rtol": args.rtol,
-                   "ksp_options": f"-ksp_type cg -pc_type {args.pc} -ksp_rtol {args.rtol:g}" +
+                   "ksp_options": f"-ksp_type cg -pc_type {args.pc}" +
+                                  (f" -pc_asm_coarse {args.coarse}" if args.pc == "asm" else "") + f" -ksp_rtol {args.rtol:g}" +
                                   (f" -ksp_fischer_guess 1,{args.fischer}" if args.fischer > 0 else "") +
                                   "".join(" -" + kv.replace("=", " ") for kv in args.opt),
                    "dt": args.dt, "rhs_evals_per_step": evals / args.steps,
@@ -376,7 +383,31 @@ def run_b200(args, rank, world):
         out["e2e"] = e2e
     if matfree:
         out["matfree"] = matfree
+    if world == 1 and args.pc == "asm" and not args.no_alt:
+        out["alt_pc_bjacobi"] = run_alt_pc(args, ctx, "bjacobi")
     return out
+
+
+def run_alt_pc(args, ctx, pc):
+    """the same K timed steps (after W warm-up steps from the initial condition) with another
+    preconditioner -- node-block Jacobi, the round-1 default and PETSc's pbjacobi -- for comparison"""
+    fem = build_problem(args, pc=pc)
+    fem.ts.setSolution(fem.vort)
+    for _ in range(args.warmup):
+        fem.ts.step()
+    ctx.sync()
+    its0 = fem.kspIterations
+    ctx.timer_start()
+    for _ in range(args.steps):
+        fem.ts.step()
+    ms = ctx.timer_stop() / args.steps
+    ndof = fem.mat.K.getSize()[0]
+    res = {"ksp_options": f"-ksp_type cg -pc_type {pc} -ksp_rtol {args.rtol:g}" +
+                          (f" -ksp_fischer_guess 1,{args.fischer}" if args.fischer > 0 else ""),
+           "ms_per_step": ms, "value": ndof / (ms * 1e-3), "unit": UNIT,
+           "ksp_iterations_per_step": (fem.kspIterations - its0) / args.steps}
+    fem.mat.K.destroy()
+    return res
 
 
 def assembly_kernels(ctx, dm, mode, reps=3):
@@ -527,17 +558,22 @@ def field_checksum(vort, vel):
             "vort_max": float(np.abs(vort).max())}
 
 
+def cpu_pc(args):
+    """the CPU arm's preconditioner: the GPU arm's when the C port has it, else node-block Jacobi (PETSc's
+    pbjacobi) -- the Schwarz preconditioner of the GPU arm has no CPU port; same KSP type, tolerance,
+    Fischer guess, mesh and time step either way"""
+    return args.pc if args.pc in ("jacobi", "bjacobi") else "bjacobi"
+
+
 def cpu_problem(args):
     """the CPU restatement on the SAME mesh as the GPU arm: oracle/boxmesh.py tables, oracle/sem.py cell
     matrices, oracle/ckle.c assembly + scalar-CSR products + CG on all host cores (oracle/cport.py).
     No import of the product package."""
     from oracle import boxmesh, cport
-    if args.pc not in ("jacobi", "bjacobi"):
-        raise SystemExit(f"the CPU arm has no '{args.pc}' preconditioner (jacobi, bjacobi); add --no-cpu-baseline")
     t0 = time.perf_counter()
     mesh = boxmesh.box_mesh([args.nelem] * 3, [0.0] * 3, [1.0] * 3, args.ngl)
     prob = cport.CProblem(3, args.ngl, mesh.corner_xyz, mesh.elem_nodes, mesh.coords, mesh.border_nodes,
-                          rho=0.5, mu=0.01, rtol=args.rtol, pc=args.pc, fischer=args.fischer)
+                          rho=0.5, mu=0.01, rtol=args.rtol, pc=cpu_pc(args), fischer=args.fischer)
     return prob, mesh.nnodes * 3, time.perf_counter() - t0, cport.threads()
 
 
@@ -570,7 +606,7 @@ def cpu_run(args, steps, warmup, budget_s):
     its = (prob.iterations - its0) / done
     sample = (f"{done} timed RK5BS step(s) after {done_w} warm-up step(s) of the SAME problem ({args.nelem}^3 elements, "
               f"ngl={args.ngl}, {ndof} dofs): cell matrices from the numpy oracle, scatter-add assembly, scalar-CSR "
-              f"SpMV and CG + {args.pc} (rtol {args.rtol:g}" +
+              f"SpMV and CG + {cpu_pc(args)} (rtol {args.rtol:g}" +
               (f", Fischer guess 1,{args.fischer}" if args.fischer > 0 else "") +
               f") in C + OpenMP on {cores} threads; {its:.0f} CG its/step, {wall:.1f} s timed, "
               f"{setup_s:.1f} s set-up + assembly")
@@ -590,7 +626,7 @@ def run_reference(args, rank, world):
             "steps": r["steps"], "warmup": r["warmup"], "steps_requested": args.steps,
             "warmup_requested": args.warmup, "ms_per_step": r["ms"], "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": workload_name(args), "dofs": int(r["ndof"]), "ksp": f"cg+{args.pc}",
+            "config": {"workload": workload_name(args), "dofs": int(r["ndof"]), "ksp": f"cg+{cpu_pc(args)}",
                        "ksp_rtol": args.rtol, "dt": args.dt, "ksp_iterations_per_step": r["its"],
                        "K_scalar_nnz": r["K_nnz"],
                        "note": "petsc4py/PETSc/mpirun are not installed: the reference's own modules cannot be "
