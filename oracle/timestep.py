@@ -39,6 +39,8 @@ RK5BS_A = [
 ]
 RK5BS_B = [587 / 8064, 0, 4440339 / 15491840, 24353 / 124800, 387 / 44800, 2152 / 5985, 7267 / 94080, 0]
 RK5BS_C = [0, 1 / 6, 2 / 9, 3 / 7, 2 / 3, 3 / 4, 1, 1]
+# embedded fourth-order weights of the pair
+RK5BS_BE = [2479 / 34992, 0, 123 / 416, 612941 / 3411720, 43 / 1440, 2272 / 6561, 79937 / 1113912, 3293 / 556956]
 
 
 # ---- analytic fields -------------------------------------------------------------------------
@@ -271,6 +273,48 @@ class OracleProblem:
                 unew += h * RK5BS_B[j] * k[j]
         self.vort = unew
         return t + h, k[s - 1]
+
+
+def step_adaptive(prob, t, h, k0=None, rtol=1e-4, atol=1e-4):
+    """One ACCEPTED step of an OracleProblem / OracleProblemNS under the `basic` step controller as PETSc
+    documents it (TSAdaptBasic: weighted 2-norm of the embedded error estimate with tolerances atol + rtol
+    max(|u|, |u_new|), safety 0.9, halved after a rejection, step factor clipped to [0.1, 10], exponent
+    -1/(order-1) with order = 5).  PETSc's sources are not in the reference tree (ts_solver.py:5-23 leaves
+    everything to its defaults): UNPINNED against PETSc, restated here so that the device time stepper has
+    a CPU statement to agree with.  Returns (t_new, FSAL stage, next step size, rejected attempts)."""
+    s = len(RK5BS_B)
+    rejected = 0
+    while True:
+        k = [None] * s
+        u0 = prob.vort.copy()
+        for i in range(s):
+            if i == 0 and k0 is not None:
+                k[0] = k0
+                continue
+            k[i] = prob.eval_rhs(t + RK5BS_C[i] * h)
+        u = prob.vort                       # (eval_rhs wrote the boundary values of the last stage time into it)
+        unew = u.copy()
+        err = np.zeros_like(u)
+        for j in range(s):
+            if RK5BS_B[j] != 0.0:
+                unew += h * RK5BS_B[j] * k[j]
+            if RK5BS_B[j] != RK5BS_BE[j]:
+                err += h * (RK5BS_B[j] - RK5BS_BE[j]) * k[j]
+        tol = atol + rtol * np.maximum(np.abs(u), np.abs(unew))
+        enorm = float(np.sqrt(np.mean((err / tol) ** 2)))
+        safety = 0.9
+        accept = enorm <= 1.0
+        if not accept:
+            safety *= 0.5
+        fac = 10.0 if enorm == 0.0 else safety * enorm ** (-1.0 / 4.0)
+        hnew = h * min(max(fac, 0.1), 10.0)
+        if accept:
+            prob.vort = unew
+            return t + h, k[s - 1], hnew, rejected
+        rejected += 1
+        h = hnew
+        k0 = k[0]                           # still f(t, u)
+        del u0
 
 
 # ---- no-slip (NS) path --------------------------------------------------------------------------

@@ -133,3 +133,43 @@ def test_bench_options_fields_at_8cube(extra):
     finally:
         for k in list(extra) + ["ksp_fischer_guess"]:
             Options().delValue(k)
+
+
+def test_adaptive_steps_follow_the_oracle_controller():
+    """-ts_adapt_type basic (the reference never pins a step: ts_solver.py:5-23 leaves dt and the controller
+    to PETSc's defaults): the device time stepper against the oracle's restatement of the same controller --
+    same accepted step sizes, same rejections, same fields.  Unpinned against PETSc itself."""
+    from pynama_b200.cases.base_problem import BaseProblem
+    from pynama_b200.petsc import Options
+    from pynama_b200.run_case import loadCase
+    o = _options()
+    o.setValue("ts_adapt_type", "basic")
+    o.setValue("ts_dt", 0.05)                       # the controller overshoots after the first step: rejections follow
+    o.setValue("ts_rtol", 1e-6)
+    o.setValue("ts_atol", 1e-6)
+    try:
+        fem = BaseProblem(loadCase("taylor-green"), case="taylor-green", nelem=[4, 4], ngl=4)
+        fem.setUp()
+        fem.setUpSolver()
+        fem.ts._post = None
+        fem.ts.setSolution(fem.vort)
+        mesh = fem.dom.getMesh()
+        orc = timestep.OracleProblem(2, 4, mesh.corner_xyz, mesh.elem_nodes, mesh.coords, mesh.getBordersNodes(),
+                                     rho=fem.rho, mu=fem.mu, solver="direct")
+        t, k0, h = 0.0, None, 0.05
+        taken, rej = [], 0
+        for _ in range(5):
+            fem.ts.step()
+            t, k0, hnext, r = timestep.step_adaptive(orc, t, h, k0, rtol=1e-6, atol=1e-6)
+            taken.append((fem.ts._last_dt, t))
+            rej += r
+            assert abs(fem.ts.getTime() - t) <= 1e-9 * t, (fem.ts.getTime(), t)
+            assert abs(fem.ts.getTimeStep() - hnext) <= 1e-6 * hnext
+            h = hnext
+        assert rej >= 1 and fem.ts.rejections == rej
+        assert _rel(fem.vort.getArray(), orc.vort) < 1e-7
+        assert _rel(fem.solverKLE.getSolution().getArray(), orc.vel) < 1e-7
+    finally:
+        for k in ("ts_rtol", "ts_atol"):
+            Options().delValue(k)
+        Options().setValue("ts_adapt_type", "none")
