@@ -122,6 +122,24 @@ __global__ void cg_scalars_kernel(double* S, int parity, int maxit) {
   cg_bookkeeping(S, S[S_LRZ], S[S_LZZ], parity, maxit);
 }
 
+// the same with the allreduce of (r.z, z.z) over peer memory: this rank's partials are pushed into every
+// rank's window and summed in rank order (one warp; used after the Schwarz preconditioner, whose apply
+// sits between the vector update and this reduction)
+__global__ void cg_scalars_p2p_kernel(double* S, int parity, int maxit, P2PRed red) {
+  if (S[S_DONE] != 0.0) return;
+  double t[2] = {S[S_LRZ], S[S_LZZ]}, g[2];
+  p2p_push<2>(red, 1, t);
+  const bool ok = p2p_wait_sum<2>(red, 1, g);
+  if (threadIdx.x == 0) {
+    if (ok) {
+      cg_bookkeeping(S, g[0], g[1], parity, maxit);
+    } else {
+      S[S_REASON] = -100.0;              // a peer never answered
+      S[S_DONE] = 1.0;
+    }
+  }
+}
+
 // step (2) of the iteration + convergence test in the last CTA
 template <int B>
 __global__ void __launch_bounds__(256)
@@ -196,6 +214,13 @@ cg_update_kernel(int pc, const double* __restrict__ pcd, const double* __restric
     if (lane == 0) sm[wid] = t;
   }
   __syncthreads();
+  if (dist == 2) {                 // Schwarz preconditioner: z, r.z and the bookkeeping follow in other kernels
+    if (threadIdx.x == 0) {
+      *ticket = 0u;
+      S[S_PW] = pw;
+    }
+    return;
+  }
   if (red.nranks > 1) {            // fused allreduce over peer memory, then the bookkeeping
     if (threadIdx.x < 32) {
       double t[2] = {sm[0], sm[1]}, g[2];
@@ -613,9 +638,10 @@ template <int B>
 static int ksp_solve_cg(pyn_ksp* k, const double* b, double* x, int* its, int* reason, double* rnorm) {
   pyn_ctx* ctx = k->ctx;
   const int dist = k->A->halo != nullptr && ctx->nranks > 1;
-  // fused peer-memory allreduce instead of NCCL; not under the Schwarz preconditioner, whose apply
-  // sits between the vector update and the reduction of r.z
-  const bool p2p = dist && p2p_enabled(ctx) && k->pc != PYN_PC_ASM;
+  // fused peer-memory allreduce instead of NCCL.  Under the Schwarz preconditioner, whose apply sits
+  // between the vector update and the reduction of r.z, p.Ap still rides in the product / update kernels
+  // and (r.z, z.z) are reduced by cg_scalars_p2p_kernel after the apply
+  const bool p2p = dist && p2p_enabled(ctx);
   P2PRed red_off;
   memset(&red_off, 0, sizeof(red_off));
   red_off.nranks = 1;
@@ -713,13 +739,16 @@ static int ksp_solve_cg(pyn_ksp* k, const double* b, double* x, int* its, int* r
       cg_update_kernel<B><<<gridn, 256, 0, ctx->stream>>>(asmpc ? PYN_PC_NONE : k->pc, k->pcd.p, k->p.p,
                                                           k->w.p, x, k->r.p, k->z.p, nn, S, parity, k->maxit,
                                                           ctx->red_partials, ctx->red_ticket,
-                                                          dist || asmpc ? 1 : 0, red);
+                                                          asmpc ? 2 : (dist ? 1 : 0), red);
       prof_end(ctx);
       PYN_LAUNCHED(ctx);
       // z = M^-1 r with r.z and z.z (this rank's part) into the partial slots
       if (asmpc) PYN_CHECK(asm_apply(ctx, k->asmpc, k->r.p, k->z.p, S + S_LRZ, S + S_DONE));
       if (dist && !p2p) PYN_CHECK(comm_allreduce_sum(ctx, S + S_LRZ, 2));
-      if (asmpc || (dist && !p2p)) {
+      if (asmpc && p2p) {
+        cg_scalars_p2p_kernel<<<1, 32, 0, ctx->stream>>>(S, parity, k->maxit, red);
+        PYN_LAUNCHED(ctx);
+      } else if (asmpc || (dist && !p2p)) {
         cg_scalars_kernel<<<1, 1, 0, ctx->stream>>>(S, parity, k->maxit);
         PYN_LAUNCHED(ctx);
       }
