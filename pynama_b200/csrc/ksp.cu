@@ -634,8 +634,23 @@ static int ksp_pc_dots(pyn_ksp* k, const double* r, double* z, int64_t nn, int g
   return PYN_OK;
 }
 
+// PYN_KSP_TRACE=1: one line per solve on stderr with the host wall time of its phases (us): enqueue of
+// the set-up (guess, residual, preconditioner), the iteration loop up to the moment the host sees the
+// convergence flag, the epilogue (Fischer update + final read-back), and the gap since the previous solve
+// returned (the caller's time: right-hand-side evaluation, Python)
+static double trace_now_us() {
+  timespec ts;
+  clock_gettime(CLOCK_MONOTONIC, &ts);
+  return ts.tv_sec * 1e6 + ts.tv_nsec * 1e-3;
+}
+static double g_trace_last_return = 0.0;
+
 template <int B>
 static int ksp_solve_cg(pyn_ksp* k, const double* b, double* x, int* its, int* reason, double* rnorm) {
+  static const bool trace = getenv("PYN_KSP_TRACE") != nullptr;
+  const double tr0 = trace ? trace_now_us() : 0.0;
+  double tr1 = 0.0, tr2 = 0.0;
+  int tr_chunks = 0;
   pyn_ctx* ctx = k->ctx;
   const int dist = k->A->halo != nullptr && ctx->nranks > 1;
   // fused peer-memory allreduce instead of NCCL.  Under the Schwarz preconditioner, whose apply sits
@@ -699,7 +714,9 @@ static int ksp_solve_cg(pyn_ksp* k, const double* b, double* x, int* its, int* r
   // Chunks of `check_every` iterations; the status of chunk c-1 is read while
   // chunk c runs, so the GPU never idles on the host.
   int it = 0;
+  if (trace) tr1 = trace_now_us();
   for (int chunk = 0;; ++chunk) {
+    tr_chunks = chunk + 1;
     // Successive KLE systems need about the same number of iterations, so the first chunk runs to
     // just short of the previous count and the following ones are short: iterations launched after
     // convergence return at once but still cost their launches (r2c: ~7 iterations per solve under
@@ -767,6 +784,7 @@ static int ksp_solve_cg(pyn_ksp* k, const double* b, double* x, int* its, int* r
     }
     if (it >= k->maxit) break;
   }
+  if (trace) tr2 = trace_now_us();
   if (fischer) {
     // d = x - x0, A d = r0 - r; A-orthogonalise against the basis; append (restart when full)
     fischer_delta_kernel<<<gridv, 256, 0, ctx->stream>>>(x, k->x0.p, k->r0.p, k->r.p, k->fd.p, k->fad.p, n);
@@ -820,6 +838,13 @@ static int ksp_solve_cg(pyn_ksp* k, const double* b, double* x, int* its, int* r
   if (fischer && k->status_host[S_COUNT] != 0.0) k->fischer_n++;
   const double* st = k->status_host;
   k->last_its = (int)st[S_ITS];
+  if (trace) {
+    const double tr3 = trace_now_us();
+    fprintf(stderr, "[ksp_trace] its %d launched %d chunks %d gap_before %.0f setup %.0f loop %.0f epilogue %.0f total %.0f\n",
+            (int)st[S_ITS], it, tr_chunks, g_trace_last_return > 0 ? tr0 - g_trace_last_return : 0.0, tr1 - tr0,
+            tr2 - tr1, tr3 - tr2, tr3 - tr0);
+    g_trace_last_return = tr3;
+  }
   if (its) *its = (int)st[S_ITS];
   if (reason) *reason = st[S_DONE] != 0.0 ? (int)st[S_REASON] : -3;
   if (rnorm) *rnorm = st[S_RNORM];
