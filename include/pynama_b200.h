@@ -297,6 +297,10 @@ int pyn_ksp_set_tolerances(pyn_ksp* k, double rtol, double atol, int maxit, int 
  * iteration merged into one reduction (fused into the product kernel) and the rest of the
  * recurrence in one vector kernel: 2 launches and 1 reduction per iteration instead of 3 and 2. */
 int pyn_ksp_set_cg_single_reduction(pyn_ksp* k, int on);
+/* How many iterations the caller expects the NEXT solve to take (n < 0: no idea).  CG launches its
+ * iterations ahead of the convergence test in chunks; the hint sizes the first chunk, so that few
+ * iterations are launched after convergence.  No effect on the result.  (No counterpart in PETSc.) */
+int pyn_ksp_hint_iterations(pyn_ksp* k, int n);
 /* -pc_asm_coarse <steps> (PYN_PC_ASM only): adds a second level to the Schwarz preconditioner, the Q1
  * space on the element corners with the Galerkin operator P^T K P (probed through K's own product,
  * one product per colour and component), solved approximately by <steps> Chebyshev steps with point

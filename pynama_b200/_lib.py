@@ -122,6 +122,7 @@ _PROTOS = {
     "pyn_ksp_set_tolerances": [vp, c_dbl, c_dbl, c_int, c_int],
     "pyn_ksp_set_fischer_guess": [vp, c_int, c_int],
     "pyn_ksp_set_cg_single_reduction": [vp, c_int],
+    "pyn_ksp_hint_iterations": [vp, c_int],
     "pyn_ksp_set_asm_coarse": [vp, c_int],
     "pyn_ksp_solve": [vp, vp, vp, P(c_int), P(c_int), P(c_dbl)],
     "pyn_ksp_destroy": [vp],

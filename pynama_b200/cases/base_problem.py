@@ -123,7 +123,13 @@ class BaseProblem(object):
             self.dom.applyBoundaryConditionsNS(velFS, "velocity", t, self.nu)
             self.operator.Curl.mult(velFS, w)
 
+        # the same stage of the last step is the best predictor of this solve's iteration count
+        stage = getattr(ts, "stage_index", None)
+        hints = self.__dict__.setdefault("_itsOfStage", {})
+        if stage in hints and hasattr(self.solverKLE.solver, "setIterationHint"):
+            self.solverKLE.solver.setIterationHint(hints[stage])
         self.solverKLE.solve(w)
+        hints[stage] = self.solverKLE.solver.getIterationNumber()
         self.kspIterations += self.solverKLE.solver.getIterationNumber()
         self.kspSolves += 1
 

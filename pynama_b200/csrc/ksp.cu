@@ -575,6 +575,7 @@ struct pyn_ksp {
   int maxit = 10000, restart = 30;
   int check_every = pyn::g_ksp_check_every;
   int last_its = -1;              // iterations of the previous solve: sizes the first chunk of the next
+  int hint_its = -1;              // pyn_ksp_hint_iterations: the caller's expectation for the NEXT solve
   int B = 0;
   int64_t n = 0, nnodes = 0;
   DevBuf<double> pcd, r, z, p, w, S, tmp2;
@@ -723,7 +724,10 @@ static int ksp_solve_cg(pyn_ksp* k, const double* b, double* x, int* its, int* r
     // the two-level preconditioner, up to 9 dead iterations of 7 launches each in chunks of 8).
     // Every rank sees the same counts, so the launch sequences stay identical across ranks.
     const int tail = std::max(1, std::min(k->check_every, asmpc ? 2 : 4));
-    const int first = k->last_its > 2 ? std::min(k->last_its - 1, 4 * k->check_every) : k->check_every;
+    // the caller may know better than "like the last solve" (the RK stages of a time step need
+    // 9, 17, 0, 3, 5, 6, 9 iterations, the same pattern every step: r2l trace)
+    const int expect = k->hint_its >= 0 ? k->hint_its : (k->last_its > 2 ? k->last_its - 1 : -1);
+    const int first = expect >= 0 ? std::max(1, std::min(expect, 4 * k->check_every)) : k->check_every;
     const int want = !g_ksp_adaptive_chunks ? k->check_every : (chunk == 0 ? first : tail);
     const int todo = (k->maxit - it) < want ? (k->maxit - it) : want;
     for (int j = 0; j < todo; ++j, ++it) {
@@ -838,6 +842,7 @@ static int ksp_solve_cg(pyn_ksp* k, const double* b, double* x, int* its, int* r
   if (fischer && k->status_host[S_COUNT] != 0.0) k->fischer_n++;
   const double* st = k->status_host;
   k->last_its = (int)st[S_ITS];
+  k->hint_its = -1;
   if (trace) {
     const double tr3 = trace_now_us();
     fprintf(stderr, "[ksp_trace] its %d launched %d chunks %d gap_before %.0f setup %.0f loop %.0f epilogue %.0f total %.0f\n",
@@ -1153,6 +1158,11 @@ int pyn_ksp_set_asm_coarse(pyn_ksp* k, int steps) {
   return PYN_OK;
 }
 
+int pyn_ksp_hint_iterations(pyn_ksp* k, int n) {
+  PYN_REQUIRE(k, "null ksp");
+  k->hint_its = n;
+  return PYN_OK;
+}
 int pyn_ksp_set_cg_single_reduction(pyn_ksp* k, int on) {
   PYN_REQUIRE(k, "null ksp");
   k->single_reduction = on != 0;

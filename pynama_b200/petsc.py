@@ -872,6 +872,10 @@ class KSP:
         self._cg_single_reduction = bool(flag)
         self._drop()
 
+    def setIterationHint(self, n):
+        """expected iteration count of the next solve (sizes the first chunk of launches; result unchanged)"""
+        self._hint = int(n)
+
     def setASMCoarse(self, steps):
         """second level of -pc_type asm: Q1 coarse space, `steps` Chebyshev steps (0 = off)"""
         self._asm_coarse = int(steps)
@@ -942,6 +946,10 @@ class KSP:
         self.setUp()
         if not self._guess_nonzero and self._fischer[1] == 0:
             x.set(0.0)
+        hint = getattr(self, "_hint", -1)
+        if hint >= 0:
+            call("pyn_ksp_hint_iterations", self._h, hint)
+            self._hint = -1
         its, reason, rn = c_int(), c_int(), c_dbl()
         call("pyn_ksp_solve", self._h, b._h, x._h, ctypes.byref(its), ctypes.byref(reason),
              ctypes.byref(rn))

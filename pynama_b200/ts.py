@@ -78,6 +78,7 @@ class TS:
         self.rejections = 0
         self.rhs_evals = 0
         self.next_rhs_time = None
+        self.stage_index = 0
 
     def create(self, comm=None):
         self._init_fields()
@@ -225,6 +226,7 @@ class TS:
                     self.next_rhs_time = t + c[i + 1] * h
                 else:
                     self.next_rhs_time = t + h + c[1 if tab["fsal"] else 0] * self._dt
+                self.stage_index = i
                 self._rhs(self, t + c[i] * h, stage, k[i])
                 self.rhs_evals += 1
             # u_new = u + h sum b_j k_j  (into y, so a rejected step leaves u untouched)
