@@ -76,7 +76,9 @@ int pyn_prof_get(pyn_ctx* ctx, int cls, int64_t* count, double* total_ms);
  * start; 0 multiplies the interior rows first and lets each warp wait before its first boundary row
  * (measured slower at 2 GPUs, profiles/README.md r2f/r2g; kept for experiments at higher rank counts).
  * "ksp_adaptive_chunks": 0 launches CG iterations in fixed chunks of ksp_check_every between status
- * polls (round 1); default 1 sizes the first chunk from the previous solve's iteration count. */
+ * polls (round 1); default 1 sizes the first chunk from the previous solve's iteration count.
+ * "ksp_graphs": 0 launches the kernels of a CG iteration one by one; default 1 replays one captured CUDA
+ * graph per iteration on a single GPU (same kernels, same arguments, same results). */
 int pyn_tune(const char* key, int value);
 /* page-locked host memory for the caller's staging buffers (cudaMallocHost) */
 int pyn_host_alloc(int64_t bytes, void** out);

@@ -106,6 +106,10 @@ int pyn_tune(const char* key, int value) {
     g_ksp_adaptive_chunks = value != 0;
     return PYN_OK;
   }
+  if (strcmp(key, "ksp_graphs") == 0) {            // 0: plain kernel launches in the CG loop (no CUDA graphs)
+    g_ksp_graphs = value != 0;
+    return PYN_OK;
+  }
   if (strcmp(key, "force_idx64") == 0) {          // tests: take the 64-bit index instantiations on small meshes
     g_force_idx64 = value != 0;
     return PYN_OK;

@@ -61,6 +61,7 @@ extern bool g_force_idx64;
 extern bool g_asm_coarse_unfused;
 extern bool g_halo_wait_at_start;
 extern bool g_ksp_adaptive_chunks;
+extern bool g_ksp_graphs;
 
 }  // namespace pyn
 

@@ -25,6 +25,7 @@ bool g_force_idx64 = false;
 bool g_asm_coarse_unfused = false;
 bool g_halo_wait_at_start = true;    // r2f/r2g: the deferred per-warp wait measured 16 % slower at 2 GPUs
 bool g_ksp_adaptive_chunks = true;
+bool g_ksp_graphs = true;
 
 // device scalar block
 enum {
@@ -576,6 +577,17 @@ struct pyn_ksp {
   int check_every = pyn::g_ksp_check_every;
   int last_its = -1;              // iterations of the previous solve: sizes the first chunk of the next
   int hint_its = -1;              // pyn_ksp_hint_iterations: the caller's expectation for the NEXT solve
+  // one GPU: the launches of a CG iteration differ from one iteration to the next only in the parity of
+  // the iteration, so they are captured once per parity in a CUDA graph and replayed (one graph launch
+  // instead of 3 - 7 kernel launches; the gaps between dependent launches were ~75 us of a 358 us
+  // iteration under the two-level preconditioner, r2n trace).  Re-captured when what the kernels were
+  // given changes (solution vector, stored / matrix-free product, iteration limit).
+  cudaGraphExec_t gexec[2] = {nullptr, nullptr};
+  int gnodes[2] = {0, 0};
+  const void* g_x = nullptr;
+  const void* g_mf = nullptr;
+  int g_maxit = -1;
+  bool g_failed = false;          // capture was refused once: plain launches from then on
   int B = 0;
   int64_t n = 0, nnodes = 0;
   DevBuf<double> pcd, r, z, p, w, S, tmp2;
@@ -595,12 +607,22 @@ struct pyn_ksp {
   DevBuf<double> gcoef;
   AsmPc* asmpc = nullptr;               // -pc_type asm (asm_pc.cuh)
   int asm_coarse = 0;                   // -pc_asm_coarse <k>: Chebyshev steps of the coarse level (0: off)
-  ~pyn_ksp() { delete asmpc; }
+  void drop_graphs() {
+    for (int i = 0; i < 2; ++i) {
+      if (gexec[i]) cudaGraphExecDestroy(gexec[i]);
+      gexec[i] = nullptr;
+    }
+  }
+  ~pyn_ksp() {
+    drop_graphs();
+    delete asmpc;
+  }
 };
 
 template <int B>
 static int ksp_setup_pc(pyn_ksp* k) {
   pyn_ctx* ctx = k->ctx;
+  k->drop_graphs();                 // captured iterations hold pointers into the old preconditioner
   if (k->pc == PYN_PC_NONE) {
     k->pc_ready = true;
     return PYN_OK;
@@ -714,24 +736,8 @@ static int ksp_solve_cg(pyn_ksp* k, const double* b, double* x, int* its, int* r
   memset(&hw, 0, sizeof(hw));
   // Chunks of `check_every` iterations; the status of chunk c-1 is read while
   // chunk c runs, so the GPU never idles on the host.
-  int it = 0;
-  if (trace) tr1 = trace_now_us();
-  for (int chunk = 0;; ++chunk) {
-    tr_chunks = chunk + 1;
-    // Successive KLE systems need about the same number of iterations, so the first chunk runs to
-    // just short of the previous count and the following ones are short: iterations launched after
-    // convergence return at once but still cost their launches (r2c: ~7 iterations per solve under
-    // the two-level preconditioner, up to 9 dead iterations of 7 launches each in chunks of 8).
-    // Every rank sees the same counts, so the launch sequences stay identical across ranks.
-    const int tail = std::max(1, std::min(k->check_every, asmpc ? 2 : 4));
-    // the caller may know better than "like the last solve" (the RK stages of a time step need
-    // 9, 17, 0, 3, 5, 6, 9 iterations, the same pattern every step: r2l trace)
-    const int expect = k->hint_its >= 0 ? k->hint_its : (k->last_its > 2 ? k->last_its - 1 : -1);
-    const int first = expect >= 0 ? std::max(1, std::min(expect, 4 * k->check_every)) : k->check_every;
-    const int want = !g_ksp_adaptive_chunks ? k->check_every : (chunk == 0 ? first : tail);
-    const int todo = (k->maxit - it) < want ? (k->maxit - it) : want;
-    for (int j = 0; j < todo; ++j, ++it) {
-      const int parity = it & 1;
+  // the launches of iteration `it`
+  auto enqueue_iteration = [&](int it, int parity) -> int {
       P2PRed red = p2p ? p2p_next(ctx) : red_off;
       if (single_reduction) {
         // w = A u with w.u fused; then the whole recurrence (and r.u, u.u of the next iterate)
@@ -752,7 +758,7 @@ static int ksp_solve_cg(pyn_ksp* k, const double* b, double* x, int* its, int* r
         prof_end(ctx);
         PYN_LAUNCHED(ctx);
         if (dist && !p2p) PYN_CHECK(comm_allreduce_sum(ctx, S + S_SR + 1, 2));
-        continue;
+        return PYN_OK;
       }
       PYN_CHECK(spmv_dot(k->A, k->p.p, k->w.p, S + S_PW, S + S_DONE, &red));
       if (dist && !p2p) PYN_CHECK(comm_allreduce_sum(ctx, S + S_PW, 1));
@@ -777,6 +783,61 @@ static int ksp_solve_cg(pyn_ksp* k, const double* b, double* x, int* its, int* r
       cg_direction_kernel<<<grid_for(ctx, n > 0 ? n : 1, 256), 256, 0, ctx->stream>>>(k->z.p, k->p.p, n, S, parity);
       prof_end(ctx);
       PYN_LAUNCHED(ctx);
+      return PYN_OK;
+  };
+  // one GPU, plain CG recurrence, no per-launch profiling events: replay captured graphs
+  bool use_graph = g_ksp_graphs && !dist && !single_reduction && !ctx->prof_on && !k->g_failed;
+  if (use_graph && (k->g_x != (const void*)x || k->g_mf != (const void*)k->A->mf || k->g_maxit != k->maxit)) {
+    k->drop_graphs();
+    k->g_x = x;
+    k->g_mf = k->A->mf;
+    k->g_maxit = k->maxit;
+  }
+  int it = 0;
+  if (trace) tr1 = trace_now_us();
+  for (int chunk = 0;; ++chunk) {
+    tr_chunks = chunk + 1;
+    // Successive KLE systems need about the same number of iterations, so the first chunk runs to
+    // just short of the previous count and the following ones are short: iterations launched after
+    // convergence return at once but still cost their launches (r2c: ~7 iterations per solve under
+    // the two-level preconditioner, up to 9 dead iterations of 7 launches each in chunks of 8).
+    // Every rank sees the same counts, so the launch sequences stay identical across ranks.
+    const int tail = std::max(1, std::min(k->check_every, asmpc ? 2 : 4));
+    // the caller may know better than "like the last solve" (the RK stages of a time step need
+    // 9, 17, 0, 3, 5, 6, 9 iterations, the same pattern every step: r2l trace)
+    const int expect = k->hint_its >= 0 ? k->hint_its : (k->last_its > 2 ? k->last_its - 1 : -1);
+    const int first = expect >= 0 ? std::max(1, std::min(expect, 4 * k->check_every)) : k->check_every;
+    const int want = !g_ksp_adaptive_chunks ? k->check_every : (chunk == 0 ? first : tail);
+    const int todo = (k->maxit - it) < want ? (k->maxit - it) : want;
+    for (int j = 0; j < todo; ++j, ++it) {
+      const int parity = it & 1;
+      if (use_graph) {
+        if (!k->gexec[parity]) {
+          const int64_t l0 = ctx->launches;
+          cudaGraph_t g = nullptr;
+          bool ok = cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeThreadLocal) == cudaSuccess;
+          if (ok) {
+            const int rc = enqueue_iteration(it, parity);
+            ok = cudaStreamEndCapture(ctx->stream, &g) == cudaSuccess && rc == PYN_OK && g != nullptr;
+          }
+          if (ok) ok = cudaGraphInstantiate(&k->gexec[parity], g, 0) == cudaSuccess;
+          if (g) cudaGraphDestroy(g);
+          k->gnodes[parity] = (int)(ctx->launches - l0);
+          ctx->launches = l0;
+          if (!ok) {                       // e.g. a driver that will not capture the cooperative launch
+            cudaGetLastError();
+            k->drop_graphs();
+            k->g_failed = true;
+            use_graph = false;
+          }
+        }
+        if (use_graph) {
+          PYN_CUDA(cudaGraphLaunch(k->gexec[parity], ctx->stream));
+          ctx->launches += k->gnodes[parity];
+          continue;
+        }
+      }
+      PYN_CHECK(enqueue_iteration(it, parity));
     }
     const int slot = chunk & 1;
     PYN_CUDA(cudaMemcpyAsync(k->status_host + slot * S_COUNT, S, sizeof(double) * S_COUNT,
