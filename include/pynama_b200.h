@@ -78,10 +78,7 @@ int pyn_prof_get(pyn_ctx* ctx, int cls, int64_t* count, double* total_ms);
  * "ksp_adaptive_chunks": 0 launches CG iterations in fixed chunks of ksp_check_every between status
  * polls (round 1); default 1 sizes the first chunk from the previous solve's iteration count.
  * "ksp_graphs": 0 launches the kernels of a CG iteration one by one; default 1 replays one captured CUDA
- * graph per iteration on a single GPU (same kernels, same arguments, same results).
- * "assemble_row_classes": 0 sends every row of the KLE matrices through the gather kernel; default 1
- * gathers one representative per class of rows with identical contribution lists and dof classes and
- * copies it to the other rows of the class (bit-identical values). */
+ * graph per iteration on a single GPU (same kernels, same arguments, same results). */
 int pyn_tune(const char* key, int value);
 /* page-locked host memory for the caller's staging buffers (cudaMallocHost) */
 int pyn_host_alloc(int64_t bytes, void** out);

@@ -110,10 +110,6 @@ int pyn_tune(const char* key, int value) {
     g_ksp_graphs = value != 0;
     return PYN_OK;
   }
-  if (strcmp(key, "assemble_row_classes") == 0) {   // 0: every row of the KLE matrices through the gather kernel
-    g_assemble_row_classes = value != 0;
-    return PYN_OK;
-  }
   if (strcmp(key, "force_idx64") == 0) {          // tests: take the 64-bit index instantiations on small meshes
     g_force_idx64 = value != 0;
     return PYN_OK;
@@ -368,7 +364,6 @@ int pyn_mesh_set_dof_class(pyn_mesh* mesh, const uint8_t* cls) {
   PYN_CHECK(mesh->nodecls.upload(pack.data(), mesh->nnodes));
   PYN_CUDA(cudaStreamSynchronize(mesh->ctx->stream));
   mesh->has_cls = true;
-  mesh->dof_version++;
   return PYN_OK;
 }
 

@@ -594,16 +594,14 @@ __global__ void __launch_bounds__(256, MINB)
 numeric_kle_kernel(int64_t nrows, const int64_t* __restrict__ g_rowptr,
                    const int32_t* __restrict__ g_colidx, const int64_t* __restrict__ cptr,
                    const int2* __restrict__ csrc, const double* __restrict__ ebs, int64_t npairs64,
-                   const uint8_t* __restrict__ nodecls, KleTargets T, const int32_t* __restrict__ rowlist) {
-  // rowlist != NULL: nrows entries, the rows to assemble (representatives of the row-value classes)
+                   const uint8_t* __restrict__ nodecls, KleTargets T) {
   const I npairs = (I)npairs64;
   using Rec = KleRecord<D>;
   constexpr int RS = Rec::RS, H = Rec::HALF;
   const int lane = threadIdx.x & 31;
   const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
-  for (int64_t ri = warp; ri < nrows; ri += nwarps) {
-    const int64_t r = rowlist ? (int64_t)rowlist[ri] : ri;
+  for (int64_t r = warp; r < nrows; r += nwarps) {
     const int64_t s0 = g_rowptr[r];
     const int len = (int)(g_rowptr[r + 1] - s0);
     int64_t pK = 0, pKr = 0, pW = 0, pD = 0;
@@ -649,134 +647,6 @@ numeric_kle_kernel(int64_t nrows, const int64_t* __restrict__ g_rowptr,
     kle_zero_pad<D * DW>(T.Rw, pW, nW, oW, lane);
     kle_zero_pad<D>(T.Rd, pD, nD, oD, lane);
   }
-}
-
-// ---- row-value classes ------------------------------------------------------------------------------
-__device__ __forceinline__ unsigned long long mix64(unsigned long long x) {      // splitmix64 finaliser
-  x += 0x9E3779B97F4A7C15ull;
-  x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
-  x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
-  return x ^ (x >> 31);
-}
-
-// sig[2r], sig[2r+1]: 128-bit signature of everything the values of row r depend on -- its dof classes,
-// and slot by slot (position included) the column's dof classes, whether it is the diagonal slot, and the
-// ordered list of contributions (record store index, local pair).  One warp per row, lanes over slots.
-__global__ void __launch_bounds__(256)
-row_signature_kernel(int64_t nrows, const int64_t* __restrict__ g_rowptr, const int32_t* __restrict__ g_colidx,
-                     const int64_t* __restrict__ cptr, const int2* __restrict__ csrc,
-                     const uint8_t* __restrict__ nodecls, unsigned long long* __restrict__ sig) {
-  const int lane = threadIdx.x & 31;
-  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
-  for (int64_t r = warp; r < nrows; r += nwarps) {
-    const int64_t s0 = g_rowptr[r];
-    const int len = (int)(g_rowptr[r + 1] - s0);
-    unsigned long long h0 = 0, h1 = 0;
-    for (int u = lane; u < len; u += 32) {
-      const int32_t c = g_colidx[s0 + u];
-      const int64_t k0 = cptr[s0 + u], k1 = cptr[s0 + u + 1];
-      unsigned long long a = mix64(((unsigned long long)nodecls[c] << 1) | (unsigned long long)(c == r));
-      unsigned long long b = mix64(a ^ 0xA5A5A5A5A5A5A5A5ull);
-      for (int64_t k = k0; k < k1; ++k) {                       // ordered: the summation order is part of the value
-        const int2 e = csrc[k];
-        const unsigned long long w = ((unsigned long long)(unsigned)e.x << 32) | (unsigned)e.y;
-        a = mix64(a ^ w);
-        b = mix64(b + w * 0x9E3779B97F4A7C15ull);
-      }
-      h0 += mix64(a ^ ((unsigned long long)u * 0xD6E8FEB86659FD93ull));      // position-tagged, summed
-      h1 += mix64(b + ((unsigned long long)u << 20));
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      h0 += __shfl_xor_sync(0xffffffffu, h0, o);
-      h1 += __shfl_xor_sync(0xffffffffu, h1, o);
-    }
-    if (lane == 0) {
-      const unsigned long long tail = ((unsigned long long)nodecls[r] << 32) | (unsigned)len;
-      sig[2 * r] = mix64(h0 ^ tail);
-      sig[2 * r + 1] = mix64(h1 + tail);
-    }
-  }
-}
-
-// values of row src -> row dst in every target (same block count and layout by construction of the
-// classes): 16-byte streaming copies, one warp per row.  Row starts are 32-byte aligned (rows hold a
-// multiple of 4 blocks) and a row's value count is a multiple of 4.
-template <int D, int DW>
-__global__ void __launch_bounds__(256)
-row_copy_kernel(int64_t ncopy, const int32_t* __restrict__ dst, const int32_t* __restrict__ src, KleTargets T) {
-  const int lane = threadIdx.x & 31;
-  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
-  for (int64_t i = warp; i < ncopy; i += nwarps) {
-    const int64_t rd = dst[i], rs = src[i];
-    const KleTarget* t[4] = {&T.K, &T.Krhs, &T.Rw, &T.Rd};
-    const int bb[4] = {D * D, D * D, D * DW, D};
-#pragma unroll
-    for (int m = 0; m < 4; ++m) {
-      if (!t[m]->rowptr) continue;
-      const int64_t ps = t[m]->rowptr[rs], n = (t[m]->rowptr[rs + 1] - ps) * bb[m];
-      const int64_t pd = t[m]->rowptr[rd];
-      const double2* __restrict__ a = reinterpret_cast<const double2*>(t[m]->val + ps * bb[m]);
-      double2* __restrict__ b = reinterpret_cast<double2*>(t[m]->val + pd * bb[m]);
-      for (int64_t q = lane; q < n / 2; q += 32) {
-        const double2 v = a[q];
-        __stcs(b + q, v);
-      }
-    }
-  }
-}
-
-// groups the rows of the dense graph by signature; fills mesh->rep_rows / copy_dst / copy_src
-static int build_row_classes(pyn_mesh* mesh, const NodeGraph& g, const int2* src) {
-  pyn_ctx* ctx = mesh->ctx;
-  mesh->rowcls_class_version = mesh->class_version;
-  mesh->rowcls_dof_version = mesh->dof_version;
-  mesh->rowcls_state = 0;
-  if (g.nrows >= (int64_t)0x7fffffff) return PYN_OK;
-  DevBuf<unsigned long long> sig;
-  PYN_CHECK(sig.alloc(ctx, 2 * g.nrows));
-  row_signature_kernel<<<grid_for(ctx, g.nrows * 32, 256), 256, 0, ctx->stream>>>(
-      g.nrows, g.rowptr.p, g.colidx.p, g.cptr.p, src, mesh->nodecls.p, sig.p);
-  PYN_LAUNCHED(ctx);
-  std::vector<unsigned long long> h((size_t)(2 * g.nrows));
-  PYN_CHECK(sig.download(h.data(), 2 * g.nrows));
-  struct Key {
-    unsigned long long a, b;
-    bool operator==(const Key& o) const { return a == o.a && b == o.b; }
-  };
-  struct KeyHash {
-    size_t operator()(const Key& k) const { return (size_t)(k.a ^ (k.b * 0x9E3779B97F4A7C15ull)); }
-  };
-  std::unordered_map<Key, int32_t, KeyHash> rep;
-  rep.reserve(4096);
-  std::vector<int32_t> reps, cdst, csrc_rows;
-  for (int64_t r = 0; r < g.nrows; ++r) {          // ascending: the representative is the lowest row of a class
-    const Key k{h[(size_t)(2 * r)], h[(size_t)(2 * r + 1)]};
-    auto it = rep.find(k);
-    if (it == rep.end()) {
-      rep.emplace(k, (int32_t)r);
-      reps.push_back((int32_t)r);
-    } else {
-      cdst.push_back((int32_t)r);
-      csrc_rows.push_back(it->second);
-    }
-    if ((int64_t)reps.size() > g.nrows / 4 + 64 && r > 4096) return PYN_OK;   // little to share: gather every row
-  }
-  if ((int64_t)reps.size() > g.nrows / 4 + 64) return PYN_OK;
-  mesh->n_rep_rows = (int64_t)reps.size();
-  mesh->n_copy_rows = (int64_t)cdst.size();
-  PYN_CHECK(mesh->rep_rows.alloc(ctx, mesh->n_rep_rows + 1));
-  PYN_CHECK(mesh->rep_rows.upload(reps.data(), mesh->n_rep_rows));
-  PYN_CHECK(mesh->copy_dst.alloc(ctx, mesh->n_copy_rows + 1));
-  PYN_CHECK(mesh->copy_src.alloc(ctx, mesh->n_copy_rows + 1));
-  if (mesh->n_copy_rows) {
-    PYN_CHECK(mesh->copy_dst.upload(cdst.data(), mesh->n_copy_rows));
-    PYN_CHECK(mesh->copy_src.upload(csrc_rows.data(), mesh->n_copy_rows));
-  }
-  mesh->rowcls_state = 1;
-  return PYN_OK;
 }
 
 static KleTarget kle_target(const MatSpec& sp, const pyn_mat* m) {
@@ -829,23 +699,13 @@ static int assemble_kle_fused_impl(pyn_mesh* mesh, const MatSpec* sp, pyn_mat** 
   // compiled for 2 resident CTAs per SM (128 registers, no spills): measured fastest on B200
   // (3 CTAs at 80 registers spill the pipeline state: 0.93 against 0.78 ms at 16^3, ngl = 4;
   // two half passes K|Krhs and Rw|Rd: 0.82 ms)
+  const int grid = grid_for(ctx, g.nrows * 32, 256, 2);   // one resident wave
   // 32-bit contribution / record indices when they fit
   const bool idx32 = !g_force_idx64 && g.ncontrib < (int64_t)0x7fffffff &&
                      mesh->nclass * npairs * kle_record_stride(d) < (int64_t)0x7fffffff;
-  // row-value classes (uniform meshes: a few hundred distinct rows among 117 649 at 16^3, ngl = 4)
-  if (g_assemble_row_classes && getenv("PYN_ASSEMBLE_PER_MATRIX") == nullptr &&
-      (mesh->rowcls_state < 0 || mesh->rowcls_class_version != mesh->class_version ||
-       mesh->rowcls_dof_version != mesh->dof_version))
-    PYN_CHECK(build_row_classes(mesh, g, src));
-  const bool shared = g_assemble_row_classes && mesh->rowcls_state == 1 &&
-                      mesh->rowcls_class_version == mesh->class_version &&
-                      mesh->rowcls_dof_version == mesh->dof_version;
-  const int64_t nrun = shared ? mesh->n_rep_rows : g.nrows;
-  const int32_t* rowlist = shared ? mesh->rep_rows.p : nullptr;
-  const int grid = grid_for(ctx, nrun * 32, 256, 2);   // one resident wave
-#define NKLE_ARGS                                                                                \
-  <<<grid, 256, 0, ctx->stream>>>(nrun, g.rowptr.p, g.colidx.p, g.cptr.p, src, sp[0].ebs, npairs, \
-                                  mesh->nodecls.p, T, rowlist)
+#define NKLE_ARGS                                                                                   \
+  <<<grid, 256, 0, ctx->stream>>>(g.nrows, g.rowptr.p, g.colidx.p, g.cptr.p, src, sp[0].ebs, npairs, \
+                                  mesh->nodecls.p, T)
 #define NKLE_CALL(D, DW, MB)                                              \
   do {                                                                    \
     if (idx32) numeric_kle_kernel<D, DW, MB, int32_t> NKLE_ARGS;          \
@@ -856,16 +716,8 @@ static int assemble_kle_fused_impl(pyn_mesh* mesh, const MatSpec* sp, pyn_mat** 
   else NKLE_CALL(3, 3, 2);
 #undef NKLE_CALL
 #undef NKLE_ARGS
-  PYN_LAUNCHED(ctx);
-  if (shared && mesh->n_copy_rows > 0) {
-    const int gridc = grid_for(ctx, mesh->n_copy_rows * 32, 256, 8);
-    if (d == 2)
-      row_copy_kernel<2, 1><<<gridc, 256, 0, ctx->stream>>>(mesh->n_copy_rows, mesh->copy_dst.p, mesh->copy_src.p, T);
-    else
-      row_copy_kernel<3, 3><<<gridc, 256, 0, ctx->stream>>>(mesh->n_copy_rows, mesh->copy_dst.p, mesh->copy_src.p, T);
-    PYN_LAUNCHED(ctx);
-  }
   prof_end(ctx);
+  PYN_LAUNCHED(ctx);
   return PYN_OK;
 }
 

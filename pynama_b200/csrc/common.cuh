@@ -62,7 +62,6 @@ extern bool g_asm_coarse_unfused;
 extern bool g_halo_wait_at_start;
 extern bool g_ksp_adaptive_chunks;
 extern bool g_ksp_graphs;
-extern bool g_assemble_row_classes;
 
 }  // namespace pyn
 

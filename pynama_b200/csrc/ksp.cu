@@ -26,7 +26,6 @@ bool g_asm_coarse_unfused = false;
 bool g_halo_wait_at_start = true;    // r2f/r2g: the deferred per-warp wait measured 16 % slower at 2 GPUs
 bool g_ksp_adaptive_chunks = true;
 bool g_ksp_graphs = true;
-bool g_assemble_row_classes = false;   // (default flips to true once tests/test_gpu_assembly.py has run it on a GPU)
 
 // device scalar block
 enum {

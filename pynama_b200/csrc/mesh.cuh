@@ -64,17 +64,6 @@ struct pyn_mesh {
   pyn::NodeGraph stencil;                  // grid-line pairs only (operators, compact)
   bool has_stencil = false;
   pyn::DevBuf<int32_t> stencil_of_dense;   // [nn*nn] stencil pair id of dense pair or -1
-  // Row-value classes of the KLE matrices (assemble.cu): rows of the dense graph whose slots carry the
-  // same contribution lists and dof classes get the same values in all eight matrices (on a uniform box
-  // every node at the same position inside an element).  One representative row per class goes through
-  // the gather kernel, the other rows are streamed copies.  Recomputed when the congruence classes or
-  // the dof classes change; rowcls_state: -1 unknown, 0 not worth it (e.g. every cell its own class), 1 on.
-  int rowcls_state = -1;
-  int64_t rowcls_class_version = -1, rowcls_dof_version = -1;
-  int64_t dof_version = 0;                  // bumped by pyn_mesh_set_dof_class
-  int64_t n_rep_rows = 0, n_copy_rows = 0;
-  pyn::DevBuf<int32_t> rep_rows;            // [n_rep_rows] ascending
-  pyn::DevBuf<int32_t> copy_dst, copy_src;  // [n_copy_rows] row <- its representative
   double phase_ms[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   pyn_matfree* mf = nullptr;               // matrix-free K data, built on first use
   ~pyn_mesh();                             // matfree.cu

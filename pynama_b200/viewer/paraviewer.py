@@ -27,6 +27,7 @@ class Paraviewer:
         self.enabled = bool(Options().getBool("pynama_save", False))
         self._steps = []               # [(step, time, [(name, kind, ncomp, file)])]
         self._nnodes = 0
+        self._mesh_file = None          # set by saveMesh; xdmf() leaves the geometry out while it is None
         self.dim = None
 
     def configure(self, dim, saveDir=None):
@@ -73,11 +74,12 @@ class Paraviewer:
         for step, time, items in self._steps:
             out += [f'   <Grid Name="mesh1" GridType="Uniform">',
                     f'    <Time Value="{time!r}"/>',
-                    f'    <Topology TopologyType="Polyvertex" Dimensions="{n}"/>',
-                    f'    <Geometry GeometryType="{geo}">',
-                    f'     <DataItem Dimensions="{n} {dim}" NumberType="Float" Precision="8" Format="Binary" '
-                    f'Endian="Little">{self._mesh_file}</DataItem>',
-                    '    </Geometry>']
+                    f'    <Topology TopologyType="Polyvertex" Dimensions="{n}"/>']
+            if self._mesh_file is not None:            # createMesh(saveMesh=False): data without a geometry block
+                out += [f'    <Geometry GeometryType="{geo}">',
+                        f'     <DataItem Dimensions="{n} {dim}" NumberType="Float" Precision="8" Format="Binary" '
+                        f'Endian="Little">{self._mesh_file}</DataItem>',
+                        '    </Geometry>']
             for vname, kind, ncomp, fname in items:
                 dims = f"{n}" if ncomp == 1 else f"{n} {ncomp}"
                 out += [f'    <Attribute Name="{vname}" AttributeType="{kind}" Center="Node">',

@@ -196,32 +196,3 @@ def test_64bit_index_path_equals_32bit_and_oracle(mode, nelem, ngl, perturb):
         for x, y in zip(ga, gb):
             assert np.array_equal(x, y), name
         assert_same_csr(csr_of(b[name]), want[name], name=name)
-
-
-@pytest.mark.parametrize("mode,nelem,ngl", [("FS", [5, 4, 4], 3), ("NS", [4, 4, 3], 3), ("NS", [6, 5], 4), ("FS", [3, 3, 3], 4)])
-def test_row_value_classes_are_bit_identical_to_the_full_gather(mode, nelem, ngl):
-    """uniform box: rows with the same contribution lists and dof classes are gathered once and copied
-    (pyn_tune assemble_row_classes, default on); every matrix must equal, bit for bit, the assembly that
-    sends every row through the gather kernel -- and the oracle"""
-    from pynama_b200 import _lib
-    mesh, dm, tab = _setup(nelem, ngl)
-    cls = ns_classes(mesh, None) if mode == "NS" else fs_classes(mesh)
-    dm.set_dof_class(cls)
-    shared = dm.assemble_kle(mode)
-    _lib.call("pyn_tune", b"assemble_row_classes", 0)
-    try:
-        full = dm.assemble_kle(mode)
-    finally:
-        _lib.call("pyn_tune", b"assemble_row_classes", 1)
-    want = assembly.assemble_kle(tab, mesh.corner_xyz, mesh.elem_nodes, mesh.nnodes, cls, mode)
-    for name in want:
-        if mode == "FS" and name == "Rd":
-            continue
-        a, b = shared[name].getValuesCSR(), full[name].getValuesCSR()
-        for x, y in zip(a, b):
-            assert np.array_equal(x, y), name
-        assert_same_csr(csr_of(shared[name]), want[name], name=name)
-    # and the products (padding blocks included) agree bit for bit
-    from pynama_b200.petsc import Vec
-    x = Vec().createWithArray(np.random.default_rng(5).uniform(-1, 1, shared["K"].getSize()[1]))
-    assert np.array_equal((shared["K"] * x).getArray(), (full["K"] * x).getArray())

@@ -23,7 +23,9 @@ from pynama_b200.device_mesh import DeviceMesh  # noqa: E402
 from pynama_b200.domain.box_mesh import BoxMesh  # noqa: E402
 from pynama_b200.petsc import COMM_WORLD, KSP, PC, Context, Layout, PynamaError, Vec  # noqa: E402
 
-GPU_BYTES = 170e9          # usable HBM per B200 (180 GB minus context, pools, Krylov vectors)
+GPU_BYTES = 120e9          # what the estimate may reach per B200: r2k showed 128^3 / ngl=4 on 8 GPUs (estimate
+                           # 161 GB) failing in a 66 GB allocation -- graphs, the halo-layer elements and the
+                           # transient buffers of the symbolic phase are not in the estimate
 PEAK = 6548.8
 
 
