@@ -5,8 +5,9 @@ Workload (N=1): configs[1], "3-D Taylor-Green vortex, 16^3 elements, ngl=4, one
 B200".  A *step* is one RK-5BS time step of the vorticity-transport equation
 through the reference's own time loop (run_case.py:152-162 -> TS -> evalRHS,
 base_problem.py:111-136): 7 right-hand-side evaluations (FSAL), each = BC scatter
-+ KLE solve (CG + node-block Jacobi on K, to --rtol) + SpMV with Rw, Krhs, SrT,
-DivSrT, Curl + the pointwise stress kernel.  The operators are assembled once
++ KLE solve (CG on K to --rtol; preconditioner --pc: the two-level element Schwarz
+method by default, node-block Jacobi in the "alt_pc_bjacobi" block) + SpMV with Rw,
+Krhs, SrT, DivSrT, Curl + the pointwise stress kernel.  The operators are assembled once
 before the loop, as in the reference (setUpSolver, base_problem.py:156-179); the
 assembly is timed separately and reported under "assembly".
 

@@ -293,7 +293,7 @@ int pyn_vec_device_ptr(pyn_vec* v, void** ptr);
 int pyn_ksp_create(pyn_ctx* ctx, pyn_mat* a, int type, int pc, pyn_ksp** out);
 int pyn_ksp_set_tolerances(pyn_ksp* k, double rtol, double atol, int maxit, int restart);
 /* KSPSetUseFischerGuess / -ksp_fischer_guess <model>,<size>: model 1 (A-conjugate projection
- * of the new right-hand side on the last <size> <= 8 solution increments) forms the initial
+ * of the new right-hand side on the last <size> <= 32 solution increments) forms the initial
  * guess; size 0 switches it off (default, as in PETSc). */
 /* KSPCGUseSingleReduction / -ksp_cg_single_reduction: CG with the inner products of an
  * iteration merged into one reduction (fused into the product kernel) and the rest of the

@@ -9,7 +9,9 @@ from $PYNAMA_REFERENCE (default /root/reference; skipped when absent -- the GPU 
   (AST walk over the files, receivers recognised by name);
 * `BaseProblem.__init__`, `readMaterialData`, `setUpTimeSolver` run on the shim without a GPU;
 * with a GPU: `setUp`, `setUpSolver` (the reference's KleSolver/KspSolver on the drop-in KSP), one
-  `evalRHS` and one `ts.step()` give the fields of the repo's own mirror of the same case.
+  `evalRHS` and one `ts.step()` give the fields of the repo's own mirror of the same case.  NOTE: this last
+  test needs the reference tree AND a GPU on the same machine; in this project's two machines (container:
+  reference, no GPU; GPU box: GPU, no reference) it has never run -- it is written for a maintainer's machine.
 """
 import ast
 import importlib
@@ -147,6 +149,17 @@ def test_reference_base_problem_constructs_on_the_shim(ref):
     # the reference's KspSolver is a subclass of the drop-in KSP and skips its __init__ (kle_solver.py:51-52)
     ksp = ref.kle.KspSolver()
     assert ksp.logger is None and hasattr(ksp, "createSolver")
+    # setUp() as far as it goes without a device: Domain (mesh, boundary conditions) and viewer come up on the
+    # drop-in packages; createMesh then makes the first Vec, and the library says loudly that it has no CPU path
+    fem.setUpDomain()
+    fem.setUpViewer()
+    assert (fem.dim, fem.dim_w, fem.dim_s) == (3, 3, 6) and fem.dom.getNumOfNodes() == 7 ** 3
+    assert fem.dom.getBoundaryType() == "FS"
+    from tests.conftest import _cuda_devices
+    if _cuda_devices() == 0:
+        from pynama_b200._lib import PynamaError
+        with pytest.raises(PynamaError, match="no CPU path"):
+            fem.createMesh()
 
 
 @pytest.mark.gpu
