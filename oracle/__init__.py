@@ -10,6 +10,11 @@ Only ``tests/``, ``__graft_entry__.smoke()`` and ``bench.py``'s CPU-baseline /
 the product path is CUDA behind ``libpynama_b200.so`` and fails loudly without
 it.
 
+Modules: sem (tables, element matrices), assembly (scatter-add, also restricted to a
+sample of rows), timestep (KLE solve, RHS, RK5BS fixed and adaptive, preconditioners as
+numpy), ibm (immersed boundary), boxmesh (standalone box-mesh tables), cport + ckle.c
+(C + OpenMP assembly / SpMV / CG for the CPU arm of bench.py at the full size).
+
 Pinning: the element tables and element matrices are pinned against golden
 vectors generated from the reference's own ``Spectral`` class
 (``tests/golden/make_golden.py`` -> ``tests/golden/*.npz``); the assembled
