@@ -121,8 +121,9 @@ class ClockSampler:
 
 
 def workload_name(args):
+    which = "BASELINE.json configs[1]" if (args.nelem, args.ngl) == (16, 4) else "NOT the configs[1] size 16^3 / ngl=4"
     return (f"3-D Taylor-Green vortex, {args.nelem}^3 elements, ngl={args.ngl}, unit box "
-            "(BASELINE.json configs[1]); one RK5BS time step = 7 evalRHS")
+            f"({which}); one RK5BS time step = 7 evalRHS")
 
 
 def case_config(nelem, ngl):
