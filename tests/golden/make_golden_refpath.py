@@ -43,6 +43,12 @@ CASES = {
     "tg3d": ("taylor-green3d", dict(lower=[0, 0, 0], upper=[1, 1, 1], nelem=[2, 3, 2]), 3, 2e-3, 2),
     "cavity2d": ("cavity-2d", dict(lower=[0, 0], upper=[1, 1], nelem=[4, 3]), 3, 5e-3, 2),
     "cavity3d": ("cavity", dict(lower=[0, 0, 0], upper=[3, 1, 1], nelem=[3, 2, 2]), 3, 5e-3, 2),
+    # non-affine cells (interior vertices displaced): no two element matrices are equal, so a wrong cell -> corner or
+    # cell -> node association cannot hide behind identical blocks
+    "tg2d_p": ("taylor-green", dict(lower=[0, 0], upper=[1, 1], nelem=[3, 2], perturb=0.15), 5, 2e-3, 2),
+    "tg3d_p": ("taylor-green3d", dict(lower=[0, 0, 0], upper=[1, 1, 1], nelem=[2, 2, 2], perturb=0.2), 3, 2e-3, 2),
+    "cavity3d_p": ("cavity", dict(lower=[0, 0, 0], upper=[3, 1, 1], nelem=[3, 3, 2], perturb=0.2), 2, 5e-3, 2),
+    "tg3d_ngl4": ("taylor-green3d", dict(lower=[0, 0, 0], upper=[2, 1, 1], nelem=[2, 1, 1]), 4, 2e-3, 2),
 }
 
 
@@ -60,7 +66,7 @@ def run_case(ref, name):
     fem = ref.base_problem.BaseProblem(cfg, case=case)
     fem.setUp()
     fem.setUpSolver()
-    out = {"ngl": np.int64(ngl), "dim": np.int64(fem.dim), "dt": np.float64(dt), "nsteps": np.int64(nsteps),
+    out = {"perturb": np.float64(box.get("perturb", 0.0)), "ngl": np.int64(ngl), "dim": np.int64(fem.dim), "dt": np.float64(dt), "nsteps": np.int64(nsteps),
            "rho": np.float64(fem.rho), "mu": np.float64(fem.mu), "bc_type": np.array(fem.dom.getBoundaryType()),
            "case": np.array(case)}
     dm = fem.dom.getDM()

@@ -30,6 +30,9 @@ def make_box_dom(dmplex, PETSc):
         # ---- construction --------------------------------------------------------------------------
         def create(self, data):
             self._cfg = {k: list(data[k]) for k in ("nelem", "lower", "upper")}
+            # not a key of the reference's case files: interior vertices displaced by perturb * h (seeded), so that
+            # the cells are non-affine and no two element matrices are equal
+            self._perturb = float(data.get("perturb", 0.0))
             self.dim = len(self._cfg["nelem"])
             self.dim_w = 1 if self.dim == 2 else 3
             self.dim_s = 3 if self.dim == 2 else 6
@@ -42,7 +45,7 @@ def make_box_dom(dmplex, PETSc):
         def setFemIndexing(self, ngl):
             self.indicesManager = dmplex.IndicesManager(self.dim, ngl, self.comm)
             c = self._cfg
-            self._m = boxmesh.box_mesh(c["nelem"], c["lower"], c["upper"], ngl)
+            self._m = boxmesh.box_mesh(c["nelem"], c["lower"], c["upper"], ngl, perturb=self._perturb)
             self.cellStart, self.cellEnd = 0, self._m.nel
 
         def getTotalNodes(self):

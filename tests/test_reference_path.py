@@ -54,7 +54,12 @@ def dof_classes(g):
 
 
 def test_golden_files_present():
-    assert set(CASES) >= {"uniform2d", "tg2d", "tg3d", "cavity2d", "cavity3d"}
+    assert set(CASES) >= {"uniform2d", "tg2d", "tg3d", "cavity2d", "cavity3d", "tg2d_p", "tg3d_p", "cavity3d_p",
+                          "tg3d_ngl4"}
+    # the perturbed cases really have pairwise different cells
+    g = load("tg3d_p")
+    X = g["corner_xyz"]
+    assert len({np.round((x - x[0]) * 1e9).astype(np.int64).tobytes() for x in X}) == len(X)
 
 
 @pytest.mark.parametrize("name", CASES)
@@ -177,7 +182,11 @@ GOLDEN_BOX = {"uniform2d": ("uniform", dict(lower=[0, 0], upper=[1, 1], nelem=[3
               "tg2d": ("taylor-green", dict(lower=[0, 0], upper=[1, 1], nelem=[4, 3])),
               "tg3d": ("taylor-green3d", dict(lower=[0, 0, 0], upper=[1, 1, 1], nelem=[2, 3, 2])),
               "cavity2d": ("cavity-2d", dict(lower=[0, 0], upper=[1, 1], nelem=[4, 3])),
-              "cavity3d": ("cavity", dict(lower=[0, 0, 0], upper=[3, 1, 1], nelem=[3, 2, 2]))}
+              "cavity3d": ("cavity", dict(lower=[0, 0, 0], upper=[3, 1, 1], nelem=[3, 2, 2])),
+              "tg2d_p": ("taylor-green", dict(lower=[0, 0], upper=[1, 1], nelem=[3, 2], perturb=0.15)),
+              "tg3d_p": ("taylor-green3d", dict(lower=[0, 0, 0], upper=[1, 1, 1], nelem=[2, 2, 2], perturb=0.2)),
+              "cavity3d_p": ("cavity", dict(lower=[0, 0, 0], upper=[3, 1, 1], nelem=[3, 3, 2], perturb=0.2)),
+              "tg3d_ngl4": ("taylor-green3d", dict(lower=[0, 0, 0], upper=[2, 1, 1], nelem=[2, 1, 1]))}
 
 
 def product_domain(name, g):
