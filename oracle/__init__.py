@@ -19,7 +19,11 @@ Pinning: the element tables and element matrices are pinned against golden
 vectors generated from the reference's own ``Spectral`` class
 (``tests/golden/make_golden.py`` -> ``tests/golden/*.npz``); the assembled
 solve is pinned through the reference's known-answer tests KAT-1/2/3
-(``src/tests/test_solver.py``).  Global node numbering of PETSc DMPlex for
+(``src/tests/test_solver.py``); the assembled matrices (patterns bit for bit),
+the no-slip dof classes, the KLE solves, evalRHS and fixed RK5BS steps are pinned
+against outputs of the reference's own unmodified modules run over a numpy
+stand-in for petsc4py (``tests/refshim/``, ``tests/golden/make_golden_refpath.py``
+-> ``tests/golden/refpath_*.npz``, ``tests/test_reference_path.py``).  Global node numbering of PETSc DMPlex for
 ngl >= 3, PETSc's TS adaptivity and KSP internals are NOT in the reference
 tree: for those parts parity is unpinned.
 """
