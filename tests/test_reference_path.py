@@ -302,3 +302,51 @@ def test_goldens_are_what_the_reference_computes_now():
         a, b = np.asarray(out[k]), g[k]
         assert a.shape == b.shape and (np.array_equal(a, b) if a.dtype.kind in "iuUS" else
                                        np.abs(a - b).max() <= 1e-13 * max(np.abs(b).max(), 1.0)), k
+
+
+LIVE = {"cavity3d_6x4x4": ("cavity", dict(lower=[0, 0, 0], upper=[3, 1, 1], nelem=[6, 4, 4]), 3, 5e-3, 1),
+        "cavity2d_8x8_ngl4": ("cavity-2d", dict(lower=[0, 0], upper=[1, 1], nelem=[8, 8]), 4, 5e-3, 1),
+        "tg3d_4x4x4_p": ("taylor-green3d", dict(lower=[0, 0, 0], upper=[1, 1, 1], nelem=[4, 4, 4], perturb=0.2), 3,
+                         2e-3, 1)}
+
+
+@pytest.mark.skipif(not _ref_available(), reason="reference tree not present")
+@pytest.mark.parametrize("name", sorted(LIVE))
+def test_oracle_equals_the_reference_run_live_at_larger_sizes(name):
+    """sizes too large to commit as vectors (cavity above 3^3 cells, 4^3 non-affine cells): the reference's code is
+    run on the stand-ins now and the oracle compared with it directly -- matrices, first solve, evalRHS, one step"""
+    import contextlib
+    import importlib.util
+    import io
+    import logging
+    spec = importlib.util.spec_from_file_location("make_golden_refpath", os.path.join(GOLD, "make_golden_refpath.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    mod.CASES[name] = LIVE[name]
+    from tests.refshim.loader import reference_modules
+    logging.disable(logging.CRITICAL)
+    try:
+        with reference_modules() as ref, contextlib.redirect_stdout(io.StringIO()):
+            out = mod.run_case(ref, name)
+    finally:
+        logging.disable(logging.NOTSET)
+    g = type("G", (dict,), {"files": property(lambda self: list(self))})({k: np.asarray(v) for k, v in out.items()})
+    dim, ngl, n = int(g["dim"]), int(g["ngl"]), len(g["coords"])
+    ns = str(g["bc_type"]) == "NS"
+    cls, _, _ = dof_classes(g)
+    tab = sem.SpectralTables(ngl, dim)
+    mats = assembly.assemble_kle(tab, g["corner_xyz"], g["elem_nodes"], n, cls, "NS" if ns else "FS", reuse=False)
+    mats.update(assembly.assemble_ops(tab, g["corner_xyz"], g["elem_nodes"], n, reuse=False))
+    for nm in (KLE_NS if ns else ["K", "Krhs", "Rw"]) + OPS:
+        ref_m, m = golden_csr(g, nm), mats[nm].tocsr()
+        m.sort_indices()
+        assert np.array_equal(m.indptr, ref_m.indptr) and np.array_equal(m.indices, ref_m.indices), nm
+        assert np.abs(m.data - ref_m.data).max() <= 1e-13 * np.abs(ref_m.data).max(), nm
+    p = make_problem(g)
+    f = p.eval_rhs(float(g["t0"]))
+    assert np.abs(p.vel - g["vel1"]).max() <= 1e-10 * np.abs(g["vel1"]).max()
+    assert np.abs(f - g["rhs0"]).max() <= 1e-9 * np.abs(g["rhs0"]).max()
+    p = make_problem(g)
+    t, k0 = p.step(float(g["t0"]), float(g["dt"]), None)
+    assert np.abs(p.vort - g["vort_steps"]).max() <= 1e-9 * np.abs(g["vort_steps"]).max()
+    assert np.abs(p.vel - g["vel_steps"]).max() <= 1e-9 * np.abs(g["vel_steps"]).max()
