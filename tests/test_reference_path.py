@@ -110,18 +110,10 @@ def test_matrices_equal_the_reference(name):
 def test_no_slip_dof_classes_equal_the_reference(name):
     g = load(name)
     cls, _, _ = dof_classes(g)
-    assert np.array_equal(np.flatnonzero(cls == timestep_NORMAL()), g["normal_dofs"])
+    assert np.array_equal(np.flatnonzero(cls == assembly.NORMAL), g["normal_dofs"])
     # the reference's tangential set still holds the dofs that are also normal; the builder removes them (mat_ns.py:61)
     tang = np.setdiff1d(g["tang_dofs"], g["normal_dofs"])
-    assert np.array_equal(np.flatnonzero(cls == timestep_TANG()), tang)
-
-
-def timestep_NORMAL():
-    return assembly.NORMAL
-
-
-def timestep_TANG():
-    return assembly.TANG
+    assert np.array_equal(np.flatnonzero(cls == assembly.TANG), tang)
 
 
 def make_problem(g):
