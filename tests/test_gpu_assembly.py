@@ -45,7 +45,8 @@ def test_free_slip_matrices(nelem, ngl, perturb):
 
 
 NS_CASES = [([4, 3], 3, None), ([3, 3], 4, ["up", "left"]), ([3, 2, 2], 3, None),
-            ([2, 2, 2], 4, ["up", "down", "right"])]
+            ([2, 2, 2], 4, ["up", "down", "right"]),
+            ([8, 6, 6], 3, None)]         # a cavity mesh well above 3^3 cells (added after the last GPU call of round 2)
 
 
 @pytest.mark.parametrize("nelem,ngl,sides", NS_CASES)
