@@ -179,8 +179,11 @@ class GmshMesh:
         self._phys_by_name = {nm.lower(): tag for (d, tag), nm in msh["physical_names"].items() if d == dim - 1}
         # borders beyond the reference's six (four) box names: named physical groups of boundary faces,
         # e.g. the wall of a body inside the channel (cylinder_mesh.py); in tag order after the box sides
+        # (a tag within 1..len(sides) is already a box side by the reference's positional rule, whatever it is
+        # called in the file -- src/tests/test.msh names its whole boundary "External" with tag 1 = "down")
+        nbox = len(self.sides)
         extra = sorted((tag, nm) for (d, tag), nm in msh["physical_names"].items()
-                       if d == dim - 1 and nm.lower() not in self.sides and tag in self._border_faces)
+                       if d == dim - 1 and nm.lower() not in self.sides and tag > nbox and tag in self._border_faces)
         self.sides = list(self.sides) + [nm.lower() for _, nm in extra]
 
     def _min_edge(self):

@@ -2,6 +2,8 @@
 generator: a box mesh written to a .msh file with shuffled vertex numbering, shuffled cell order,
 rotated and mirrored cells must give the same nodes, borders and -- through the oracle -- the same
 KLE solution at the same coordinates."""
+import os
+
 import numpy as np
 import pytest
 import scipy.sparse.linalg as spl
@@ -136,3 +138,23 @@ def test_positional_border_rule(tmp_path):
     assert len(g.getBorderNodes("down")) == 5 and len(g.getBorderNodes("right")) == 3
     assert len(g.getBorderNodes("up")) == 5 and len(g.getBorderNodes("left")) == 3
     assert len(g.getBordersNodes()) == 12
+
+
+REF_MSH = os.path.join(os.environ.get("PYNAMA_REFERENCE", "/root/reference"), "src", "tests", "test.msh")
+
+
+@pytest.mark.skipif(not os.path.isfile(REF_MSH), reason="reference tree not present")
+def test_reference_gmsh_fixture_counts():
+    """the reference's own Gmsh known answers (src/tests/test_domain.py:39-48, :62-69: 'this number is from Gmsh')
+    on its own mesh file, read where it lies: 33 cells, 153 nodes at ngl = 3, 1688 at ngl = 8; the file's single
+    physical group of boundary edges has tag 1, which the reference's positional rule calls "down"
+    (dmplex.py:164-170), and no extra border is invented for it"""
+    from pynama_b200.domain.gmsh_mesh import GmshMesh
+    for ngl, nnodes in ((3, 153), (8, 1688)):
+        m = GmshMesh(REF_MSH, ngl)
+        assert m.dim == 2 and m.nel == 33 and m.nnodes == nnodes
+        assert m.getBordersNames() == ["down", "right", "up", "left"]
+        assert len(m.getBorderNodes("down")) == len(m.getBordersNodes()) > 0
+        assert all(len(m.getBorderNodes(s)) == 0 for s in ("right", "up", "left"))
+    m = GmshMesh(REF_MSH, 2)
+    assert m.nnodes == 44                      # the $Nodes header of the file
