@@ -38,6 +38,8 @@ from tests.refshim.loader import load_case, reference_modules  # noqa: E402
 
 CASES = {
     # name: (case file, box overrides, ngl, dt, steps)
+    # BASELINE.json configs[0]: 2-D Taylor-Green vortex, 4x4 spectral elements, ngl = 3 (the reference's correctness run)
+    "config0": ("taylor-green", dict(lower=[0, 0], upper=[1, 1], nelem=[4, 4]), 3, 2e-3, 3),
     "uniform2d": ("uniform", dict(lower=[0, 0], upper=[1, 1], nelem=[3, 3]), 3, 1e-2, 2),
     "tg2d": ("taylor-green", dict(lower=[0, 0], upper=[1, 1], nelem=[4, 3]), 4, 2e-3, 2),
     "tg3d": ("taylor-green3d", dict(lower=[0, 0, 0], upper=[1, 1, 1], nelem=[2, 3, 2]), 3, 2e-3, 2),
@@ -66,7 +68,9 @@ def run_case(ref, name):
     fem = ref.base_problem.BaseProblem(cfg, case=case)
     fem.setUp()
     fem.setUpSolver()
-    out = {"perturb": np.float64(box.get("perturb", 0.0)), "ngl": np.int64(ngl), "dim": np.int64(fem.dim), "dt": np.float64(dt), "nsteps": np.int64(nsteps),
+    out = {"box_lower": np.array(box["lower"], dtype=np.float64), "box_upper": np.array(box["upper"], dtype=np.float64),
+           "box_nelem": np.array(box["nelem"], dtype=np.int64),
+           "perturb": np.float64(box.get("perturb", 0.0)), "ngl": np.int64(ngl), "dim": np.int64(fem.dim), "dt": np.float64(dt), "nsteps": np.int64(nsteps),
            "rho": np.float64(fem.rho), "mu": np.float64(fem.mu), "bc_type": np.array(fem.dom.getBoundaryType()),
            "case": np.array(case)}
     dm = fem.dom.getDM()

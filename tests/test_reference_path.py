@@ -54,7 +54,7 @@ def dof_classes(g):
 
 
 def test_golden_files_present():
-    assert set(CASES) >= {"uniform2d", "tg2d", "tg3d", "cavity2d", "cavity3d", "tg2d_p", "tg3d_p", "cavity3d_p",
+    assert set(CASES) >= {"config0", "uniform2d", "tg2d", "tg3d", "cavity2d", "cavity3d", "tg2d_p", "tg3d_p", "cavity3d_p",
                           "tg3d_ngl4"}
     # the perturbed cases really have pairwise different cells
     g = load("tg3d_p")
@@ -170,21 +170,19 @@ def test_uniform_flow_stays_uniform_in_the_reference():
 
 
 # ---- the product's host layer (no device needed) against the same reference outputs --------------------------------
-GOLDEN_BOX = {"uniform2d": ("uniform", dict(lower=[0, 0], upper=[1, 1], nelem=[3, 3])),
-              "tg2d": ("taylor-green", dict(lower=[0, 0], upper=[1, 1], nelem=[4, 3])),
-              "tg3d": ("taylor-green3d", dict(lower=[0, 0, 0], upper=[1, 1, 1], nelem=[2, 3, 2])),
-              "cavity2d": ("cavity-2d", dict(lower=[0, 0], upper=[1, 1], nelem=[4, 3])),
-              "cavity3d": ("cavity", dict(lower=[0, 0, 0], upper=[3, 1, 1], nelem=[3, 2, 2])),
-              "tg2d_p": ("taylor-green", dict(lower=[0, 0], upper=[1, 1], nelem=[3, 2], perturb=0.15)),
-              "tg3d_p": ("taylor-green3d", dict(lower=[0, 0, 0], upper=[1, 1, 1], nelem=[2, 2, 2], perturb=0.2)),
-              "cavity3d_p": ("cavity", dict(lower=[0, 0, 0], upper=[3, 1, 1], nelem=[3, 3, 2], perturb=0.2)),
-              "tg3d_ngl4": ("taylor-green3d", dict(lower=[0, 0, 0], upper=[2, 1, 1], nelem=[2, 1, 1]))}
+def box_of(g):
+    """(case file, box keywords) the golden was made with"""
+    box = dict(lower=[float(v) for v in g["box_lower"]], upper=[float(v) for v in g["box_upper"]],
+               nelem=[int(v) for v in g["box_nelem"]])
+    if float(g["perturb"]):
+        box["perturb"] = float(g["perturb"])
+    return str(g["case"]), box
 
 
 def product_domain(name, g):
     from pynama_b200.domain.domain import Domain
     from pynama_b200.run_case import loadCase
-    case, box = GOLDEN_BOX[name]
+    case, box = box_of(g)
     cfg = loadCase(case)                                   # the product's copy of the reference's case file
     dom = Domain()
     dom.configure(cfg)

@@ -1,6 +1,6 @@
 """GPU parity against the reference's OWN outputs: tests/golden/refpath_*.npz (the reference's unmodified
 Domain / MatFS / MatNS / KleSolver / BaseProblem.evalRHS run over the numpy stand-in for petsc4py, see
-tests/golden/make_golden_refpath.py).  Nine cases: free-slip 2-D / 3-D and no-slip cavity 2-D / 3-D, affine and
+tests/golden/make_golden_refpath.py).  Ten cases (BASELINE.json configs[0] among them): free-slip 2-D / 3-D and no-slip cavity 2-D / 3-D, affine and
 non-affine cells, ngl 2-5.
 
 * every assembled matrix (K, Krhs, Rw, Rd, Kfs, Krhsfs, Rwfs, Rdfs, Curl, SrT, DivSrT) through the C ABI:
@@ -25,15 +25,17 @@ from tests.util import assert_same_csr, csr_of
 pytestmark = pytest.mark.gpu
 GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 CASES = sorted(os.path.basename(p)[len("refpath_"):-4] for p in glob.glob(os.path.join(GOLD, "refpath_*.npz")))
-BOX = {"uniform2d": ("uniform", dict(lower=[0, 0], upper=[1, 1], nelem=[3, 3])),
-       "tg2d": ("taylor-green", dict(lower=[0, 0], upper=[1, 1], nelem=[4, 3])),
-       "tg3d": ("taylor-green3d", dict(lower=[0, 0, 0], upper=[1, 1, 1], nelem=[2, 3, 2])),
-       "cavity2d": ("cavity-2d", dict(lower=[0, 0], upper=[1, 1], nelem=[4, 3])),
-       "cavity3d": ("cavity", dict(lower=[0, 0, 0], upper=[3, 1, 1], nelem=[3, 2, 2])),
-       "tg2d_p": ("taylor-green", dict(lower=[0, 0], upper=[1, 1], nelem=[3, 2], perturb=0.15)),
-       "tg3d_p": ("taylor-green3d", dict(lower=[0, 0, 0], upper=[1, 1, 1], nelem=[2, 2, 2], perturb=0.2)),
-       "cavity3d_p": ("cavity", dict(lower=[0, 0, 0], upper=[3, 1, 1], nelem=[3, 3, 2], perturb=0.2)),
-       "tg3d_ngl4": ("taylor-green3d", dict(lower=[0, 0, 0], upper=[2, 1, 1], nelem=[2, 1, 1]))}
+
+
+def box_of(g):
+    """(case file, box keywords) the golden was made with"""
+    box = dict(lower=[float(v) for v in g["box_lower"]], upper=[float(v) for v in g["box_upper"]],
+               nelem=[int(v) for v in g["box_nelem"]])
+    if float(g["perturb"]):
+        box["perturb"] = float(g["perturb"])
+    return str(g["case"]), box
+
+
 TOL = 1e-8
 
 
@@ -100,7 +102,7 @@ def test_fields_after_fixed_steps_equal_the_reference_goldens(name):
                  ("ksp_max_it", 50000), ("ts_adapt_type", "none"), ("ts_dt", float(g["dt"]))):
         o.setValue(k, v)
     o.delValue("ksp_fischer_guess")
-    case, box = BOX[name]
+    case, box = box_of(g)
     cfg = loadCase(case)
     fem = BaseProblem(cfg, case=case, ngl=int(g["ngl"]), **box)
     fem.setUp()
