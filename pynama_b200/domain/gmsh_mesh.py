@@ -30,7 +30,7 @@ NODES_OF_TYPE = {15: 1, 1: 2, 3: 4, 5: 8}
 
 
 def read_msh(path):
-    """Minimal Gmsh 4.1 ASCII reader -> dict(physical_names, entity_physical, nodes, elements).
+    """Minimal Gmsh ASCII reader (MSH 4.1 and MSH 2.2) -> dict(physical_names, entity_physical, nodes, elements).
     nodes: {tag: xyz}; elements: {type: (entity_dim, entity_tag, node tags)[]}"""
     with open(path) as f:
         tok = f.read().split("\n")
@@ -45,12 +45,14 @@ def read_msh(path):
         elif name is not None and s:
             buf.append(s)
     ver = float(sections["MeshFormat"][0].split()[0])
-    if not 4.0 <= ver < 5.0 or int(sections["MeshFormat"][0].split()[1]) != 0:
-        raise ValueError(f"{path}: only Gmsh 4.x ASCII files are supported (found {sections['MeshFormat'][0]})")
+    if int(sections["MeshFormat"][0].split()[1]) != 0 or not (2.0 <= ver < 3.0 or 4.0 <= ver < 5.0):
+        raise ValueError(f"{path}: only Gmsh 2.x and 4.x ASCII files are supported (found {sections['MeshFormat'][0]})")
     phys = {}
     for s in sections.get("PhysicalNames", [])[1:]:
         d, tag, nm = s.split(None, 2)
         phys[(int(d), int(tag))] = nm.strip().strip('"')
+    if ver < 3.0:
+        return _read_msh2(sections, phys)
     ent_phys = {}
     ent = sections.get("Entities", [])
     if ent:
@@ -85,6 +87,35 @@ def read_msh(path):
             if nn is not None:
                 elements.setdefault(typ, []).append((ed, et, v[1:1 + nn]))
         i += 1 + n
+    return {"physical_names": phys, "entity_physical": ent_phys, "nodes": nodes, "elements": elements}
+
+
+DIM_OF_TYPE = {15: 0, 1: 1, 3: 2, 5: 3}
+
+
+def _read_msh2(sections, phys):
+    """MSH 2.x ASCII (what DMPlexCreateFromFile of PETSc 3.12 also reads): `$Nodes` = count, then `id x y z`;
+    `$Elements` = count, then `id type ntags physical elementary ... node ids`.  Mapped to the structure of the
+    4.1 reader: the elementary tag is the entity, its physical tag the entity's physical group."""
+    nodes = {}
+    for s in sections["Nodes"][1:]:
+        v = s.split()
+        nodes[int(v[0])] = [float(x) for x in v[1:4]]
+    elements, ent_phys = {}, {}
+    for s in sections["Elements"][1:]:
+        v = [int(t) for t in s.split()]
+        typ, ntags = v[1], v[2]
+        nn = NODES_OF_TYPE.get(typ)
+        if nn is None:
+            continue
+        physical = v[3] if ntags >= 1 else 0
+        elementary = v[4] if ntags >= 2 else physical
+        d = DIM_OF_TYPE[typ]
+        elements.setdefault(typ, []).append((d, elementary, v[3 + ntags:3 + ntags + nn]))
+        if physical:
+            tags = ent_phys.setdefault((d, elementary), [])
+            if physical not in tags:
+                tags.append(physical)
     return {"physical_names": phys, "entity_physical": ent_phys, "nodes": nodes, "elements": elements}
 
 
@@ -242,13 +273,15 @@ class GmshMesh:
         return self.coords[np.asarray(nodes, dtype=np.int64)]
 
 
-def write_msh(path, vxyz, cells, boundary, physical_names=None):
+def write_msh(path, vxyz, cells, boundary, physical_names=None, version=4.1):
     """Gmsh 4.1 ASCII writer for tests and synthetic unstructured inputs.  vxyz [nv, 2|3];
     cells [nel, 4|8] vertex ids in GMSH order; boundary: list of (physical tag, vertex ids)."""
     vxyz = np.asarray(vxyz, dtype=np.float64)
     dim = vxyz.shape[1]
     cells = np.asarray(cells)
     tags = sorted({t for t, _ in boundary})
+    if version < 3.0:
+        return _write_msh2(path, vxyz, cells, boundary, physical_names or {}, dim)
     with open(path, "w") as f:
         f.write("$MeshFormat\n4.1 0 8\n$EndMeshFormat\n")
         names = physical_names or {}
@@ -283,5 +316,29 @@ def write_msh(path, vxyz, cells, boundary, physical_names=None):
         f.write(f"{dim} 1 {CELL_TYPE[dim]} {len(cells)}\n")
         for c in cells:
             f.write(f"{k} " + " ".join(str(int(i) + 1) for i in c) + "\n")
+            k += 1
+        f.write("$EndElements\n")
+
+
+def _write_msh2(path, vxyz, cells, boundary, names, dim):
+    """the same mesh as an MSH 2.2 ASCII file (boundary elements first, physical tag = elementary tag)"""
+    with open(path, "w") as f:
+        f.write("$MeshFormat\n2.2 0 8\n$EndMeshFormat\n")
+        f.write(f"$PhysicalNames\n{len(names)}\n")
+        for (d, t), nm in names.items():
+            f.write(f'{d} {t} "{nm}"\n')
+        f.write("$EndPhysicalNames\n")
+        f.write(f"$Nodes\n{len(vxyz)}\n")
+        for i, x in enumerate(vxyz):
+            xx = list(x) + [0.0] * (3 - dim)
+            f.write(f"{i + 1} {xx[0]:.17g} {xx[1]:.17g} {xx[2]:.17g}\n")
+        f.write("$EndNodes\n")
+        f.write(f"$Elements\n{len(cells) + len(boundary)}\n")
+        k = 1
+        for t, v in boundary:
+            f.write(f"{k} {FACE_TYPE[dim]} 2 {t} {t} " + " ".join(str(int(i) + 1) for i in v) + "\n")
+            k += 1
+        for c in cells:
+            f.write(f"{k} {CELL_TYPE[dim]} 2 1000 1 " + " ".join(str(int(i) + 1) for i in c) + "\n")
             k += 1
         f.write("$EndElements\n")

@@ -15,7 +15,7 @@ from pynama_b200.domain.gmsh_mesh import GmshMesh, read_msh, write_msh
 CLOSURE_TO_GMSH_HEX = [0, 3, 2, 1, 4, 5, 6, 7]
 
 
-def box_as_msh(path, nelem, perturb=0.1, seed=1, scramble=True):
+def box_as_msh(path, nelem, perturb=0.1, seed=1, scramble=True, version=4.1):
     dim = len(nelem)
     box = BoxMesh(nelem, [0.0] * dim, [1.0, 1.5, 0.75][:dim], 2, perturb=perturb)      # ngl=2: nodes = vertices
     rng = np.random.default_rng(seed)
@@ -64,7 +64,7 @@ def box_as_msh(path, nelem, perturb=0.1, seed=1, scramble=True):
                     on = [on[i] for i in np.argsort(ang)]
                 boundary.append((k + 1, perm[on]))
     names[(dim, 1000)] = "Internal"
-    write_msh(path, vxyz, cells, boundary, names)
+    write_msh(path, vxyz, cells, boundary, names, version=version)
     return box
 
 
@@ -120,10 +120,29 @@ def test_same_kle_solution_on_both_meshes(tmp_path):
 
 
 def test_reader_rejects_other_formats(tmp_path):
-    p = tmp_path / "old.msh"
-    p.write_text("$MeshFormat\n2.2 0 8\n$EndMeshFormat\n")
+    p = tmp_path / "bin.msh"
+    p.write_text("$MeshFormat\n4.1 1 8\n$EndMeshFormat\n")                 # binary
     with pytest.raises(ValueError):
         read_msh(str(p))
+    p.write_text("$MeshFormat\n1.0 0 8\n$EndMeshFormat\n")
+    with pytest.raises(ValueError):
+        read_msh(str(p))
+
+
+@pytest.mark.parametrize("nelem,ngl", [([4, 3], 3), ([3, 2, 2], 3)])
+def test_msh22_file_gives_the_same_mesh_as_msh41(tmp_path, nelem, ngl):
+    """MSH 2.2 ASCII (PETSc 3.12's DMPlexCreateFromFile reads both): same scrambled mesh written in both formats"""
+    p4, p2 = str(tmp_path / "a41.msh"), str(tmp_path / "a22.msh")
+    box_as_msh(p4, nelem, version=4.1)
+    box_as_msh(p2, nelem, version=2.2)
+    assert open(p2).read().startswith("$MeshFormat\n2.2 0 8")
+    a, b = GmshMesh(p4, ngl), GmshMesh(p2, ngl)
+    assert (a.dim, a.nel, a.nnodes) == (b.dim, b.nel, b.nnodes)
+    assert np.array_equal(a.elem_nodes, b.elem_nodes) and np.abs(a.corner_xyz - b.corner_xyz).max() == 0.0
+    assert np.abs(a.coords - b.coords).max() == 0.0 and a.getBordersNames() == b.getBordersNames()
+    for s_ in a.getBordersNames():
+        assert np.array_equal(a.getBorderNodes(s_), b.getBorderNodes(s_)) and len(a.getBorderNodes(s_)) > 0
+    assert np.array_equal(a.getBordersNodes(), b.getBordersNodes())
 
 
 def test_positional_border_rule(tmp_path):
